@@ -1,0 +1,621 @@
+// TEST INFRASTRUCTURE — driver around the UNMODIFIED reference hot path.
+//
+// oracle/Makefile compiles this file together with /root/reference/first_ray/{path,hitable,
+// hitable_list,scene,pdf,material,texture,image}.cpp (from where they lie) into
+// oracle/_ref/frt_ref (std::mt19937 sampler, as shipped) and oracle/_ref/frt_ref_ctr
+// (-DFRT_REF_CTR_RNG, counter-based sampler from ref_prelude.h).  Everything that decides a
+// pixel value or a hit — path::Li, parallel_bvh_node, triangle, sphere, material, pdf,
+// microfacet, camera — is the reference's own object code.
+//
+// What is NOT the reference here (documented deviations):
+//  * mesh_loader.cpp / triangle.cpp need Assimp (cmake + generated config.h): not built.  The
+//    OBJ/MTL reader below feeds the reference's own triangle_mesh / triangle classes and
+//    restates the MTL→material mapping of mesh_loader.cpp:59-112 and its fallback vertex
+//    normals (mesh_loader.cpp:114-155).
+//  * path::Render only covers rows 101..209 (path.cpp:120); the row loop below covers the
+//    whole frame like ao.h:17 does, on the reference's own tf::Taskflow.
+//  * veach_mis(): plates become rough_conductor (alphas from veach_mi/mi.xml), root becomes
+//    parallel_bvh_node (main.cpp:313 alternative), as BASELINE config 3 asks.
+//
+// Commands (all print one JSON line on stdout):
+//   frt_ref trace  <scene> <aspect> closest|shadow <rays.f32> <out.bin>
+//   frt_ref render <scene> <w> <h> <spp> <out.pfm> [--threads N] [--seed S] [--rows y0 y1] [--ystep K]
+//   frt_ref dump   <scene> <aspect> <out.bin>
+#include "Scene.h"
+#include "sphere.h"
+#include "triangle.h"
+#include "material.h"
+#include "camera.h"
+#include "texture.h"
+#include "util.h"
+#include "bvh.h"
+#include "parallel_bvh.h"
+#include "pdf.h"
+#include "sampler.h"
+#include "integrator.h"
+#include "path.h"
+
+static std::string g_assets = "assets";
+
+// ------------------------------------------------------------------------------------------
+// OBJ / MTL reader (driver-side stand-in for Assimp; see header comment)
+// ------------------------------------------------------------------------------------------
+struct mtl_entry
+{
+    float Kd[3] = {0.6f, 0.6f, 0.6f}, Ks[3] = {0, 0, 0}, Ke[3] = {0, 0, 0};
+    float Ns = 0.f, Ni = 1.f, d = 1.f;
+};
+
+static std::map<std::string, mtl_entry> read_mtl(const std::string &path)
+{
+    std::map<std::string, mtl_entry> out;
+    std::ifstream is(path);
+    std::string line, cur;
+    while (std::getline(is, line))
+    {
+        const size_t hash = line.find('#');
+        if (hash != std::string::npos) line.resize(hash);
+        std::istringstream ss(line);
+        std::string key;
+        if (!(ss >> key)) continue;
+        if (key == "newmtl") { ss >> cur; out[cur] = mtl_entry(); continue; }
+        if (cur.empty()) continue;
+        mtl_entry &m = out[cur];
+        if (key == "Kd") ss >> m.Kd[0] >> m.Kd[1] >> m.Kd[2];
+        else if (key == "Ks") ss >> m.Ks[0] >> m.Ks[1] >> m.Ks[2];
+        else if (key == "Ke") ss >> m.Ke[0] >> m.Ke[1] >> m.Ke[2];
+        else if (key == "Ns") ss >> m.Ns;
+        else if (key == "Ni") ss >> m.Ni;
+        else if (key == "d") ss >> m.d;
+    }
+    return out;
+}
+
+// mesh_loader.cpp:59-112
+static std::unique_ptr<material> material_from_mtl(const mtl_entry *m)
+{
+    if (!m)
+        return std::make_unique<lambertian>(new constant_texture(Vector3f(0.5, 0.5, 0.5)));
+    if (m->Ke[0] != 0 || m->Ke[1] != 0 || m->Ke[2] != 0)
+        return std::make_unique<diffuse_light>(new constant_texture(Vector3f(m->Ke[0], m->Ke[1], m->Ke[2])));
+    if (m->Ks[0] != 0 || m->Ks[1] != 0 || m->Ks[2] != 0)
+    {
+        const Vector3f ks(FromSrgb(m->Ks[0]), FromSrgb(m->Ks[1]), FromSrgb(m->Ks[2]));
+        if (double(m->d) < 1.0)
+            return std::make_unique<dielectric>(double(m->Ni), new constant_texture(ks),
+                                                new constant_texture(Vector3f(1.0, 1.0, 1.0)));
+        const Vector3f kd(FromSrgb(m->Kd[0]), FromSrgb(m->Kd[1]), FromSrgb(m->Kd[2]));
+        return std::make_unique<modified_phong>(new constant_texture(kd), new constant_texture(ks), double(m->Ns));
+    }
+    return std::make_unique<lambertian>(
+        new constant_texture(Vector3f(FromSrgb(m->Kd[0]), FromSrgb(m->Kd[1]), FromSrgb(m->Kd[2]))));
+}
+
+struct raw_mesh
+{
+    std::string group, mtl;
+    std::map<std::array<int, 3>, int> remap;
+    std::vector<Vector3f> v, n;
+    std::vector<Vector2f> t;
+    std::vector<int> idx;
+    bool has_normals = true;
+};
+
+static std::vector<std::shared_ptr<triangle_mesh>> read_obj(const std::string &file, bool use_geometry_normals)
+{
+    std::ifstream is(file);
+    if (!is.is_open()) throw std::runtime_error("cannot open " + file);
+    const std::string dir = file.substr(0, file.find_last_of('/') + 1);
+    std::vector<std::array<float, 3>> P, N;
+    std::vector<std::array<float, 2>> T;
+    std::map<std::string, mtl_entry> mtls;
+    std::vector<raw_mesh> meshes;
+    std::map<std::pair<std::string, std::string>, int> mesh_of;
+    std::string group = "default", mtl = "";
+    std::string line;
+    while (std::getline(is, line))
+    {
+        const size_t hash = line.find('#');
+        if (hash != std::string::npos) line.resize(hash);
+        std::istringstream ss(line);
+        std::string key;
+        if (!(ss >> key)) continue;
+        if (key == "v") { std::array<float, 3> p; ss >> p[0] >> p[1] >> p[2]; P.push_back(p); }
+        else if (key == "vn") { std::array<float, 3> p; ss >> p[0] >> p[1] >> p[2]; N.push_back(p); }
+        else if (key == "vt") { std::array<float, 2> p; ss >> p[0] >> p[1]; T.push_back(p); }
+        else if (key == "g" || key == "o") { group = "default"; ss >> group; }
+        else if (key == "usemtl") { mtl = ""; ss >> mtl; }
+        else if (key == "mtllib") { std::string f; ss >> f; auto m = read_mtl(dir + f); mtls.insert(m.begin(), m.end()); }
+        else if (key == "f")
+        {
+            auto mk = std::make_pair(group, mtl);
+            auto it = mesh_of.find(mk);
+            if (it == mesh_of.end())
+            {
+                it = mesh_of.emplace(mk, (int)meshes.size()).first;
+                meshes.emplace_back();
+                meshes.back().group = group;
+                meshes.back().mtl = mtl;
+            }
+            raw_mesh &m = meshes[it->second];
+            std::vector<int> corner;
+            std::string tok;
+            while (ss >> tok)
+            {
+                int vi = 0, ti = 0, ni = 0;
+                const size_t s1 = tok.find('/');
+                vi = std::atoi(tok.substr(0, s1).c_str());
+                if (s1 != std::string::npos)
+                {
+                    const size_t s2 = tok.find('/', s1 + 1);
+                    const std::string a = tok.substr(s1 + 1, s2 == std::string::npos ? std::string::npos : s2 - s1 - 1);
+                    if (!a.empty()) ti = std::atoi(a.c_str());
+                    if (s2 != std::string::npos) ni = std::atoi(tok.substr(s2 + 1).c_str());
+                }
+                if (vi < 0) vi = (int)P.size() + vi + 1;
+                if (ti < 0) ti = (int)T.size() + ti + 1;
+                if (ni < 0) ni = (int)N.size() + ni + 1;
+                std::array<int, 3> k = {vi, ti, ni};
+                auto f = m.remap.find(k);
+                if (f == m.remap.end())
+                {
+                    f = m.remap.emplace(k, (int)m.v.size()).first;
+                    m.v.push_back(Vector3f(P[vi - 1][0], P[vi - 1][1], P[vi - 1][2]));
+                    m.t.push_back(ti ? Vector2f(T[ti - 1][0], T[ti - 1][1]) : Vector2f(0, 0));
+                    if (ni) m.n.push_back(Vector3f(N[ni - 1][0], N[ni - 1][1], N[ni - 1][2]));
+                    else { m.n.push_back(Vector3f(0, 0, 0)); m.has_normals = false; }
+                }
+                corner.push_back(f->second);
+            }
+            for (size_t k = 1; k + 1 < corner.size(); ++k)
+            {
+                m.idx.push_back(corner[0]);
+                m.idx.push_back(corner[k]);
+                m.idx.push_back(corner[k + 1]);
+            }
+        }
+    }
+
+    std::vector<std::shared_ptr<triangle_mesh>> out;
+    for (raw_mesh &m : meshes)
+    {
+        const int nv = (int)m.v.size(), nt = (int)m.idx.size() / 3;
+        Vector3f *vertices = new Vector3f[nv];
+        Vector3f *normals = new Vector3f[nv];
+        Vector2f *uv = new Vector2f[nv];
+        for (int i = 0; i < nv; ++i) { vertices[i] = m.v[i]; normals[i] = m.n[i]; uv[i] = m.t[i]; }
+        if (!m.has_normals)
+        {
+            // mesh_loader.cpp:114-155 (angle-weighted facet normals)
+            for (int i = 0; i < nv; ++i) normals[i] = Vector3f(0, 0, 0);
+            for (int j = 0; j < nt; ++j)
+            {
+                Vector3f n(0.0, 0.0, 0.0);
+                const int *V = &m.idx[3 * j];
+                for (int i = 0; i < 3; ++i)
+                {
+                    const Vector3f &v0 = vertices[V[i]];
+                    const Vector3f &v1 = vertices[V[(i + 1) % 3]];
+                    const Vector3f &v2 = vertices[V[(i + 2) % 3]];
+                    const Vector3f e1 = v1 - v0, e2 = v2 - v0;
+                    if (i == 0)
+                    {
+                        n = cross(e1, e2);
+                        const double length = n.length();
+                        if (length == 0) break;
+                        n /= length;
+                    }
+                    const double angle = unit_angle(unit_vector(e1), unit_vector(e2));
+                    normals[V[i]] += n * angle;
+                }
+            }
+            for (int i = 0; i < nv; ++i)
+            {
+                const double length = normals[i].length();
+                if (length != 0) normals[i] /= length; else normals[i] = Vector3f(1, 0, 0);
+            }
+        }
+        const mtl_entry *me = nullptr;
+        auto f = mtls.find(m.mtl);
+        if (!m.mtl.empty() && f != mtls.end()) me = &f->second;
+        out.push_back(std::make_shared<triangle_mesh>(nt, nv, vertices, m.idx.data(), normals, uv,
+                                                      material_from_mtl(me), use_geometry_normals,
+                                                      me ? m.mtl : std::string("unknown"), true));
+        out.back()->name = m.group; // group name is what the scene builders key on
+    }
+    return out;
+}
+
+// triangle.cpp:9-26 without the Assimp call
+static void push_triangles(const std::vector<std::shared_ptr<triangle_mesh>> &meshes,
+                           std::vector<std::shared_ptr<hitable>> &tris, std::vector<hitable *> &lights)
+{
+    for (auto &mesh : meshes)
+        for (int i = 0; i < mesh->nTriangles; ++i)
+        {
+            tris.push_back(std::make_shared<triangle>(mesh, i));
+            if (dynamic_cast<diffuse_light *>(mesh->mat.get()))
+                lights.push_back(tris.back().get());
+        }
+}
+
+static std::shared_ptr<triangle_mesh> quad_mesh(const Vector3f &a, const Vector3f &b, const Vector3f &c,
+                                                const Vector3f &d, std::unique_ptr<material> mat, const char *name)
+{
+    Vector3f *v = new Vector3f[4]{a, b, c, d};
+    const Vector3f nn = unit_vector(cross(b - a, c - a));
+    Vector3f *n = new Vector3f[4]{nn, nn, nn, nn};
+    Vector2f *uv = new Vector2f[4]{Vector2f(0, 0), Vector2f(1, 0), Vector2f(1, 1), Vector2f(0, 1)};
+    const int idx[6] = {0, 1, 2, 0, 2, 3};
+    return std::make_shared<triangle_mesh>(2, 4, v, idx, n, uv, std::move(mat), true, name, true);
+}
+
+// ------------------------------------------------------------------------------------------
+// Scenes
+// ------------------------------------------------------------------------------------------
+struct built_scene
+{
+    std::unique_ptr<Scene> scene;
+    std::vector<std::shared_ptr<hitable>> keep;          // owners of triangles
+    std::vector<hitable *> creation_order;                // primitive id = index here
+    std::vector<std::shared_ptr<triangle_mesh>> meshes;
+};
+
+static built_scene &build_scene(const std::string &name, double aspect)
+{
+    built_scene &b = *new built_scene;
+    std::vector<hitable *> lights;
+    std::vector<hitable *> list;
+    camera cam;
+    Vector3f env(0, 0, 0);
+
+    if (name == "cornell" || name == "cornell_glossy" || name == "cornell_sphere")
+    {
+        // main.cpp:222-252 (cornell_box_obj)
+        const char *file = name == "cornell" ? "/CornellBox/CornellBox-Original.obj"
+                         : name == "cornell_glossy" ? "/CornellBox/CornellBox-Glossy.obj"
+                                                    : "/CornellBox/CornellBox-Sphere.obj";
+        b.meshes = read_obj(g_assets + file, true);
+        push_triangles(b.meshes, b.keep, lights);
+        for (auto &t : b.keep) list.push_back(t.get());
+        cam = camera(Vector3f(0, 1, 3.9f), Vector3f(0, 1, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.0, 10.0);
+    }
+    else if (name == "veach")
+    {
+        // main.cpp:281-314 (veach_mis) + SURVEY §8c(iii)
+        b.meshes = read_obj(g_assets + "/veach_mi/veach_mi.obj", false);
+        const double alpha[4] = {0.005, 0.02, 0.05, 0.1}; // veach_mi/mi.xml:84,95,106,117
+        for (auto &m : b.meshes)
+            for (int p = 0; p < 4; ++p)
+                if (m->name == "plate" + std::to_string(p + 1))
+                    m->mat.reset(new rough_conductor(alpha[p], 1.0, Vector3f(1.65746, 0.880369, 0.521229),
+                                                     Vector3f(9.22387, 6.26952, 4.837),
+                                                     new constant_texture(Vector3f(1, 1, 1)), "ggx"));
+        push_triangles(b.meshes, b.keep, lights);
+        for (auto &t : b.keep) list.push_back(t.get());
+        const Vector3f c[5] = {Vector3f(10, 10, 4), Vector3f(-1.25f, 0, 0), Vector3f(-3.75f, 0, 0),
+                               Vector3f(1.25f, 0, 0), Vector3f(3.75f, 0, 0)};
+        const double r[5] = {0.5, 0.1f, 0.03333f, 0.3f, 0.9f};
+        const double e[5] = {800, 100, 901.803f, 11.1111f, 1.23457};
+        for (int i = 0; i < 5; ++i)
+        {
+            list.push_back(new sphere(c[i], r[i], new diffuse_light(new constant_texture(Vector3f(e[i], e[i], e[i])))));
+            lights.push_back(new sphere(c[i], r[i], new diffuse_light(new constant_texture(Vector3f(e[i], e[i], e[i])))));
+        }
+        cam = camera(Vector3f(0, 2, 15), Vector3f(0, -2, 2.5), Vector3f(0, 1, 0), 28.0, aspect, 0.0, 50.0);
+    }
+    else if (name == "teapot")
+    {
+        // stand-in for the unshipped Mitsuba matpreview mesh; camera from
+        // furnace_test_scene main.cpp:207-212
+        b.meshes = read_obj(g_assets + "/cube/teapot.obj", false);
+        b.meshes.push_back(quad_mesh(Vector3f(-150, 0, -150), Vector3f(-150, 0, 150), Vector3f(150, 0, 150),
+                                     Vector3f(150, 0, -150),
+                                     std::make_unique<lambertian>(new constant_texture(Vector3f(0.4, 0.4, 0.4))), "floor"));
+        b.meshes.push_back(quad_mesh(Vector3f(-40, 160, -40), Vector3f(40, 160, -40), Vector3f(40, 160, 40),
+                                     Vector3f(-40, 160, 40),
+                                     std::make_unique<diffuse_light>(new constant_texture(Vector3f(30, 30, 30))), "light"));
+        push_triangles(b.meshes, b.keep, lights);
+        for (auto &t : b.keep) list.push_back(t.get());
+        cam = camera(Vector3f(0, 125, 175.0), Vector3f(0, 50, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.0, 300.0);
+        env = Vector3f(0.05, 0.06, 0.08);
+    }
+    else if (name.rfind("soupfile:", 0) == 0)
+    {
+        // raw float32 triangle soup: n x 9 floats (v0,v1,v2), one lambertian mesh
+        std::ifstream is(name.substr(9), std::ios::binary);
+        if (!is.is_open()) throw std::runtime_error("cannot open soup file");
+        is.seekg(0, std::ios::end);
+        const size_t bytes = is.tellg();
+        is.seekg(0);
+        const int nt = int(bytes / 36);
+        std::vector<float> raw(size_t(nt) * 9);
+        is.read((char *)raw.data(), bytes);
+        Vector3f *v = new Vector3f[size_t(nt) * 3];
+        Vector3f *n = new Vector3f[size_t(nt) * 3];
+        Vector2f *uv = new Vector2f[size_t(nt) * 3];
+        std::vector<int> idx(size_t(nt) * 3);
+        for (size_t i = 0; i < size_t(nt) * 3; ++i)
+        {
+            v[i] = Vector3f(raw[3 * i], raw[3 * i + 1], raw[3 * i + 2]);
+            n[i] = Vector3f(0, 0, 1);
+            uv[i] = Vector2f(0, 0);
+            idx[i] = int(i);
+        }
+        b.meshes.push_back(std::make_shared<triangle_mesh>(nt, nt * 3, v, idx.data(), n, uv,
+                           std::make_unique<lambertian>(new constant_texture(Vector3f(0.5, 0.5, 0.5))), true, "soup", true));
+        push_triangles(b.meshes, b.keep, lights);
+        for (auto &t : b.keep) list.push_back(t.get());
+        cam = camera(Vector3f(0.5, 0.5, 3.0), Vector3f(0.5, 0.5, 0.5), Vector3f(0, 1, 0), 30.0, aspect, 0.0, 10.0);
+        env = Vector3f(1, 1, 1);
+    }
+    else
+        throw std::runtime_error("unknown scene " + name);
+
+    b.creation_order = list;
+    hitable **arr = new hitable *[list.size()];
+    for (size_t i = 0; i < list.size(); ++i) arr[i] = list[i];
+    b.scene.reset(new Scene(parallel_bvh_node::create_bvh(arr, (int)list.size(), 0.0, 0.0),
+                            new environment_map(std::make_unique<constant_texture>(env)), cam, lights));
+    return b;
+}
+
+// ------------------------------------------------------------------------------------------
+// Ray counting wrapper (closest: t_max == FLT_MAX, shadow: t_max < 2), SURVEY §8d
+// ------------------------------------------------------------------------------------------
+static std::atomic<uint64_t> g_closest{0}, g_shadow{0};
+static thread_local uint64_t tl_closest = 0, tl_shadow = 0;
+struct counting_world : public hitable
+{
+    counting_world(hitable *inner_) : inner(inner_) {}
+    bool hit(const ray &r, double t_min, double t_max, hit_record &rec) const override
+    {
+        if (t_max < 2.0) ++tl_shadow; else ++tl_closest;
+        return inner->hit(r, t_min, t_max, rec);
+    }
+    bool bounding_box(double t0, double t1, aabb &b) const override { return inner->bounding_box(t0, t1, b); }
+    std::unique_ptr<hitable> inner;
+};
+static void flush_counts()
+{
+    g_closest += tl_closest; g_shadow += tl_shadow; tl_closest = tl_shadow = 0;
+}
+
+static double now_s()
+{
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// ------------------------------------------------------------------------------------------
+static int cmd_trace(int argc, char **argv)
+{
+    if (argc < 7) return 2;
+    const std::string scene_name = argv[2];
+    const double aspect = std::atof(argv[3]);
+    const bool shadow = std::string(argv[4]) == "shadow";
+    const double t0 = now_s();
+    built_scene &b = build_scene(scene_name, aspect);
+    const double t_build = now_s() - t0;
+    std::map<const hitable *, int> id_of;
+    for (size_t i = 0; i < b.creation_order.size(); ++i) id_of[b.creation_order[i]] = (int)i;
+
+    std::ifstream is(argv[5], std::ios::binary);
+    is.seekg(0, std::ios::end);
+    const size_t n = size_t(is.tellg()) / 24;
+    is.seekg(0);
+    std::vector<float> rays(n * 6);
+    is.read((char *)rays.data(), n * 24);
+
+    std::vector<int32_t> prim(n);
+    std::vector<double> tt(n), uu(n), vv(n);
+    const double t1 = now_s();
+    for (size_t i = 0; i < n; ++i)
+    {
+        const ray r(Vector3f(rays[6 * i], rays[6 * i + 1], rays[6 * i + 2]),
+                    Vector3f(rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5]));
+        hit_record rec;
+        // path.cpp:10 / path.cpp:50
+        const bool h = shadow ? b.scene->world->hit(r, EPSILON, 1 - SHADOW_EPSILON, rec)
+                              : b.scene->world->hit(r, EPSILON, FLT_MAX, rec);
+        prim[i] = h ? id_of[rec.obj] : -1;
+        tt[i] = h ? rec.t : 0.0;
+        uu[i] = h ? rec.uv.x : 0.0;
+        vv[i] = h ? rec.uv.y : 0.0;
+    }
+    const double t_trace = now_s() - t1;
+    std::ofstream os(argv[6], std::ios::binary | std::ios::trunc);
+    os.write((char *)prim.data(), n * 4);
+    os.write((char *)tt.data(), n * 8);
+    os.write((char *)uu.data(), n * 8);
+    os.write((char *)vv.data(), n * 8);
+    std::printf("{\"cmd\": \"trace\", \"scene\": \"%s\", \"n_rays\": %zu, \"n_prims\": %zu, \"build_s\": %.6f, "
+                "\"trace_s\": %.6f, \"threads\": 1, \"bvh_nodes\": %u}\n",
+                scene_name.c_str(), n, b.creation_order.size(), t_build, t_trace, (unsigned)Scene::num_bvh_nodes);
+    return 0;
+}
+
+static int cmd_render(int argc, char **argv)
+{
+    if (argc < 7) return 2;
+    const std::string scene_name = argv[2];
+    const int nx = std::atoi(argv[3]), ny = std::atoi(argv[4]);
+    const uint_fast64_t ns = std::atoll(argv[5]);
+    const std::string out = argv[6];
+    int threads = (int)std::thread::hardware_concurrency();
+    uint32_t seed = 1;
+    int y0 = 0, y1 = ny, ystep = 1;
+    for (int i = 7; i < argc; ++i)
+    {
+        const std::string a = argv[i];
+        if (a == "--threads") threads = std::atoi(argv[++i]);
+        else if (a == "--seed") seed = (uint32_t)std::atoll(argv[++i]);
+        else if (a == "--rows") { y0 = std::atoi(argv[i + 1]); y1 = std::atoi(argv[i + 2]); i += 2; }
+        else if (a == "--ystep") ystep = std::atoi(argv[++i]);
+    }
+    const double tb = now_s();
+    built_scene &b = build_scene(scene_name, double(nx) / double(ny));
+    const double t_build = now_s() - tb;
+    Scene *scene = b.scene.get();
+    scene->world.reset(new counting_world(scene->world.release()));
+    const bool has_lights = scene->lights.list_size > 0;
+    (void)has_lights;
+    viewer film(nx, ny, ns, 3);
+    path integrator;
+    std::atomic<uint64_t> nonfinite{0};
+
+    tf::Taskflow tf(threads > 0 ? threads : 1);
+    // path.cpp:120-147 with the full row range of ao.h:17
+    tf.parallel_for(y1 - 1, y0 - 1, -ystep, [&, seed](int y)
+    {
+#ifdef FRT_REF_CTR_RNG
+        sampler random_sampler;
+#else
+        sampler random_sampler(int(seed) * 7919 + y * 39);
+#endif
+        for (int x = 0; x < nx; x++)
+        {
+            Vector3f col(0.0, 0.0, 0.0);
+            for (uint_fast64_t s = 0; s < ns; s++)
+            {
+#ifdef FRT_REF_CTR_RNG
+                random_sampler.begin_sample(seed, uint32_t(y * nx + x), uint32_t(s), has_lights);
+#endif
+                double u = double(x + random_sampler.get1d()) / double(nx);
+                double v = double(y + random_sampler.get1d()) / double(ny);
+                ray r = scene->cam.get_ray(u, v, random_sampler.get2d());
+                hit_record hrec;
+                const Vector3f sample = integrator.Li(r, scene, 0, hrec, 0.0, random_sampler);
+                if (!(std::isfinite(sample[0]) && std::isfinite(sample[1]) && std::isfinite(sample[2])))
+                {
+                    ++nonfinite;
+                    continue;
+                }
+                col += sample;
+            }
+            film.add_sample(Vector2i(x, y), col);
+        }
+        flush_counts();
+    });
+    const double t1 = now_s();
+    tf.dispatch().get();
+    const double secs = now_s() - t1;
+
+    // image.h:89-118 (PFM, rows in buffer order = bottom row first), without the $HOME prefix
+    {
+        std::ofstream os(out, std::ios::binary | std::ios::trunc);
+        os << "PF\n" << nx << " " << ny << "\n-1\n";
+        std::vector<float> row(size_t(nx) * 3);
+        for (int y = 0; y < ny; ++y)
+        {
+            for (int i = 0; i < nx * 3; ++i) row[i] = (float)film.fout_image[size_t(y) * nx * 3 + i];
+            os.write((char *)row.data(), row.size() * 4);
+        }
+    }
+    const int rows = (y1 - y0 + ystep - 1) / ystep;
+    const double samples = double(rows) * nx * double(ns);
+    const double rays = double(g_closest.load() + g_shadow.load());
+    std::printf("{\"cmd\": \"render\", \"scene\": \"%s\", \"nx\": %d, \"ny\": %d, \"spp\": %llu, \"rows\": %d, "
+                "\"threads\": %d, \"seconds\": %.6f, \"build_s\": %.6f, \"samples\": %.0f, \"samples_per_s\": %.3f, "
+                "\"closest_rays\": %llu, \"shadow_rays\": %llu, \"mrays_per_s\": %.6f, \"nonfinite\": %llu, "
+                "\"rng\": \"%s\", \"node_visits\": %u, \"tri_tests\": %u}\n",
+                scene_name.c_str(), nx, ny, (unsigned long long)ns, rows, threads, secs, t_build, samples,
+                samples / secs, (unsigned long long)g_closest.load(), (unsigned long long)g_shadow.load(),
+                rays / secs / 1e6, (unsigned long long)nonfinite.load(),
+#ifdef FRT_REF_CTR_RNG
+                "philox",
+#else
+                "mt19937",
+#endif
+                (unsigned)Scene::num_rays_traversed, (unsigned)Scene::num_ray_tri_intersections);
+    return 0;
+}
+
+// Scene dump: lets the tests check that the product's own loader / scene builders feed the GPU
+// exactly the geometry and materials the reference driver renders.
+static int cmd_dump(int argc, char **argv)
+{
+    if (argc < 5) return 2;
+    built_scene &b = build_scene(argv[2], std::atof(argv[3]));
+    std::ofstream os(argv[4], std::ios::binary | std::ios::trunc);
+    auto wd = [&](double x) { os.write((char *)&x, 8); };
+    auto wv = [&](const Vector3f &v) { wd(v[0]); wd(v[1]); wd(v[2]); };
+    const camera &c = b.scene->cam;
+    wd(3.0); // version tag
+    wv(c.origin); wv(c.lower_left_corner); wv(c.horizontal); wv(c.vertical); wv(c.u); wv(c.v); wv(c.w); wd(c.lens_radius);
+    wd((double)b.creation_order.size());
+    wd((double)b.scene->lights.list_size);
+    for (hitable *h : b.creation_order)
+    {
+        material *m = nullptr;
+        if (auto *t = dynamic_cast<triangle *>(h))
+        {
+            wd(0.0);
+            const Vector3f &v0 = t->mesh->vertices[t->V[0]];
+            wv(v0); wv(v0 + t->edge1); wv(v0 + t->edge2);
+            wv(t->mesh->normals[t->V[0]]); wv(t->mesh->normals[t->V[1]]); wv(t->mesh->normals[t->V[2]]);
+            wd(t->inv_area); wd(t->mesh->use_geometry_normals ? 1.0 : 0.0);
+            m = t->mat_ptr;
+        }
+        else if (auto *s = dynamic_cast<sphere *>(h))
+        {
+            wd(1.0);
+            wv(s->center); wv(Vector3f(s->radius, 0, 0)); wv(Vector3f(0, 0, 0));
+            wv(Vector3f(0, 0, 0)); wv(Vector3f(0, 0, 0)); wv(Vector3f(0, 0, 0));
+            wd(0.0); wd(0.0);
+            m = s->mat_ptr;
+        }
+        hit_record dummy;
+        dummy.u = dummy.v = 0;
+        double kind = -1, p[12] = {0};
+        if (auto *l = dynamic_cast<lambertian *>(m)) { kind = 0; Vector3f a = l->albedo->value(dummy); p[0] = a[0]; p[1] = a[1]; p[2] = a[2]; }
+        else if (auto *ph = dynamic_cast<modified_phong *>(m))
+        {
+            kind = 1; Vector3f a = ph->diffuse_reflectance->value(dummy), s = ph->specular_reflectance->value(dummy);
+            p[0] = a[0]; p[1] = a[1]; p[2] = a[2]; p[3] = s[0]; p[4] = s[1]; p[5] = s[2]; p[6] = ph->specular_exponent;
+        }
+        else if (auto *d = dynamic_cast<dielectric *>(m))
+        {
+            kind = 2; Vector3f s = d->specular_reflectance->value(dummy);
+            p[0] = s[0]; p[1] = s[1]; p[2] = s[2]; p[6] = d->ref_idx;
+        }
+        else if (auto *rc = dynamic_cast<rough_conductor *>(m))
+        {
+            kind = 3; Vector3f s = rc->specular_reflectance->value(dummy);
+            p[0] = s[0]; p[1] = s[1]; p[2] = s[2]; p[3] = rc->eta[0]; p[4] = rc->eta[1]; p[5] = rc->eta[2];
+            p[6] = rc->alphaU; p[7] = rc->k[0]; p[8] = rc->k[1]; p[9] = rc->k[2];
+            p[10] = rc->distribution_type == microfacet_distributions::ggx ? 0 : 1;
+        }
+        else if (auto *mt = dynamic_cast<metal *>(m)) { kind = 4; p[0] = mt->albedo[0]; p[1] = mt->albedo[1]; p[2] = mt->albedo[2]; }
+        else if (auto *dl = dynamic_cast<diffuse_light *>(m)) { kind = 5; Vector3f e = dl->emit->value(dummy); p[0] = e[0]; p[1] = e[1]; p[2] = e[2]; }
+        wd(kind);
+        for (double x : p) wd(x);
+    }
+    std::printf("{\"cmd\": \"dump\", \"n_prims\": %zu, \"n_lights\": %d, \"bvh_nodes\": %u, \"bvh_leaves\": %u}\n",
+                b.creation_order.size(), b.scene->lights.list_size, (unsigned)Scene::num_bvh_nodes,
+                (unsigned)Scene::num_bvh_leaf_nodes);
+    return 0;
+}
+
+int main(int argc, char **argv)
+{
+    if (const char *a = std::getenv("FRT_ASSETS")) g_assets = a;
+    if (argc < 2) { std::fprintf(stderr, "usage: frt_ref trace|render|dump ...\n"); return 2; }
+    const std::string cmd = argv[1];
+    try
+    {
+        // The reference double-owns its primitives (parallel_bvh.h:134,148 vs triangle.cpp:17), so
+        // nothing is destroyed: leave through _Exit once the output is flushed.
+        int rc = 2;
+        if (cmd == "trace") rc = cmd_trace(argc, argv);
+        else if (cmd == "render") rc = cmd_render(argc, argv);
+        else if (cmd == "dump") rc = cmd_dump(argc, argv);
+        std::fflush(stdout);
+        std::_Exit(rc);
+    }
+    catch (const std::exception &e)
+    {
+        std::fprintf(stderr, "frt_ref: %s\n", e.what());
+        return 1;
+    }
+    return 2;
+}
