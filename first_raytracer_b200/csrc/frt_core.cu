@@ -1,0 +1,209 @@
+// libfrt.so — context, scene upload, wavefront driver loop, film readback and the ray-cast
+// entry points behind include/frt.h.  sm_100a only; no CPU path exists in this library.
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "frt_shade.cuh"
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct KernelTimer
+{
+    std::vector<cudaEvent_t> ev; // pairs
+    std::vector<int> kind;
+    double ms[4] = {0, 0, 0, 0};
+};
+
+struct Device
+{
+    int ordinal = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    // scene
+    void *d_nodes = nullptr, *d_tris = nullptr, *d_normals = nullptr, *d_spheres = nullptr, *d_mats = nullptr,
+         *d_lights = nullptr;
+    // pool
+    PathPool pool{};
+    std::vector<void *> pool_allocs;
+    Counters *d_ctr = nullptr;
+    Counters *h_ctr = nullptr; // pinned
+    float *d_film = nullptr;
+    float *d_film_peer = nullptr; // staging when peer access is unavailable
+    size_t film_floats = 0;
+    int sms = 0;
+    int blocks_extend = 0, blocks_connect = 0, blocks_trace = 0;
+    bool rendered = false;
+    // per-render bookkeeping
+    bool done = true;
+    unsigned long long iterations = 0, launches = 0, tile_iter = 0;
+    KernelTimer timers;
+};
+
+} // namespace
+
+struct frt_ctx
+{
+    std::vector<Device> dev;
+    std::string error;
+    uint32_t flags = 0;
+    bool have_scene = false;
+    bool peer_ok = true;
+    DevScene host_view{}; // counts + camera; pointers filled per device
+    uint32_t nx = 0, ny = 0;
+    unsigned int n_slots = 1u << 20;
+    int poll_every = 16;
+    frt_stats stats{};
+};
+
+namespace {
+
+int fail(frt_ctx *ctx, int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->error = buf; else g_create_error = buf;
+    return code;
+}
+
+#define CU(call)                                                                                           \
+    do {                                                                                                   \
+        cudaError_t e_ = (call);                                                                           \
+        if (e_ != cudaSuccess)                                                                             \
+            return fail(ctx, FRT_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+template <class T>
+int upload_array(frt_ctx *ctx, void **dst, const T *src, size_t n)
+{
+    if (*dst) { cudaFree(*dst); *dst = nullptr; }
+    if (n == 0) return FRT_OK;
+    CU(cudaMalloc(dst, n * sizeof(T)));
+    CU(cudaMemcpy(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice));
+    return FRT_OK;
+}
+
+int alloc_pool(frt_ctx *ctx, Device &d, unsigned int n)
+{
+    for (void *p : d.pool_allocs) cudaFree(p);
+    d.pool_allocs.clear();
+    auto grab = [&](size_t bytes, void **out) -> cudaError_t {
+        cudaError_t e = cudaMalloc(out, bytes);
+        if (e == cudaSuccess) d.pool_allocs.push_back(*out);
+        return e;
+    };
+    PathPool &p = d.pool;
+    p.n_slots = n;
+    CU(grab(sizeof(float4) * n, (void **)&p.ray_o));
+    CU(grab(sizeof(float4) * n, (void **)&p.ray_d));
+    CU(grab(sizeof(float4) * n, (void **)&p.hit));
+    CU(grab(sizeof(float4) * n, (void **)&p.thr));
+    CU(grab(sizeof(float4) * n, (void **)&p.rad));
+    CU(grab(sizeof(float4) * n, (void **)&p.prev_p));
+    CU(grab(sizeof(float4) * n, (void **)&p.sh_a));
+    CU(grab(sizeof(float4) * n, (void **)&p.sh_b));
+    CU(grab(sizeof(float) * n, (void **)&p.sh_c));
+    CU(grab(sizeof(unsigned int) * n, (void **)&p.free_q[0]));
+    CU(grab(sizeof(unsigned int) * n, (void **)&p.free_q[1]));
+    CU(grab(sizeof(unsigned int) * n, (void **)&p.shadow_q));
+    return FRT_OK;
+}
+
+__global__ void k_reset_pool(PathPool pool, Counters *ctr, unsigned long long total)
+{
+    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < pool.n_slots)
+    {
+        pool.free_q[0][i] = i;
+        pool.ray_d[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    if (i == 0)
+    {
+        ctr->next_sample = 0;
+        ctr->total_samples = total;
+        ctr->n_alive = 0;
+        ctr->n_free[0] = pool.n_slots;
+        ctr->n_free[1] = 0;
+        ctr->n_shadow = 0;
+        ctr->extend_next = ctr->connect_next = 0;
+    }
+}
+
+// Sum the other devices' films into device 0's over NVLink peer loads (one pass, no staging).
+struct PeerFilms { const float *p[16]; int n; };
+__global__ void k_sum_films(float *dst, PeerFilms peers, size_t n)
+{
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    {
+        float s = dst[i];
+        for (int k = 0; k < peers.n; ++k) s += peers.p[k][i];
+        dst[i] = s;
+    }
+}
+
+template <bool ANY, bool COUNT>
+__global__ void __launch_bounds__(128) k_trace(DevScene sc, Counters *ctr, const float2 *rays, frt_hit *hits, unsigned int n)
+{
+    unsigned int n_nodes = 0, n_tris = 0;
+    while (true)
+    {
+        unsigned int base = 0;
+        if (lane_id() == 0) base = atomicAdd(&ctr->trace_next, 32u);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (base >= n) break;
+        const unsigned int i = base + lane_id();
+        if (i >= n) continue;
+        const float2 r0 = __ldg(rays + 3 * (size_t)i), r1 = __ldg(rays + 3 * (size_t)i + 1), r2 = __ldg(rays + 3 * (size_t)i + 2);
+        const RayHit h = frt_traverse<ANY, COUNT>(sc, f3(r0.x, r0.y, r1.x), f3(r1.y, r2.x, r2.y),
+                                                  ANY ? 1.0f - FRT_SHADOW_EPSILON : FRT_FLT_MAX, n_nodes, n_tris);
+        frt_hit out;
+        out.t = h.t; out.b1 = h.u; out.b2 = h.v; out.prim_id = -1;
+        if (h.prim != 0xFFFFFFFFu)
+        {
+            if (h.prim & FRT_CHILD_SPHERE)
+                out.prim_id = (int)__float_as_uint(__ldg(sc.spheres + 2 * (h.prim & FRT_LEAF_FIRST_MASK) + 1).y);
+            else
+                out.prim_id = (int)__float_as_uint(__ldg(sc.tris + 3 * (size_t)h.prim).w);
+        }
+        reinterpret_cast<float4 *>(hits)[i] = make_float4(out.t, out.b1, out.b2, __int_as_float(out.prim_id));
+    }
+    if (COUNT)
+    {
+        for (int off = 16; off > 0; off >>= 1)
+        {
+            n_nodes += __shfl_down_sync(0xFFFFFFFFu, n_nodes, off);
+            n_tris += __shfl_down_sync(0xFFFFFFFFu, n_tris, off);
+        }
+        if (lane_id() == 0)
+        {
+            atomicAdd(&ctr->node_visits, (unsigned long long)n_nodes);
+            atomicAdd(&ctr->tri_tests, (unsigned long long)n_tris);
+        }
+    }
+}
+
+DevScene device_view(const frt_ctx *ctx, const Device &d)
+{
+    DevScene sc = ctx->host_view;
+    sc.nodes = (const float4 *)d.d_nodes;
+    sc.tris = (const float4 *)d.d_tris;
+    sc.tri_normals = (const float4 *)d.d_normals;
+    sc.spheres = (const float4 *)d.d_spheres;
+    sc.materials = (const frt_material *)d.d_mats;
+    sc.lights = (const frt_light *)d.d_lights;
+    return sc;
+}
+
+} // namespace
+
+#include "frt_api.inl"
+#include "frt_render.inl"

@@ -1,0 +1,57 @@
+// Device-side scene view and small float3 helpers shared by the traversal and shading code.
+// All device arithmetic is float32 (the reference is double; tolerances in tests/).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/frt.h"
+
+#define FRT_EPSILON 1e-4f        // util.h:10
+#define FRT_SHADOW_EPSILON 1e-3f // util.h:11
+#define FRT_DELTA_EPSILON 1e-3f  // util.h:12
+#define FRT_PI 3.14159265358979323846f
+#define FRT_FLT_MAX 3.402823466e+38f
+
+struct DevScene
+{
+    const float4 *nodes;       // 8 float4 per frt_bvh4_node
+    const float4 *tris;        // 3 float4 per triangle
+    const float4 *tri_normals; // 3 float4 per triangle or nullptr
+    const float4 *spheres;     // 2 float4 per frt_sphere
+    const frt_material *materials;
+    const frt_light *lights;
+    uint32_t n_nodes, n_tris, n_spheres, n_materials, n_lights;
+    frt_camera cam;
+    float env[3];
+};
+
+struct Counters // one per device, device memory; mirrored to pinned host memory when polled
+{
+    unsigned long long next_sample;   // next unissued sample index of the current tile
+    unsigned long long total_samples; // samples in the current tile (this device's share)
+    unsigned long long closest_rays, shadow_rays, node_visits, tri_tests, samples_started, nonfinite;
+    int n_alive;                      // paths in flight
+    unsigned int n_free[2];           // ping-pong free-slot queue lengths
+    unsigned int n_shadow;            // shadow queue length of this iteration
+    unsigned int extend_next, connect_next, trace_next; // persistent-warp work cursors
+    unsigned int pad;
+};
+
+__device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
+__device__ __forceinline__ float3 f3(const float4 &v) { return make_float3(v.x, v.y, v.z); }
+__device__ __forceinline__ float3 operator+(float3 a, float3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ float3 operator-(float3 a, float3 b) { return f3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ float3 operator-(float3 a) { return f3(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ float3 operator*(float3 a, float3 b) { return f3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ float3 operator/(float3 a, float3 b) { return f3(a.x / b.x, a.y / b.y, a.z / b.z); }
+__device__ __forceinline__ float3 operator*(float3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ float3 operator*(float s, float3 a) { return f3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ float3 operator/(float3 a, float s) { return f3(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ float dot(float3 a, float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ float3 cross(float3 a, float3 b)
+{
+    return f3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+__device__ __forceinline__ float length(float3 a) { return sqrtf(dot(a, a)); }
+__device__ __forceinline__ float3 unit_vector(float3 a) { return a / length(a); } // geometry.h:445
+__device__ __forceinline__ bool nonzero(float3 a) { return a.x != 0.f || a.y != 0.f || a.z != 0.f; }
+__device__ __forceinline__ float3 arr3(const float *p) { return f3(p[0], p[1], p[2]); }

@@ -1,0 +1,296 @@
+// shade: everything path::Li does at one vertex between two world->hit calls (path.cpp:11-115),
+// plus the film splat of viewer::add_sample (viewer.cpp:109-132) when the path ends.
+#pragma once
+#include "frt_kernels.cuh"
+
+struct LightSample // what sample_direct leaves in lrec + its return value
+{
+    float3 to_light; // un-normalised
+    float3 n;        // lrec.normal
+};
+
+// triangle::sample_direct triangle.h:145-175 / sphere::sample_direct sphere.h:80-107
+__device__ __forceinline__ LightSample light_sample_direct(const frt_light &L, float3 o, float u0, float u1)
+{
+    LightSample ls;
+    if (L.kind == FRT_LIGHT_TRIANGLE)
+    {
+        const float3 v0 = arr3(L.v0), v1 = arr3(L.v1), v2 = arr3(L.v2);
+        const float su0 = sqrtf(u0);
+        const float b0 = 1.0f - su0, b1 = u1 * su0;
+        const float3 pt = (1.0f - b0 - b1) * v0 + b0 * v1 + b1 * v2;
+        if (L.flags & FRT_TRI_GEOMETRY_NORMALS)
+            ls.n = unit_vector(cross(v1 - v0, v2 - v0));
+        else
+            ls.n = unit_vector((1.0f - b0 - b1) * arr3(L.n0) + b0 * arr3(L.n1) + b1 * arr3(L.n2));
+        ls.to_light = pt - o;
+        return ls;
+    }
+    const float3 c = arr3(L.v0);
+    const float radius = L.v0[3];
+    const float3 direction = c - o;
+    const float d2 = dot(direction, direction);
+    if (d2 <= radius * radius)
+    {
+        // uniform_sample_sphere pdf.h:38-44
+        const float z = 1.0f - 2.0f * u0;
+        const float r = sqrtf(fmaxf(0.0f, 1.0f - z * z));
+        float sp, cp;
+        sincosf(2.0f * FRT_PI * u1, &sp, &cp);
+        const float3 p = c + radius * f3(r * cp, r * sp, z);
+        ls.n = unit_vector(c - p);
+        ls.to_light = p - o;
+        return ls;
+    }
+    // random_to_sphere pdf.h:46-56 pushed through the un-normalised basis (sphere.h:84-85,100)
+    const float z = 1.0f + u1 * (sqrtf(1.0f - radius * radius / d2) - 1.0f);
+    float sp, cp;
+    sincosf(2.0f * FRT_PI * u0, &sp, &cp);
+    const float s = sqrtf(1.0f - z * z);
+    const float3 p = Onb(direction).from_local(f3(cp * s, sp * s, z));
+    ls.n = unit_vector(p);
+    ls.to_light = p;
+    return ls;
+}
+
+// sphere::pdf_direct_sampling sphere.h:64-78 with the record/direction the caller passes
+__device__ __forceinline__ float sphere_pdf_direct(float3 c, float radius, float3 rec_p, float rec_t, float3 rec_n,
+                                                   float3 to_light)
+{
+    const float3 o = rec_p + to_light * (-rec_t);
+    const float3 direction = c - o;
+    const float d2 = dot(direction, direction);
+    const float r2 = radius * radius;
+    if (d2 <= r2) return 1.0f / (4.0f * FRT_PI * radius * radius);
+    const float cos_theta_max = sqrtf(1.0f - r2 / d2);
+    const float solid_angle = 2.0f * FRT_PI * (1.0f - cos_theta_max);
+    return (1.0f / solid_angle) * fabsf(dot(to_light, rec_n)) / d2;
+}
+
+__device__ __forceinline__ void end_path(const KernelArgs &a, unsigned int slot, float3 rad, unsigned int pixel,
+                                         unsigned int &nonfinite)
+{
+    if (isfinite(rad.x) && isfinite(rad.y) && isfinite(rad.z))
+    {
+        float *px = a.film + 3 * (size_t)pixel;
+        atomicAdd(px + 0, rad.x);
+        atomicAdd(px + 1, rad.y);
+        atomicAdd(px + 2, rad.z);
+    }
+    else
+        ++nonfinite;
+    a.pool.ray_d[slot].w = __uint_as_float(0u);
+}
+
+__global__ void __launch_bounds__(128) k_shade(const KernelArgs a, const int parity_out)
+{
+    const unsigned int n = a.pool.n_slots;
+    unsigned int nonfinite = 0;
+    int ended = 0;
+    const unsigned int n_round = (n + 31u) & ~31u;
+    for (unsigned int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_round; slot += gridDim.x * blockDim.x)
+    {
+        bool terminated = false, want_shadow = false;
+        float4 dw = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (slot < n) dw = a.pool.ray_d[slot];
+        const unsigned int flags = __float_as_uint(dw.w);
+        if (flags & FRT_FLAG_ALIVE)
+        {
+            const float4 ow = a.pool.ray_o[slot];
+            const float4 hw = a.pool.hit[slot];
+            float4 tw = a.pool.thr[slot];
+            float4 rw = a.pool.rad[slot];
+            const float3 o = f3(ow), d = f3(dw);
+            const float prev_pdf = ow.w;
+            const unsigned int depth = flags >> FRT_DEPTH_SHIFT;
+            const unsigned int prim = __float_as_uint(hw.w);
+            const unsigned int pixel = __float_as_uint(tw.w), sample = __float_as_uint(rw.w);
+            float3 thr = f3(tw), rad = f3(rw);
+
+            if (prim == 0xFFFFFFFFu)
+            {
+                // path.cpp:115 — constant environment (material.h:219-232 over constant_texture)
+                rad = rad + thr * arr3(a.sc.env);
+                end_path(a, slot, rad, pixel, nonfinite);
+                terminated = true;
+            }
+            else
+            {
+                // ---- hit_record as the intersector would have filled it ----
+                Surface h;
+                h.t = hw.x;
+                h.p = o + d * h.t;
+                h.wi = -unit_vector(d);
+                unsigned int mat_id;
+                float3 e1 = f3(0.f, 0.f, 0.f), e2 = e1, sph_c = e1;
+                float sph_r = 0.0f;
+                unsigned int tri_flags = 0;
+                const bool is_sphere = prim & FRT_CHILD_SPHERE;
+                if (is_sphere)
+                {
+                    const unsigned int si = prim & FRT_LEAF_FIRST_MASK;
+                    const float4 s0 = __ldg(a.sc.spheres + 2 * si), s1 = __ldg(a.sc.spheres + 2 * si + 1);
+                    sph_c = f3(s0); sph_r = s0.w;
+                    mat_id = __float_as_uint(s1.x);
+                    h.n = (h.p - sph_c) / sph_r; // sphere.h:45-48
+                    const float3 oc = o - sph_c;
+                    if (dot(oc, oc) < sph_r * sph_r) h.n = -h.n;
+                }
+                else
+                {
+                    const float4 *tp = a.sc.tris + 3 * (size_t)prim;
+                    const float4 q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+                    e1 = f3(q1); e2 = f3(q2);
+                    mat_id = __float_as_uint(q1.w);
+                    tri_flags = __float_as_uint(q2.w);
+                    if (tri_flags & FRT_TRI_GEOMETRY_NORMALS) // triangle.h:100-103
+                        h.n = unit_vector(cross(e1, e2));
+                    else
+                    {
+                        const float4 *np = a.sc.tri_normals + 3 * (size_t)prim;
+                        h.n = unit_vector((1.0f - hw.y - hw.z) * f3(__ldg(np)) + hw.y * f3(__ldg(np + 1)) + hw.z * f3(__ldg(np + 2)));
+                    }
+                }
+                const frt_material &m = a.sc.materials[mat_id];
+                const unsigned int mtype = m.type;
+
+                // ---- emitted: diffuse_light::emitted material.h:184-190 ----
+                float3 Le = f3(0.f, 0.f, 0.f);
+                if (mtype == FRT_MAT_DIFFUSE_LIGHT && dot(h.n, d) < 0.0f) Le = arr3(m.p);
+
+                if (nonzero(Le))
+                {
+                    // path.cpp:16-33
+                    if (depth == 0 || (flags & FRT_FLAG_PREV_UNWEIGHTED))
+                        rad = rad + thr * Le;
+                    else
+                    {
+                        const float cos_wo = dot(h.n, -unit_vector(d));
+                        const float3 dp = h.p - f3(a.pool.prev_p[slot]);
+                        float dist2 = dot(dp, dp);
+                        if (dist2 <= FRT_EPSILON) dist2 = FRT_EPSILON;
+                        float pdf_area;
+                        if (is_sphere)
+                            pdf_area = sphere_pdf_direct(sph_c, sph_r, h.p, h.t, h.n, d);
+                        else // triangle.h:65,139-144
+                            pdf_area = 1.0f / (0.5f * length(cross(e1, e2)) * (float)(tri_flags >> 1));
+                        const float light_pdf = pdf_area * dist2 / fabsf(cos_wo);
+                        rad = rad + thr * Le * mi_weight(prev_pdf, light_pdf);
+                    }
+                    end_path(a, slot, rad, pixel, nonfinite);
+                    terminated = true;
+                }
+                else if (depth < a.tile.max_depth && mtype != FRT_MAT_DIFFUSE_LIGHT)
+                {
+                    // path.cpp:36 — scatter
+                    const float4 r1 = frt_rng_block(a.tile.seed, pixel, sample, 1 + 2 * depth);
+                    const float4 r2 = frt_rng_block(a.tile.seed, pixel, sample, 2 + 2 * depth);
+                    ScatterRec srec;
+                    mat_scatter(m, h, d, r1.x, r1.y, srec);
+
+                    // ---- continuation first: a zero pdf voids this vertex's NEE too (path.cpp:87-90,103-106)
+                    float3 next_o, next_d, f;
+                    float pdf;
+                    if (srec.is_specular)
+                    {
+                        pdf = mat_pdf_value(m, h, srec.dir);
+                        if (srec.sampled_pdf > 0.0f) pdf = srec.sampled_pdf;
+                        f = mat_eval(m, h, srec.dir);
+                        const bool outside = dot(h.n, srec.dir) > 0.0f;
+                        next_o = outside ? (h.p + FRT_EPSILON * h.n) : (h.p - FRT_EPSILON * h.n);
+                        next_d = srec.dir;
+                    }
+                    else
+                    {
+                        // cosine_pdf::generate pdf.h:91-94 + hemisphere_to_cosine_direction pdf.h:13-23
+                        const float r = sqrtf(r2.z);
+                        float sp, cp;
+                        sincosf(2.0f * FRT_PI * r2.w, &sp, &cp);
+                        next_d = Onb(h.n).from_local(f3(r * cp, r * sp, sqrtf(1.0f - r2.z)));
+                        next_o = h.p + FRT_EPSILON * h.n;
+                        pdf = mat_pdf_value(m, h, next_d);
+                        f = mat_eval(m, h, next_d) * fabsf(dot(h.n, unit_vector(next_d)));
+                    }
+
+                    if (pdf == 0.0f)
+                    {
+                        end_path(a, slot, rad, pixel, nonfinite);
+                        terminated = true;
+                    }
+                    else
+                    {
+                        // ---- next-event estimation path.cpp:39-75 ----
+                        const unsigned int nl = a.sc.n_lights;
+                        if (nl > 0 && mtype != FRT_MAT_DIELECTRIC)
+                        {
+                            int index = (int)(r1.w * (float)nl); // hitable_list::pick_sample
+                            if (index == (int)nl) index -= 1;
+                            const frt_light &L = a.sc.lights[index];
+                            const float3 so = h.p + FRT_EPSILON * h.n;
+                            const LightSample ls = light_sample_direct(L, so, r2.x, r2.y);
+                            const float dist = length(ls.to_light);
+                            const float3 tl = ls.to_light / dist; // make_unit_vector
+                            float3 bsdf = mat_eval(m, h, tl);
+                            const float cos_wi = dot(h.n, unit_vector(tl));
+                            const float cos_wo = dot(ls.n, -unit_vector(tl));
+                            float3 contrib = f3(0.f, 0.f, 0.f);
+                            if (cos_wo != 0.0f)
+                            {
+                                const float dist2 = dist * dist;
+                                if (!srec.is_specular) bsdf = bsdf * cos_wi;
+                                float pdf_area;
+                                if (L.kind == FRT_LIGHT_TRIANGLE) pdf_area = L.v0[3];
+                                else pdf_area = sphere_pdf_direct(arr3(L.v0), L.v0[3], h.p, h.t, h.n, tl);
+                                const float light_pdf = pdf_area * dist2 / fabsf(cos_wo);
+                                const float bsdf_pdf = mat_pdf_value(m, h, tl);
+                                const float weight = mi_weight(light_pdf, bsdf_pdf);
+                                const frt_material &lm = a.sc.materials[L.material];
+                                float3 emit = f3(0.f, 0.f, 0.f);
+                                if (lm.type == FRT_MAT_DIFFUSE_LIGHT && dot(ls.n, tl) < 0.0f) emit = arr3(lm.p);
+                                contrib = thr * (emit * bsdf * weight / light_pdf);
+                            }
+                            // a zero contribution needs no visibility test: adding 0 is the identity
+                            if (nonzero(contrib) || !(isfinite(contrib.x) && isfinite(contrib.y) && isfinite(contrib.z)))
+                            {
+                                want_shadow = true;
+                                a.pool.sh_a[slot] = make_float4(so.x, so.y, so.z, ls.to_light.x);
+                                a.pool.sh_b[slot] = make_float4(ls.to_light.y, ls.to_light.z, contrib.x, contrib.y);
+                                a.pool.sh_c[slot] = contrib.z;
+                            }
+                        }
+                        // ---- continue the path: L = Le + f * Li(next) [* cos] / pdf ----
+                        thr = thr * f / pdf;
+                        unsigned int nf = FRT_FLAG_ALIVE | ((depth + 1) << FRT_DEPTH_SHIFT);
+                        if (mtype == FRT_MAT_PHONG || mtype == FRT_MAT_METAL || mtype == FRT_MAT_DIELECTRIC)
+                            nf |= FRT_FLAG_PREV_UNWEIGHTED;
+                        a.pool.ray_o[slot] = make_float4(next_o.x, next_o.y, next_o.z, pdf);
+                        a.pool.ray_d[slot] = make_float4(next_d.x, next_d.y, next_d.z, __uint_as_float(nf));
+                        a.pool.thr[slot] = make_float4(thr.x, thr.y, thr.z, tw.w);
+                        a.pool.prev_p[slot] = make_float4(h.p.x, h.p.y, h.p.z, 0.0f);
+                    }
+                }
+                else
+                {
+                    // path.cpp:112 — depth cap reached, or the back of a light: returns Le == 0
+                    end_path(a, slot, rad, pixel, nonfinite);
+                    terminated = true;
+                }
+            }
+        }
+        // queue compaction: warp ballot + one atomic per warp per queue
+        const unsigned int qi = warp_append(want_shadow, &a.ctr->n_shadow);
+        if (want_shadow) a.pool.shadow_q[qi] = slot;
+        const unsigned int fi = warp_append(terminated, &a.ctr->n_free[parity_out]);
+        if (terminated) { a.pool.free_q[parity_out][fi] = slot; ++ended; }
+    }
+    for (int off = 16; off > 0; off >>= 1)
+    {
+        ended += __shfl_down_sync(0xFFFFFFFFu, ended, off);
+        nonfinite += __shfl_down_sync(0xFFFFFFFFu, nonfinite, off);
+    }
+    if (lane_id() == 0)
+    {
+        if (ended) atomicSub(&a.ctr->n_alive, ended);
+        if (nonfinite) atomicAdd(&a.ctr->nonfinite, (unsigned long long)nonfinite);
+    }
+}

@@ -1,0 +1,75 @@
+// gpu_path_integrator — drop-in for the reference's `path` integrator (path.h:8-18) behind
+// renderer<> (integrator.h:11-47): select it with renderer<gpu_path_integrator> where main.cpp:517
+// says renderer<path>.  Render() emplaces ONE task that flattens the Scene, uploads it through the
+// C ABI (include/frt.h), renders the whole film on the context's GPUs and feeds the film exactly
+// as path.cpp:143 does: one add_sample(pixel, sum over ns) per pixel.
+// If libfrt cannot create a CUDA context the task throws: there is no CPU fallback.
+#pragma once
+#include <stdexcept>
+#include <string>
+#include <vector>
+#include "../../include/frt.h"
+#include "flatten.h"
+#ifndef FRT_WITH_REFERENCE_HEADERS
+#include "taskflow_shim.h"
+#include "viewer.h"
+#endif
+
+struct gpu_path_integrator
+{
+    // knobs the reference hard-codes: depth cap path.cpp:36, seed path.cpp:122
+    int n_gpus = 1;
+    uint32_t seed = 1;
+    uint32_t max_depth = 34;
+    int max_leaf = 4;
+    uint32_t flags = 0;
+    frt_stats stats{};
+    const std::unordered_map<const hitable *, int> *prim_ids = nullptr;
+
+    void Render(Scene *scene, viewer *film_viewer, tf::Taskflow &tf)
+    {
+        tf.emplace([this, scene, film_viewer]() { run(scene, film_viewer); });
+    }
+
+    constexpr static bool using_custom_viewer = false;
+
+private:
+    static void check(frt_ctx *ctx, int rc, const char *what)
+    {
+        if (rc == FRT_OK) return;
+        const std::string msg = std::string(what) + ": " + frt_last_error(ctx);
+        if (ctx) frt_destroy(ctx);
+        throw std::runtime_error(msg);
+    }
+
+    void run(Scene *scene, viewer *film)
+    {
+        frt_flattener flattener(prim_ids, max_leaf);
+        const frt_flat_scene flat = flattener.flatten(scene);
+        const frt_scene_desc desc = flat.desc();
+        frt_ctx *ctx = nullptr;
+        check(nullptr, frt_create(&ctx, nullptr, n_gpus), "frt_create");
+        check(ctx, frt_set_flags(ctx, flags), "frt_set_flags");
+        check(ctx, frt_upload_scene(ctx, &desc), "frt_upload_scene");
+        frt_tile tile;
+        tile.nx = (uint32_t)film->nx; tile.ny = (uint32_t)film->ny;
+        tile.x0 = tile.y0 = 0; tile.w = tile.nx; tile.h = tile.ny;
+        tile.spp_begin = 0; tile.spp_end = (uint32_t)film->ns;
+        tile.seed = seed; tile.max_depth = max_depth;
+        check(ctx, frt_render_tile(ctx, &tile), "frt_render_tile");
+        std::vector<float> sums((size_t)film->nx * film->ny * 3);
+        check(ctx, frt_readback(ctx, sums.data(), sums.size(), &stats), "frt_readback");
+        frt_destroy(ctx);
+        // path.cpp:143 / viewer.cpp:109-132: the film divides the sum by ns and tonemaps
+        for (int y = 0; y < film->ny; ++y)
+            for (int x = 0; x < film->nx; ++x)
+            {
+                const float *p = &sums[((size_t)y * film->nx + x) * 3];
+                Vector3f col(p[0], p[1], p[2]);
+                film->add_sample(Vector2i(x, y), col);
+            }
+        Scene::num_rays_traversed = (unsigned int)(stats.closest_rays + stats.shadow_rays);
+        Scene::num_ray_box_intersections = (unsigned int)stats.node_visits;
+        Scene::num_ray_tri_intersections = (unsigned int)stats.tri_tests;
+    }
+};

@@ -1,0 +1,173 @@
+// Scene builders of the north-star configurations, written against the reference's own API
+// the way main.cpp writes them (cornell_box_obj main.cpp:222-252, veach_mis main.cpp:281-314,
+// furnace_test_scene's teapot main.cpp:198-212).  Deviations are the ones BASELINE/SURVEY §8c
+// fix: veach plates are rough_conductor with the alphas of veach_mi/mi.xml and the root is a
+// parallel_bvh_node; the unshipped Mitsuba matpreview mesh is replaced by cube/teapot.obj.
+#include "scenes.h"
+#include <cstdlib>
+#include <stdexcept>
+#include "mesh_loader.h"
+#include "parallel_bvh.h"
+
+std::atomic<unsigned int> Scene::num_rays_traversed{0};
+std::atomic<unsigned int> Scene::num_ray_tri_intersections{0};
+std::atomic<unsigned int> Scene::num_ray_box_intersections{0};
+std::atomic<unsigned int> Scene::num_bvh_nodes{0};
+std::atomic<unsigned int> Scene::num_bvh_leaf_nodes{0};
+
+namespace {
+
+std::string asset(const std::string &rel)
+{
+    const char *root = std::getenv("FRT_ASSETS");
+    return std::string(root ? root : "assets") + "/" + rel;
+}
+
+// Remember creation order before create_bvh reorders the array (parallel_bvh.h:93-98).
+Scene *finish(std::vector<hitable *> &list, const camera &cam, const Vector3f &env, const std::vector<hitable *> &lights,
+              frt_scene_ids *ids)
+{
+    if (ids)
+    {
+        ids->id.clear();
+        for (size_t i = 0; i < list.size(); ++i) ids->id[list[i]] = (int)i;
+    }
+    return new Scene(parallel_bvh_node::create_bvh(list.data(), (int)list.size(), 0.0, 0.0),
+                     new environment_map(std::make_unique<constant_texture>(env)), cam, lights);
+}
+
+std::shared_ptr<triangle_mesh> quad(const Vector3f &a, const Vector3f &b, const Vector3f &c, const Vector3f &d,
+                                    std::unique_ptr<material> mat, const char *name)
+{
+    Vector3f *v = new Vector3f[4]{a, b, c, d};
+    const Vector3f nn = unit_vector(cross(b - a, c - a));
+    Vector3f *n = new Vector3f[4]{nn, nn, nn, nn};
+    Vector2f *uv = new Vector2f[4]{Vector2f(0, 0), Vector2f(1, 0), Vector2f(1, 1), Vector2f(0, 1)};
+    const int idx[6] = {0, 1, 2, 0, 2, 3};
+    return std::make_shared<triangle_mesh>(2, 4, v, idx, n, uv, std::move(mat), true, name, true);
+}
+
+void add_mesh(const std::shared_ptr<triangle_mesh> &mesh, std::vector<hitable *> &list, std::vector<hitable *> &lights)
+{
+    for (int i = 0; i < mesh->nTriangles; ++i)
+    {
+        list.push_back(new triangle(mesh, i));
+        if (dynamic_cast<diffuse_light *>(mesh->mat.get())) lights.push_back(list.back());
+    }
+}
+
+} // namespace
+
+Scene *cornell_box_obj(const double &aspect, const char *variant, frt_scene_ids *ids)
+{
+    std::vector<hitable *> list, lights;
+    const std::string file = std::string("CornellBox/CornellBox-") + (variant ? variant : "Original") + ".obj";
+    // Use geometry normals (main.cpp:229)
+    std::vector<std::shared_ptr<hitable>> mesh = create_triangle_mesh(asset(file), lights, true);
+    for (auto &t : mesh) list.push_back(t.get());
+    camera cam(Vector3f(0, 1, 3.9f), Vector3f(0, 1, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.0, 10.0);
+    return finish(list, cam, Vector3f(0.0, 0.0, 0.0), lights, ids);
+}
+
+Scene *veach_mis(const double &aspect, frt_scene_ids *ids)
+{
+    std::vector<hitable *> list, lights;
+    auto meshes = mesh_loader::load_obj(asset("veach_mi/veach_mi.obj"), false);
+    const double alpha[4] = {0.005, 0.02, 0.05, 0.1}; // veach_mi/mi.xml:84,95,106,117
+    for (auto &m : meshes)
+        for (int p = 0; p < 4; ++p)
+            if (m->name == "plate" + std::to_string(p + 1))
+                m->mat.reset(new rough_conductor(alpha[p], 1.0, Vector3f(1.65746, 0.880369, 0.521229),
+                                                 Vector3f(9.22387, 6.26952, 4.837), new constant_texture(Vector3f(1, 1, 1)), "ggx"));
+    for (auto &m : meshes) add_mesh(m, list, lights);
+    // main.cpp:292-302: the world and the light list hold separate sphere objects
+    const Vector3f c[5] = {Vector3f(10, 10, 4), Vector3f(-1.25f, 0, 0), Vector3f(-3.75f, 0, 0), Vector3f(1.25f, 0, 0), Vector3f(3.75f, 0, 0)};
+    const double r[5] = {0.5, 0.1f, 0.03333f, 0.3f, 0.9f};
+    const double e[5] = {800, 100, 901.803f, 11.1111f, 1.23457};
+    for (int i = 0; i < 5; ++i)
+    {
+        list.push_back(new sphere(c[i], r[i], new diffuse_light(new constant_texture(Vector3f(e[i], e[i], e[i])))));
+        lights.push_back(new sphere(c[i], r[i], new diffuse_light(new constant_texture(Vector3f(e[i], e[i], e[i])))));
+    }
+    camera cam(Vector3f(0, 2, 15), Vector3f(0, -2, 2.5), Vector3f(0, 1, 0), 28.0, aspect, 0.0, 50.0);
+    return finish(list, cam, Vector3f(0.0, 0.0, 0.0), lights, ids);
+}
+
+Scene *teapot_scene(const double &aspect, frt_scene_ids *ids)
+{
+    std::vector<hitable *> list, lights;
+    auto meshes = mesh_loader::load_obj(asset("cube/teapot.obj"), false);
+    meshes.push_back(quad(Vector3f(-150, 0, -150), Vector3f(-150, 0, 150), Vector3f(150, 0, 150), Vector3f(150, 0, -150),
+                          std::make_unique<lambertian>(new constant_texture(Vector3f(0.4, 0.4, 0.4))), "floor"));
+    meshes.push_back(quad(Vector3f(-40, 160, -40), Vector3f(40, 160, -40), Vector3f(40, 160, 40), Vector3f(-40, 160, 40),
+                          std::make_unique<diffuse_light>(new constant_texture(Vector3f(30, 30, 30))), "light"));
+    for (auto &m : meshes) add_mesh(m, list, lights);
+    camera cam(Vector3f(0, 125, 175.0), Vector3f(0, 50, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.0, 300.0);
+    return finish(list, cam, Vector3f(0.05, 0.06, 0.08), lights, ids);
+}
+
+// splitmix64 stream, centre ~ U[0,1)^3, two edges ~ U[-l,l]^3
+static inline uint64_t splitmix64(uint64_t &s)
+{
+    uint64_t z = (s += 0x9E3779B97F4A7C15ull);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+static inline float unit_float(uint64_t &s) { return (float)(splitmix64(s) >> 40) * (1.0f / 16777216.0f); }
+
+void soup_triangles(size_t n, uint64_t seed, float edge, std::vector<float> &out)
+{
+    out.resize(n * 9);
+    uint64_t s = seed;
+    for (size_t i = 0; i < n; ++i)
+    {
+        float c[3], e1[3], e2[3];
+        for (int k = 0; k < 3; ++k) c[k] = unit_float(s);
+        for (int k = 0; k < 3; ++k) e1[k] = (2.0f * unit_float(s) - 1.0f) * edge;
+        for (int k = 0; k < 3; ++k) e2[k] = (2.0f * unit_float(s) - 1.0f) * edge;
+        for (int k = 0; k < 3; ++k)
+        {
+            out[9 * i + k] = c[k];
+            out[9 * i + 3 + k] = c[k] + e1[k];
+            out[9 * i + 6 + k] = c[k] + e2[k];
+        }
+    }
+}
+
+Scene *soup_scene(const double &aspect, const float *tri9, size_t n, frt_scene_ids *ids)
+{
+    std::vector<hitable *> list, lights;
+    Vector3f *v = new Vector3f[n * 3];
+    Vector3f *nn = new Vector3f[n * 3];
+    Vector2f *uv = new Vector2f[n * 3];
+    std::vector<int> idx(n * 3);
+    for (size_t i = 0; i < n * 3; ++i)
+    {
+        v[i] = Vector3f(tri9[3 * i], tri9[3 * i + 1], tri9[3 * i + 2]);
+        nn[i] = Vector3f(0, 0, 1);
+        idx[i] = (int)i;
+    }
+    auto mesh = std::make_shared<triangle_mesh>((int)n, (int)(n * 3), v, idx.data(), nn, uv,
+                                                std::make_unique<lambertian>(new constant_texture(Vector3f(0.5, 0.5, 0.5))), true, "soup", true);
+    add_mesh(mesh, list, lights);
+    camera cam(Vector3f(0.5, 0.5, 3.0), Vector3f(0.5, 0.5, 0.5), Vector3f(0, 1, 0), 30.0, aspect, 0.0, 10.0);
+    return finish(list, cam, Vector3f(1, 1, 1), lights, ids);
+}
+
+Scene *make_scene(const std::string &name, double aspect, frt_scene_ids *ids)
+{
+    if (name == "cornell" || name == "cornell_box_obj") return cornell_box_obj(aspect, "Original", ids);
+    if (name == "cornell_glossy") return cornell_box_obj(aspect, "Glossy", ids);
+    if (name == "cornell_sphere") return cornell_box_obj(aspect, "Sphere", ids);
+    if (name == "veach" || name == "veach_mis") return veach_mis(aspect, ids);
+    if (name == "teapot") return teapot_scene(aspect, ids);
+    if (name.rfind("soup:", 0) == 0)
+    {
+        const size_t n = (size_t)std::atoll(name.c_str() + 5);
+        std::vector<float> t;
+        soup_triangles(n, 0x5EED0001ull, 0.004f, t);
+        return soup_scene(aspect, t.data(), n, ids);
+    }
+    throw std::runtime_error("unknown scene '" + name + "'");
+}

@@ -1,0 +1,193 @@
+/* frt.h — C ABI of the B200 ray-tracing core (libfrt.so, first_raytracer_b200/csrc).
+ *
+ * The reference (jammm/first_raytracer) has no FFI: its path integrator calls C++ virtuals in
+ * one address space.  This header is the boundary a `gpu_path_integrator` (the duck-typed
+ * integrator concept of integrator.h:11-47) binds instead of running path::Render / path::Li
+ * (path.cpp:4-148) on cpp-taskflow workers.  Each entry point cites what it replaces.
+ * Names frt_upload_scene / frt_render_tile / frt_readback are fixed by BASELINE.json.
+ *
+ * Conventions: plain C, POD structs, caller-owned host memory (copied during the call),
+ * ctx-owned device memory and streams.  Every function returns FRT_OK (0) or a negative
+ * frt_status; frt_last_error() gives the text.  No exception crosses the boundary.  A ctx is
+ * not thread-safe (it is driven from the single task the integrator emplaces on the taskflow).
+ * There is no CPU fallback: without a CUDA device frt_create fails with FRT_ERR_CUDA.
+ */
+#ifndef FRT_H
+#define FRT_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define FRT_API __attribute__((visibility("default")))
+#else
+#define FRT_API
+#endif
+
+typedef enum frt_status {
+    FRT_OK = 0,
+    FRT_ERR_INVALID = -1, /* bad argument / malformed scene description */
+    FRT_ERR_CUDA = -2,    /* CUDA runtime error or no device */
+    FRT_ERR_STATE = -3,   /* call out of order (e.g. render before upload) */
+    FRT_ERR_COMM = -4     /* multi-GPU reduce failed */
+} frt_status;
+
+typedef struct frt_ctx frt_ctx;
+
+typedef struct frt_float4 { float x, y, z, w; } frt_float4;
+
+/* ---- acceleration structure -------------------------------------------------------------
+ * Wide node built by flattening what parallel_bvh_node (parallel_bvh.h:67-160) built on the
+ * host.  128 B, 16 B aligned, child boxes stored SoA so one node is eight 128-bit loads.
+ * Replaces the pointer tree {left,right,box} of parallel_bvh.h:19-21. */
+#define FRT_CHILD_EMPTY 0xFFFFFFFFu
+#define FRT_CHILD_LEAF 0x80000000u   /* bit 31: leaf                                   */
+#define FRT_CHILD_SPHERE 0x40000000u /* bit 30: leaf indexes spheres[] instead of tris */
+#define FRT_LEAF_COUNT_SHIFT 26      /* bits 26..29: primitive count - 1 (1..16)       */
+#define FRT_LEAF_FIRST_MASK 0x03FFFFFFu
+typedef struct frt_bvh4_node {
+    float lo_x[4], hi_x[4], lo_y[4], hi_y[4], lo_z[4], hi_z[4];
+    uint32_t child[4]; /* inner: node index; leaf: flags | (count-1)<<26 | first; or EMPTY */
+    uint32_t reserved[4];
+} frt_bvh4_node;
+
+/* Triangles, in leaf order: three float4 per triangle, what triangle::hit (triangle.h:69-118)
+ * reads through mesh->vertices / edge1 / edge2:
+ *   [3i+0] = v0.xyz, w = bits of primitive id (creation order, what hit_record::obj identifies)
+ *   [3i+1] = edge1.xyz (v1-v0), w = bits of material index
+ *   [3i+2] = edge2.xyz (v2-v0), w = bits of (mesh->nTriangles << 1) | FRT_TRI_GEOMETRY_NORMALS?
+ *            (nTriangles gives inv_area = 1/(area*mesh->nTriangles), triangle.h:65)
+ * tri_normals (may be NULL when every triangle has FRT_TRI_GEOMETRY_NORMALS):
+ *   [3i+k] = vertex normal k .xyz */
+#define FRT_TRI_GEOMETRY_NORMALS 1u
+
+typedef struct frt_sphere { /* sphere.h:20-23 */
+    float cx, cy, cz, radius;
+    uint32_t material, prim_id, pad0, pad1;
+} frt_sphere;
+
+/* material.h: one POD per material object; parameters as the reference's public members */
+typedef enum frt_material_type {
+    FRT_MAT_LAMBERTIAN = 0,      /* p[0..2] albedo                         material.h:50-73   */
+    FRT_MAT_PHONG = 1,           /* p[0..2] Kd, p[3..5] Ks, p[6] exponent  material.h:75-108  */
+    FRT_MAT_DIELECTRIC = 2,      /* p[0..2] Ks, p[6] ior                   material.h:133-177 */
+    FRT_MAT_ROUGH_CONDUCTOR = 3, /* p[0..2] reflectance, p[3..5] eta, p[6] alpha,
+                                    p[7..9] k, p[10] 0=ggx 1=beckmann      material.h:246-315 */
+    FRT_MAT_METAL = 4,           /* p[0..2] albedo                         material.h:111-130 */
+    FRT_MAT_DIFFUSE_LIGHT = 5    /* p[0..2] emitted radiance               material.h:179-192 */
+} frt_material_type;
+typedef struct frt_material {
+    uint32_t type;
+    float p[15];
+} frt_material;
+
+/* Scene::lights (Scene.h:13): self-contained copies, because the reference's light list may
+ * hold objects that are not the ones in `world` (veach_mis, main.cpp:292-302). */
+typedef enum frt_light_kind { FRT_LIGHT_TRIANGLE = 0, FRT_LIGHT_SPHERE = 1 } frt_light_kind;
+typedef struct frt_light {
+    uint32_t kind, material, flags, pad;
+    float v0[4]; /* triangle: v0.xyz, w = inv_area;  sphere: center.xyz, w = radius */
+    float v1[4], v2[4];
+    float n0[4], n1[4], n2[4]; /* vertex normals when !(flags & FRT_TRI_GEOMETRY_NORMALS) */
+    float reserved[4];
+} frt_light;
+
+typedef struct frt_camera { /* camera.h:42-48 */
+    float origin[3], lower_left_corner[3], horizontal[3], vertical[3], u[3], v[3], w[3];
+    float lens_radius;
+} frt_camera;
+
+typedef struct frt_scene_desc {
+    uint32_t struct_size; /* = sizeof(frt_scene_desc) */
+    uint32_t n_nodes;
+    const frt_bvh4_node *nodes;
+    uint32_t n_tris;
+    uint32_t n_spheres;
+    const frt_float4 *tris;
+    const frt_float4 *tri_normals;
+    const frt_sphere *spheres;
+    uint32_t n_materials;
+    uint32_t n_lights;
+    const frt_material *materials;
+    const frt_light *lights;
+    frt_camera camera;
+    float env_color[3]; /* environment_map over a constant_texture, material.h:219-232 */
+    uint32_t reserved;
+} frt_scene_desc;
+
+/* One unit of rendering work: the pixel rectangle and sample range path::Render's row loop
+ * (path.cpp:120-147) would cover.  Sample s of pixel (x,y) is identified by (seed, y*nx+x, s)
+ * whatever tile / device / rank renders it, so splitting [spp_begin,spp_end) across GPUs
+ * gives the same multiset of samples as one GPU. */
+typedef struct frt_tile {
+    uint32_t nx, ny;         /* film size (viewer::nx, ny) */
+    uint32_t x0, y0, w, h;   /* pixel rectangle, row 0 = bottom (viewer.cpp:109-132) */
+    uint32_t spp_begin, spp_end;
+    uint32_t seed;
+    uint32_t max_depth;      /* deepest vertex that still scatters + 1; reference: 34 (path.cpp:36) */
+} frt_tile;
+
+typedef struct frt_stats {
+    uint64_t samples;        /* camera paths started */
+    uint64_t closest_rays;   /* world->hit(r, EPSILON, FLT_MAX) equivalents, path.cpp:10 */
+    uint64_t shadow_rays;    /* world->hit(shadow_ray, EPSILON, 1-SHADOW_EPSILON), path.cpp:50 */
+    uint64_t node_visits;    /* wide-node fetches (0 unless counters enabled) */
+    uint64_t tri_tests;      /* triangle fetches (0 unless counters enabled) */
+    uint64_t iterations;     /* wavefront iterations */
+    uint64_t kernel_launches;
+    double render_ms;        /* device time between first and last kernel, max over devices */
+    double extend_ms, shade_ms, connect_ms, generate_ms; /* only with FRT_FLAG_KERNEL_TIMERS */
+} frt_stats;
+
+typedef struct frt_ray { float ox, oy, oz, dx, dy, dz; } frt_ray; /* ray.h:6-17, d not normalised */
+typedef struct frt_hit {
+    float t, b1, b2;  /* hit_record::t and barycentric uv (hitable.h:23-36) */
+    int32_t prim_id;  /* creation-order primitive id, -1 = miss */
+} frt_hit;
+
+#define FRT_FLAG_COUNTERS 1u      /* count node visits / triangle tests (slower) */
+#define FRT_FLAG_KERNEL_TIMERS 2u /* per-kernel CUDA-event timing (serialises the loop) */
+
+/* Create a context on `n` CUDA devices (ordinals in `devices`, NULL = device 0..n-1). */
+FRT_API int frt_create(frt_ctx **out, const int *devices, int n);
+FRT_API void frt_destroy(frt_ctx *ctx);
+FRT_API const char *frt_last_error(const frt_ctx *ctx); /* ctx may be NULL: last creation error */
+FRT_API int frt_set_flags(frt_ctx *ctx, uint32_t flags);
+FRT_API int frt_device_count(const frt_ctx *ctx);
+
+/* Replaces handing `Scene*` to the integrator (integrator.h:14, Scene.h:10-26): copies the
+ * flattened scene to every device of the context.  Validates indices. */
+FRT_API int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *scene);
+
+/* Replaces path::Render + path::Li (path.cpp:4-148) for the tile: asynchronous; the sample
+ * range is split evenly over the context's devices.  Radiance is accumulated (summed, not
+ * averaged) into the context's film, which is (re)allocated and zeroed when nx/ny change. */
+FRT_API int frt_render_tile(frt_ctx *ctx, const frt_tile *tile);
+FRT_API int frt_clear_film(frt_ctx *ctx);
+
+/* Replaces viewer::add_sample's store (viewer.cpp:109-132): waits for rendering, sums the
+ * per-device films on device 0, copies nx*ny*3 float32 radiance SUMS (row 0 = bottom) to
+ * `rgb_sum` (may be NULL to only synchronise) and fills `stats` (may be NULL). */
+FRT_API int frt_readback(frt_ctx *ctx, float *rgb_sum, size_t n_floats, frt_stats *stats);
+
+/* Device address of device `dev`'s film (nx*ny*3 float32) so that a multi-process launcher can
+ * reduce it in place with its own communicator before frt_readback.  Synchronises `dev`. */
+FRT_API int frt_film_device_ptr(frt_ctx *ctx, int dev, void **ptr, size_t *n_floats);
+
+/* Test / ray-cast entry: what scene->world->hit(r, EPSILON, FLT_MAX, rec) (any_hit = 0,
+ * path.cpp:10) or world->hit(r, EPSILON, 1 - SHADOW_EPSILON, rec) (any_hit = 1, path.cpp:50;
+ * only prim_id >= 0 / -1 is meaningful) return for each ray.  Host buffers; rays are block-
+ * partitioned over the devices.  `device_ms` (may be NULL) = kernel time, max over devices. */
+FRT_API int frt_trace_rays(frt_ctx *ctx, const frt_ray *rays, size_t n, frt_hit *hits, int any_hit, double *device_ms);
+
+/* Same on device-resident buffers of device `dev` (bench: inputs already in HBM). */
+FRT_API int frt_trace_rays_device(frt_ctx *ctx, int dev, const void *d_rays, size_t n, void *d_hits, int any_hit,
+                          double *device_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FRT_H */
