@@ -23,7 +23,7 @@ FRT_FLAG_KERNEL_TIMERS = 2
 FRT_SYMBOLS = [
     "frt_create", "frt_destroy", "frt_last_error", "frt_set_flags", "frt_device_count",
     "frt_upload_scene", "frt_render_tile", "frt_clear_film", "frt_readback", "frt_film_device_ptr",
-    "frt_trace_rays", "frt_trace_rays_device",
+    "frt_trace_rays", "frt_trace_rays_device", "frt_stream_handle",
 ]
 FRTH_SYMBOLS = [
     "frth_last_error", "frth_scene_create", "frth_scene_create_soup", "frth_scene_destroy",
@@ -120,6 +120,7 @@ def load_libs():
             "frt_clear_film": (i32, [vp]),
             "frt_readback": (i32, [vp, vp, sz, C.POINTER(frt_stats)]),
             "frt_film_device_ptr": (i32, [vp, i32, C.POINTER(vp), C.POINTER(sz)]),
+            "frt_stream_handle": (i32, [vp, i32, C.POINTER(vp)]),
             "frt_trace_rays": (i32, [vp, vp, sz, vp, i32, C.POINTER(dbl)]),
             "frt_trace_rays_device": (i32, [vp, i32, vp, sz, vp, i32, C.POINTER(dbl)]),
         },
@@ -301,6 +302,11 @@ class Context:
         p, n = C.c_void_p(), C.c_size_t()
         self._check(self._frt.frt_film_device_ptr(self.handle, dev, C.byref(p), C.byref(n)), "frt_film_device_ptr")
         return p.value, n.value
+
+    def stream_handle(self, dev: int = 0) -> int:
+        p = C.c_void_p()
+        self._check(self._frt.frt_stream_handle(self.handle, dev, C.byref(p)), "frt_stream_handle")
+        return p.value
 
     def trace(self, rays: np.ndarray, any_hit: bool = False):
         """Host buffers in, host buffers out (H2D / D2H inside the call) → (hits, device_ms)."""

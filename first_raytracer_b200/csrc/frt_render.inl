@@ -182,6 +182,13 @@ int frt_film_device_ptr(frt_ctx *ctx, int dev, void **ptr, size_t *n_floats)
     return FRT_OK;
 }
 
+int frt_stream_handle(frt_ctx *ctx, int dev, void **stream)
+{
+    if (!ctx || dev < 0 || dev >= (int)ctx->dev.size() || !stream) return FRT_ERR_INVALID;
+    *stream = (void *)ctx->dev[dev].stream;
+    return FRT_OK;
+}
+
 int frt_readback(frt_ctx *ctx, float *rgb_sum, size_t n_floats, frt_stats *stats)
 {
     if (!ctx) return FRT_ERR_INVALID;

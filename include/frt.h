@@ -177,6 +177,10 @@ FRT_API int frt_readback(frt_ctx *ctx, float *rgb_sum, size_t n_floats, frt_stat
  * reduce it in place with its own communicator before frt_readback.  Synchronises `dev`. */
 FRT_API int frt_film_device_ptr(frt_ctx *ctx, int dev, void **ptr, size_t *n_floats);
 
+/* The CUDA stream (cudaStream_t) device `dev` of the context launches on, so that a harness can
+ * bracket calls with its own events or enqueue a collective behind the render. */
+FRT_API int frt_stream_handle(frt_ctx *ctx, int dev, void **stream);
+
 /* Test / ray-cast entry: what scene->world->hit(r, EPSILON, FLT_MAX, rec) (any_hit = 0,
  * path.cpp:10) or world->hit(r, EPSILON, 1 - SHADOW_EPSILON, rec) (any_hit = 1, path.cpp:50;
  * only prim_id >= 0 / -1 is meaningful) return for each ray.  Host buffers; rays are block-
