@@ -63,8 +63,13 @@ Scene *cornell_box_obj(const double &aspect, const char *variant, frt_scene_ids 
     std::vector<hitable *> list, lights;
     const std::string file = std::string("CornellBox/CornellBox-") + (variant ? variant : "Original") + ".obj";
     // Use geometry normals (main.cpp:229)
-    std::vector<std::shared_ptr<hitable>> mesh = create_triangle_mesh(asset(file), lights, true);
-    for (auto &t : mesh) list.push_back(t.get());
+    auto meshes = mesh_loader::load_obj(asset(file), true);
+    // CornellBox-Glossy.mtl as shipped has no `light` entry, so that scene renders black; give the
+    // `light` group the emitter of CornellBox-Original.mtl:81-88 (the oracle driver does the same).
+    for (auto &m : meshes)
+        if (m->name == "light" && !dynamic_cast<diffuse_light *>(m->mat.get()))
+            m->mat.reset(new diffuse_light(new constant_texture(Vector3f(17, 12, 4))));
+    for (auto &m : meshes) add_mesh(m, list, lights);
     camera cam(Vector3f(0, 1, 3.9f), Vector3f(0, 1, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.0, 10.0);
     return finish(list, cam, Vector3f(0.0, 0.0, 0.0), lights, ids);
 }
@@ -72,13 +77,26 @@ Scene *cornell_box_obj(const double &aspect, const char *variant, frt_scene_ids 
 Scene *veach_mis(const double &aspect, frt_scene_ids *ids)
 {
     std::vector<hitable *> list, lights;
-    auto meshes = mesh_loader::load_obj(asset("veach_mi/veach_mi.obj"), false);
+    // veach_mi/veach_mi.obj numbers each object's faces from 1 again; OBJ indices are global, so as
+    // shipped every plate collapses onto the floor's first two triangles (coincident geometry whose
+    // winner depends on traversal order).  The per-object files carry the intended geometry
+    // (SURVEY §8c(iii)); floor colour = Kd of `floor` in veach_mi/veach_mi.mtl.
+    std::vector<std::shared_ptr<triangle_mesh>> meshes;
     const double alpha[4] = {0.005, 0.02, 0.05, 0.1}; // veach_mi/mi.xml:84,95,106,117
-    for (auto &m : meshes)
-        for (int p = 0; p < 4; ++p)
-            if (m->name == "plate" + std::to_string(p + 1))
+    for (int p = -1; p < 4; ++p)
+    {
+        const std::string file = p < 0 ? "veach_mi/floor.obj" : "veach_mi/plate" + std::to_string(p + 1) + ".obj";
+        for (auto &m : mesh_loader::load_obj(asset(file), false))
+        {
+            if (p < 0)
+                m->mat.reset(new lambertian(new constant_texture(FromSrgb(Vector3f(0.4, 0.4, 0.4)))));
+            else
                 m->mat.reset(new rough_conductor(alpha[p], 1.0, Vector3f(1.65746, 0.880369, 0.521229),
                                                  Vector3f(9.22387, 6.26952, 4.837), new constant_texture(Vector3f(1, 1, 1)), "ggx"));
+            m->name = p < 0 ? "floor" : "plate" + std::to_string(p + 1);
+            meshes.push_back(m);
+        }
+    }
     for (auto &m : meshes) add_mesh(m, list, lights);
     // main.cpp:292-302: the world and the light list hold separate sphere objects
     const Vector3f c[5] = {Vector3f(10, 10, 4), Vector3f(-1.25f, 0, 0), Vector3f(-3.75f, 0, 0), Vector3f(1.25f, 0, 0), Vector3f(3.75f, 0, 0)};

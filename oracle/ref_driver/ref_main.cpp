@@ -21,6 +21,7 @@
 //   frt_ref trace  <scene> <aspect> closest|shadow <rays.f32> <out.bin>
 //   frt_ref render <scene> <w> <h> <spp> <out.pfm> [--threads N] [--seed S] [--rows y0 y1] [--ystep K]
 //   frt_ref dump   <scene> <aspect> <out.bin>
+//   frt_ref bsdf   <in.f64> <out.f64>
 #include "Scene.h"
 #include "sphere.h"
 #include "triangle.h"
@@ -276,6 +277,10 @@ static built_scene &build_scene(const std::string &name, double aspect)
                          : name == "cornell_glossy" ? "/CornellBox/CornellBox-Glossy.obj"
                                                     : "/CornellBox/CornellBox-Sphere.obj";
         b.meshes = read_obj(g_assets + file, true);
+        // CornellBox-Glossy.mtl has no `light` entry (the shipped scene is black): same emitter as Original
+        for (auto &m : b.meshes)
+            if (m->name == "light" && !dynamic_cast<diffuse_light *>(m->mat.get()))
+                m->mat.reset(new diffuse_light(new constant_texture(Vector3f(17, 12, 4))));
         push_triangles(b.meshes, b.keep, lights);
         for (auto &t : b.keep) list.push_back(t.get());
         cam = camera(Vector3f(0, 1, 3.9f), Vector3f(0, 1, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.0, 10.0);
@@ -283,14 +288,23 @@ static built_scene &build_scene(const std::string &name, double aspect)
     else if (name == "veach")
     {
         // main.cpp:281-314 (veach_mis) + SURVEY §8c(iii)
-        b.meshes = read_obj(g_assets + "/veach_mi/veach_mi.obj", false);
+        // veach_mi.obj restarts its face indices per object, which (OBJ indices being global) puts
+        // every plate on top of the floor triangles; the per-object files hold the intended geometry.
         const double alpha[4] = {0.005, 0.02, 0.05, 0.1}; // veach_mi/mi.xml:84,95,106,117
-        for (auto &m : b.meshes)
-            for (int p = 0; p < 4; ++p)
-                if (m->name == "plate" + std::to_string(p + 1))
+        for (int p = -1; p < 4; ++p)
+        {
+            const std::string file = p < 0 ? "/veach_mi/floor.obj" : "/veach_mi/plate" + std::to_string(p + 1) + ".obj";
+            for (auto &m : read_obj(g_assets + file, false))
+            {
+                if (p < 0)
+                    m->mat.reset(new lambertian(new constant_texture(FromSrgb(Vector3f(0.4, 0.4, 0.4)))));
+                else
                     m->mat.reset(new rough_conductor(alpha[p], 1.0, Vector3f(1.65746, 0.880369, 0.521229),
                                                      Vector3f(9.22387, 6.26952, 4.837),
                                                      new constant_texture(Vector3f(1, 1, 1)), "ggx"));
+                b.meshes.push_back(m);
+            }
+        }
         push_triangles(b.meshes, b.keep, lights);
         for (auto &t : b.keep) list.push_back(t.get());
         const Vector3f c[5] = {Vector3f(10, 10, 4), Vector3f(-1.25f, 0, 0), Vector3f(-3.75f, 0, 0),
@@ -596,6 +610,58 @@ static int cmd_dump(int argc, char **argv)
     return 0;
 }
 
+// BSDF unit vectors: each input record is 24 doubles
+//   kind, p[0..10], n[3], wi[3], s[3], wo_probe[3]
+// and each output record 12 doubles (layout of frt_oracle_bsdf, oracle/frt_oracle.h), computed by the
+// reference's own material::scatter / pdf::generate / pdf::value / eval_bsdf.
+static int cmd_bsdf(int argc, char **argv)
+{
+    if (argc < 4) return 2;
+    std::ifstream is(argv[2], std::ios::binary);
+    is.seekg(0, std::ios::end);
+    const size_t n = size_t(is.tellg()) / (24 * 8);
+    is.seekg(0);
+    std::vector<double> in(n * 24), out(n * 12, 0.0);
+    is.read((char *)in.data(), n * 24 * 8);
+    for (size_t i = 0; i < n; ++i)
+    {
+        const double *q = &in[i * 24];
+        const int kind = int(q[0]);
+        const double *p = q + 1;
+        std::unique_ptr<material> m;
+        if (kind == 0) m.reset(new lambertian(new constant_texture(Vector3f(p[0], p[1], p[2]))));
+        else if (kind == 1) m.reset(new modified_phong(new constant_texture(Vector3f(p[0], p[1], p[2])), new constant_texture(Vector3f(p[3], p[4], p[5])), p[6]));
+        else if (kind == 2) m.reset(new dielectric(p[6], new constant_texture(Vector3f(p[0], p[1], p[2])), new constant_texture(Vector3f(1, 1, 1))));
+        else if (kind == 3) m.reset(new rough_conductor(p[6], 1.0, Vector3f(p[3], p[4], p[5]), Vector3f(p[7], p[8], p[9]), new constant_texture(Vector3f(p[0], p[1], p[2])), p[10] == 0 ? "ggx" : "beckmann"));
+        else if (kind == 4) m.reset(new metal(Vector3f(p[0], p[1], p[2])));
+        else continue;
+        hit_record hrec;
+        hrec.t = 1.0; hrec.u = hrec.v = 0.0;
+        hrec.p = Vector3f(0, 0, 0);
+        hrec.normal = Vector3f(q[12], q[13], q[14]);
+        hrec.wi = Vector3f(q[15], q[16], q[17]);
+        hrec.mat_ptr = m.get();
+        const ray r_in(hrec.wi, -hrec.wi);
+        scatter_record srec(hrec);
+        if (!m->scatter(r_in, hrec, srec, Vector3f(q[18], q[19], q[20]))) continue;
+        Vector3f dir = srec.is_specular ? srec.specular_ray.direction()
+                                        : srec.pdf_ptr->generate(Vector2f(q[18], q[19]), srec);
+        const Vector3f probe(q[21], q[22], q[23]);
+        double *o = &out[i * 12];
+        o[0] = dir[0]; o[1] = dir[1]; o[2] = dir[2];
+        o[3] = srec.sampled_pdf;
+        o[4] = srec.pdf_ptr->value(hrec, dir);
+        const Vector3f f = m->eval_bsdf(r_in, hrec, dir), fp = m->eval_bsdf(r_in, hrec, probe);
+        o[5] = f[0]; o[6] = f[1]; o[7] = f[2];
+        o[8] = srec.pdf_ptr->value(hrec, probe);
+        o[9] = fp[0]; o[10] = fp[1]; o[11] = fp[2];
+    }
+    std::ofstream os(argv[3], std::ios::binary | std::ios::trunc);
+    os.write((char *)out.data(), out.size() * 8);
+    std::printf("{\"cmd\": \"bsdf\", \"n\": %zu}\n", n);
+    return 0;
+}
+
 int main(int argc, char **argv)
 {
     if (const char *a = std::getenv("FRT_ASSETS")) g_assets = a;
@@ -609,6 +675,7 @@ int main(int argc, char **argv)
         if (cmd == "trace") rc = cmd_trace(argc, argv);
         else if (cmd == "render") rc = cmd_render(argc, argv);
         else if (cmd == "dump") rc = cmd_dump(argc, argv);
+        else if (cmd == "bsdf") rc = cmd_bsdf(argc, argv);
         std::fflush(stdout);
         std::_Exit(rc);
     }

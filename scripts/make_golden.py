@@ -1,0 +1,104 @@
+"""Generates tests/golden/*.npz from the reference's OWN object code (oracle/_ref/frt_ref*, compiled
+from /root/reference by oracle/Makefile).  Run in the build container, where /root/reference
+exists; the fixtures are committed so that the oracle stays pinned on machines without it.
+
+    python scripts/make_golden.py
+
+Fixtures:
+  trace_<scene>.npz      F1/F2: rays + closest-hit (prim id, t, u, v) and segments + occluded flag
+  render_<scene>_WxHxS   F3: path::Li images with the counter-based sampler (same numbers as the GPU)
+  bsdf_vectors.npz       F4: scatter / generate / value / eval_bsdf of every material class
+"""
+from __future__ import annotations
+
+import subprocess
+import sys
+import tempfile
+from pathlib import Path
+
+import numpy as np
+
+REPO = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(REPO))
+sys.path.insert(0, str(REPO / "tests"))
+
+import refutil  # noqa: E402
+from first_raytracer_b200 import api  # noqa: E402
+
+OUT = REPO / "tests" / "golden"
+SEED = 7
+
+
+def flat(rays):
+    return np.concatenate([rays["o"], rays["d"]], axis=1).astype(np.float32)
+
+
+def trace_fixture(name, aspect, n_cam=48, n_rand=6000, n_seg=4000):
+    scene = api.HostScene(name, aspect, 4)
+    info = scene.info
+    rays = np.concatenate([scene.camera_rays(n_cam, n_cam),
+                           refutil.random_rays(n_rand, info["bounds_lo"], info["bounds_hi"], seed=101)])
+    ref, _ = refutil.ref_trace(name, aspect, rays)
+    seg = refutil.segment_rays(n_seg, info["bounds_lo"], info["bounds_hi"], seed=102)
+    sref, _ = refutil.ref_trace(name, aspect, seg, shadow=True)
+    np.savez_compressed(OUT / f"trace_{name}.npz", rays=flat(rays), prim=ref["prim"], t=ref["t"], u=ref["u"], v=ref["v"],
+                        segments=flat(seg), occluded=sref["prim"] >= 0)
+    print(f"trace_{name}: {rays.shape[0]} rays, hit fraction {np.mean(ref['prim'] >= 0):.3f}, "
+          f"{seg.shape[0]} segments, occluded {np.mean(sref['prim'] >= 0):.3f}")
+
+
+def render_fixture(name, nx, ny, spp):
+    img, info = refutil.ref_render(name, nx, ny, spp, ctr=True, seed=SEED)
+    np.savez_compressed(OUT / f"render_{name}_{nx}x{ny}x{spp}.npz", image=img.astype(np.float32), seed=SEED,
+                        closest_rays=info["closest_rays"], shadow_rays=info["shadow_rays"], nonfinite=info["nonfinite"])
+    print(f"render_{name}_{nx}x{ny}x{spp}: mean {img.mean():.6f}, rays {info['closest_rays']}+{info['shadow_rays']}")
+
+
+def unit(v):
+    return v / np.linalg.norm(v, axis=-1, keepdims=True)
+
+
+def bsdf_fixture(n_per=600):
+    rng = np.random.default_rng(5)
+    cu = [1.65746, 0.880369, 0.521229]
+    ck = [9.22387, 6.26952, 4.837]
+    mats = [(0, [.7, .6, .5] + [0] * 8), (1, [.3, .2, .1, .5, .6, .7, 20] + [0] * 4), (1, [.1, .1, .1, .9, .9, .9, 1024] + [0] * 4),
+            (2, [.9, .9, .9, 0, 0, 0, 1.5] + [0] * 4), (2, [.3, .3, .3, 0, 0, 0, 2.5] + [0] * 4),
+            (3, [1, 1, 1] + cu + [0.005] + ck + [0]), (3, [1, 1, 1] + cu + [0.05] + ck + [0]), (3, [1, 1, 1] + cu + [0.1] + ck + [0]),
+            (3, [1, 1, 1] + cu + [0.1] + ck + [1]), (3, [.8, .9, 1] + cu + [0.3] + ck + [1]), (4, [.8, .7, .6] + [0] * 8)]
+    rec = np.zeros((len(mats) * n_per, 24))
+    for k, (kind, p) in enumerate(mats):
+        r = rec[k * n_per:(k + 1) * n_per]
+        r[:, 0] = kind
+        r[:, 1:12] = np.asarray(p, np.float32)  # what a frt_material can hold
+        n = unit(rng.normal(size=(n_per, 3)))
+        wi = unit(rng.normal(size=(n_per, 3)))
+        flip = (np.sum(n * wi, axis=1) < 0) & (rng.random(n_per) < 0.9)
+        wi[flip] *= -1
+        r[:, 12:15], r[:, 15:18] = n, wi
+        r[:, 18:21] = np.floor(rng.random((n_per, 3)) * 2 ** 24) / 2 ** 24  # 24-bit uniforms like the RNG
+        r[:, 21:24] = unit(n + 0.7 * unit(rng.normal(size=(n_per, 3))))
+    with tempfile.TemporaryDirectory() as td:
+        rec.tofile(td + "/in")
+        subprocess.run([str(refutil.REF_BIN), "bsdf", td + "/in", td + "/out"], check=True, capture_output=True)
+        out = np.fromfile(td + "/out").reshape(-1, 12)
+    np.savez_compressed(OUT / "bsdf_vectors.npz", records=rec, outputs=out)
+    print(f"bsdf_vectors: {rec.shape[0]} records, finite {np.isfinite(out).all(axis=1).mean():.4f}")
+
+
+def main():
+    if not refutil.have_ref():
+        raise SystemExit("oracle/_ref is missing: run `make -C oracle` where /root/reference exists")
+    OUT.mkdir(parents=True, exist_ok=True)
+    for name, aspect in [("cornell", 1.0), ("veach", 1.5), ("teapot", 16 / 9), ("cornell_sphere", 1.0)]:
+        trace_fixture(name, aspect)
+    for name, nx, ny, spp in [("cornell", 48, 48, 4), ("veach", 48, 32, 4), ("cornell_sphere", 32, 32, 2),
+                              ("cornell_glossy", 32, 32, 2), ("teapot", 48, 27, 2),
+                              # larger ones for the GPU parity tests (statistical bars need pixels x spp)
+                              ("cornell", 128, 128, 16), ("veach", 192, 128, 16)]:
+        render_fixture(name, nx, ny, spp)
+    bsdf_fixture()
+
+
+if __name__ == "__main__":
+    main()
