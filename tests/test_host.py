@@ -1,0 +1,155 @@
+"""CPU tests of the host layer and of the C-ABI surface (no compute calls: there is no GPU here).
+
+ * both shared libraries load and export every symbol include/*.h declares;
+ * without a CUDA device the product fails loudly (no CPU fallback);
+ * the flattened scene description equals what the reference driver builds for the same scene;
+ * the wide BVH is well formed: every primitive in exactly one leaf, child boxes enclose them;
+ * the fast soup builder and the reference-shaped builder describe the same triangles."""
+import ctypes as C
+import re
+
+import numpy as np
+import pytest
+
+import refutil
+from first_raytracer_b200 import api
+
+REPO = refutil.REPO
+
+
+def _declared(header):
+    text = (REPO / "include" / header).read_text()
+    return sorted(set(re.findall(r"FRT_API\s+[\w\s\*]+?\b(frth?_\w+)\s*\(", text)))
+
+
+def test_abi_exports_every_declared_symbol(built):
+    frt, frth = api.load_libs()
+    core, host = _declared("frt.h"), _declared("frt_host.h")
+    assert len(core) >= 12 and len(host) >= 9
+    for name in core:
+        assert hasattr(frt, name), f"libfrt.so does not export {name}"
+    for name in host:
+        assert hasattr(frth, name), f"libfrt_host.so does not export {name}"
+    assert sorted(api.FRT_SYMBOLS) == core
+    assert sorted(api.FRTH_SYMBOLS) == host
+
+
+def test_struct_layouts_match_header(built):
+    assert C.sizeof(api.frt_tile) == 40
+    assert api.NODE_DTYPE.itemsize == 128 and api.MATERIAL_DTYPE.itemsize == 64
+    assert api.LIGHT_DTYPE.itemsize == 128 and api.SPHERE_DTYPE.itemsize == 32
+    assert api.RAY_DTYPE.itemsize == 24 and api.HIT_DTYPE.itemsize == 16
+    scene = api.HostScene("cornell", 1.0, 4)
+    assert scene.desc.struct_size == C.sizeof(api.frt_scene_desc)
+
+
+def test_no_cpu_fallback(built):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(api.FrtError, match="no CUDA device|CUDA"):
+        api.Context()
+    scene = api.HostScene("cornell", 1.0, 4)
+    with pytest.raises(api.FrtError):
+        scene.render(8, 8, 1)
+
+
+def _leaf_ranges(nodes):
+    tri_seen, sph_seen = [], []
+    for n in nodes:
+        for c in n["child"]:
+            c = int(c)
+            if c == 0xFFFFFFFF or not (c & 0x80000000):
+                continue
+            first, count = c & 0x03FFFFFF, ((c >> 26) & 15) + 1
+            (sph_seen if c & 0x40000000 else tri_seen).extend(range(first, first + count))
+    return tri_seen, sph_seen
+
+
+@pytest.mark.parametrize("name,aspect,max_leaf", [("cornell", 1.0, 1), ("cornell", 1.0, 4), ("veach", 1.5, 4),
+                                                  ("teapot", 16 / 9, 4), ("teapot", 16 / 9, 8), ("cornell_sphere", 1.0, 2)])
+def test_wide_bvh_is_well_formed(built, name, aspect, max_leaf):
+    scene = api.HostScene(name, aspect, max_leaf)
+    a = scene.arrays()
+    nodes, tris = a["nodes"], a["tris"]
+    tri_seen, sph_seen = _leaf_ranges(nodes)
+    assert sorted(tri_seen) == list(range(tris.shape[0])), "every triangle in exactly one leaf"
+    assert sorted(sph_seen) == list(range(a["spheres"].shape[0]))
+    ids = np.concatenate([tris[:, 0, 3].view(np.uint32), a["spheres"]["prim_id"]])
+    assert sorted(ids.tolist()) == list(range(ids.size)), "creation-order ids are a permutation"
+    # children follow parents (frt_upload_scene's validation relies on it) and boxes enclose the geometry
+    for i, n in enumerate(nodes):
+        for k in range(4):
+            c = int(n["child"][k])
+            if c == 0xFFFFFFFF:
+                continue
+            lo = np.array([n["lo_x"][k], n["lo_y"][k], n["lo_z"][k]])
+            hi = np.array([n["hi_x"][k], n["hi_y"][k], n["hi_z"][k]])
+            if not (c & 0x80000000):
+                assert i < c < len(nodes)
+                ch = nodes[c]
+                used = ch["child"] != 0xFFFFFFFF
+                clo = np.array([ch["lo_x"][used].min(), ch["lo_y"][used].min(), ch["lo_z"][used].min()])
+                chi = np.array([ch["hi_x"][used].max(), ch["hi_y"][used].max(), ch["hi_z"][used].max()])
+                assert (clo >= lo - 1e-4 * np.abs(lo) - 1e-5).all() and (chi <= hi + 1e-4 * np.abs(hi) + 1e-5).all()
+            elif not (c & 0x40000000):
+                first, count = c & 0x03FFFFFF, ((c >> 26) & 15) + 1
+                assert count <= max_leaf
+                t = tris[first:first + count]
+                v0, v1, v2 = t[:, 0, :3], t[:, 0, :3] + t[:, 1, :3], t[:, 0, :3] + t[:, 2, :3]
+                pts = np.concatenate([v0, v1, v2]).astype(np.float64)
+                tol = 1e-5 * max(1.0, np.abs(pts).max())
+                assert (pts >= lo - tol).all() and (pts <= hi + tol).all(), "leaf box must enclose its triangles"
+
+
+@pytest.mark.skipif(not refutil.have_ref(), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("name,aspect", [("cornell", 1.0), ("veach", 1.5), ("teapot", 16 / 9), ("cornell_sphere", 1.0),
+                                         ("cornell_glossy", 1.0)])
+def test_scene_description_equals_reference_dump(built, name, aspect):
+    """The product's own OBJ/MTL loader + scene builders feed the GPU what the reference driver renders."""
+    ref, info = refutil.ref_dump(name, aspect)
+    scene = api.HostScene(name, aspect, 4)
+    a = scene.arrays()
+    tris = a["tris"]
+    order = np.argsort(tris[:, 0, 3].view(np.uint32))
+    is_tri = ref["kind"] == 0
+    g = ref["geom"][is_tri]
+    assert np.abs(tris[order, 0, :3] - g[:, 0]).max() == 0.0  # float32 vertices are exact
+    assert np.abs(tris[order, 1, :3] - (g[:, 1] - g[:, 0])).max() < 1e-6 * max(1.0, np.abs(g).max())
+    assert np.abs(tris[order, 2, :3] - (g[:, 2] - g[:, 0])).max() < 1e-6 * max(1.0, np.abs(g).max())
+    if a["tri_normals"].size:
+        assert np.abs(a["tri_normals"][order][:, :, :3] - g[:, 3:6]).max() < 1e-6
+    mats = a["materials"]
+    mid = tris[order, 1, 3].view(np.uint32)
+    assert (mats["type"][mid] == ref["mat_kind"][is_tri]).all()
+    assert np.abs(mats["p"][mid][:, :11] - ref["mat_p"][is_tri][:, :11]).max() < 1e-5
+    geo_flag = (tris[order, 2, 3].view(np.uint32) & 1).astype(np.float64)
+    assert (geo_flag == ref["geo_normals"][is_tri]).all()
+    assert scene.info["n_lights"] == ref["n_lights"]
+    cam = scene.desc.camera
+    mine = np.concatenate([np.array(getattr(cam, f)) for f in
+                           ("origin", "lower_left_corner", "horizontal", "vertical", "u", "v", "w")] + [[cam.lens_radius]])
+    assert np.abs(mine - ref["camera"]).max() < 1e-5 * max(1.0, np.abs(ref["camera"]).max())
+    # the host SAH build reports the node counts the reference prints (Scene::num_bvh_nodes, parallel_bvh.h:70,132,146)
+    assert scene.info["bvh_nodes"] == info["bvh_nodes"] and scene.info["bvh_leaves"] == info["bvh_leaves"]
+
+
+def test_soup_generator_and_builders(built):
+    tri = api.soup_triangles(5000)
+    assert np.array_equal(tri, api.soup_triangles(5000)), "splitmix64 stream is deterministic"
+    assert tri.min() >= -0.004 and tri.max() <= 1.004
+    slow = api.HostScene(soup=tri, max_leaf=4)
+    fast = api.HostScene(soup=tri, max_leaf=4, fast_bvh=True)
+    for s in (slow, fast):
+        a = s.arrays()
+        ids = a["tris"][:, 0, 3].view(np.uint32)
+        order = np.argsort(ids)
+        assert np.array_equal(np.sort(ids), np.arange(5000))
+        assert np.abs(a["tris"][order, 0, :3] - tri[:, :3]).max() == 0.0
+        seen, _ = _leaf_ranges(a["nodes"])
+        assert sorted(seen) == list(range(5000))
+
+
+def test_invalid_arguments_are_reported(built):
+    with pytest.raises(api.FrtError, match="unknown scene"):
+        api.HostScene("no_such_scene", 1.0, 4)
