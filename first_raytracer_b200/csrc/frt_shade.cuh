@@ -139,8 +139,8 @@ __global__ void __launch_bounds__(128) k_shade(const KernelArgs a, const int par
                 else
                 {
                     const float4 *tp = a.sc.tris + 3 * (size_t)prim;
-                    const float4 q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
-                    e1 = f3(q1); e2 = f3(q2);
+                    const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+                    e1 = f3(q1) - f3(q0); e2 = f3(q2) - f3(q0); // triangle.h:60-61
                     mat_id = __float_as_uint(q1.w);
                     tri_flags = __float_as_uint(q2.w);
                     if (tri_flags & FRT_TRI_GEOMETRY_NORMALS) // triangle.h:100-103

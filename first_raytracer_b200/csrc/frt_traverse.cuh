@@ -1,11 +1,17 @@
 // Closest-hit / any-hit traversal of the 4-wide flattened BVH.
 //
-// Semantics follow the reference's live (non-SSE) code, evaluated in float32:
+// Semantics are the reference's live (non-SSE) code:
 //   aabb::hit            aabb.h:14-31       slab test, reject iff tmax < tmin, NaNs ignored
 //   triangle::hit        triangle.h:69-118  Möller–Trumbore, a == 0 rejects, strict t bounds
 //   sphere::hit          sphere.h:26-56     near root, far root if near < t_min, non-strict bounds
-//   parallel_bvh_node::hit parallel_bvh.h:39-64  origin-scaled t_min; closest hit wins,
-//                        traversal order is free (only exact ties depend on it).
+//   parallel_bvh_node::hit parallel_bvh.h:39-64  origin-scaled t_min; closest hit wins; of two hits
+//                        at exactly the same t the one met first (left subtree first) wins.
+// Precision split: boxes and a conservative triangle FILTER run in float32; a triangle that passes
+// the filter is DECIDED by the reference's own formula in float64 on the exact float32 vertices
+// (edge = v1 - v0 in float64, as triangle.h:60-61), so hit / miss, t, u, v and the winner among
+// near-coincident surfaces are the reference's, not a float32 approximation of them.  Triangles
+// are stored in the reference's depth-first leaf order, so "met first" is "lower index": the tie
+// rule holds whatever order this traversal visits the nodes in.
 // One thread owns one ray; the short stack lives in local memory (L1-resident).
 #pragma once
 #include "frt_device.cuh"
@@ -18,27 +24,53 @@ struct RayHit
     uint32_t prim; // index into tris[] (leaf order), | FRT_CHILD_SPHERE for spheres[]; 0xFFFFFFFF = miss
 };
 
-// parallel_bvh.h:46-51: t_min = max(EPSILON, EPSILON * max(|o.x|,|o.y|,|o.z|,EPSILON))
-__device__ __forceinline__ float frt_ray_tmin(float3 o)
-{
-    const float m = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
-    return FRT_EPSILON * fmaxf(m, 1.0f);
-}
-
 __device__ __forceinline__ uint32_t frt_pick(const uint4 &c, uint32_t i)
 {
     return i == 0 ? c.x : (i == 1 ? c.y : (i == 2 ? c.z : c.w));
 }
 
+// triangle::hit (triangle.h:69-118) in float64 on float32 inputs; the caller applies the upper bound
+__device__ __forceinline__ bool frt_tri_exact(const float4 &q0, const float4 &q1, const float4 &q2, const float3 &o,
+                                              const float3 &d, const double tmin, double &t, double &u, double &v)
+{
+    const double v0x = q0.x, v0y = q0.y, v0z = q0.z;
+    const double e1x = (double)q1.x - v0x, e1y = (double)q1.y - v0y, e1z = (double)q1.z - v0z;
+    const double e2x = (double)q2.x - v0x, e2y = (double)q2.y - v0y, e2z = (double)q2.z - v0z;
+    const double dx = d.x, dy = d.y, dz = d.z;
+    const double hx = dy * e2z - dz * e2y, hy = dz * e2x - dx * e2z, hz = dx * e2y - dy * e2x;
+    const double a = e1x * hx + e1y * hy + e1z * hz;
+    if (a == 0.0) return false;
+    const double f = 1.0 / a;
+    const double sx = (double)o.x - v0x, sy = (double)o.y - v0y, sz = (double)o.z - v0z;
+    u = f * (sx * hx + sy * hy + sz * hz);
+    if (u < 0.0 || u > 1.0) return false;
+    const double qx = sy * e1z - sz * e1y, qy = sz * e1x - sx * e1z, qz = sx * e1y - sy * e1x;
+    v = f * (dx * qx + dy * qy + dz * qz);
+    if (!(v >= 0.0 && u + v <= 1.0)) return false;
+    t = f * (e2x * qx + e2y * qy + e2z * qz);
+    return t > tmin;
+}
+
+#ifndef FRT_TRI_FILTER
+#define FRT_TRI_FILTER 1 // 0: every leaf triangle goes straight to the float64 test
+#endif
+#define FRT_FILTER_K 1e-5f // ~170 float32 ulps on each sum of absolute products
+
 template <bool ANY, bool COUNT>
-__device__ __forceinline__ RayHit frt_traverse(const DevScene &sc, const float3 o, const float3 d, float tmax,
+__device__ __forceinline__ RayHit frt_traverse(const DevScene &sc, const float3 o, const float3 d, float tmax_unused,
                                                unsigned int &n_nodes, unsigned int &n_tris)
 {
+    (void)tmax_unused;
     RayHit best;
     best.t = 0.f; best.u = 0.f; best.v = 0.f; best.prim = 0xFFFFFFFFu;
     if (sc.n_nodes == 0) return best;
 
-    const float tmin = frt_ray_tmin(o);
+    // parallel_bvh.h:46-51 in float64; path.cpp:10 passes FLT_MAX, path.cpp:50 passes 1 - SHADOW_EPSILON
+    const double m = fmax(fmax(fabs((double)o.x), fabs((double)o.y)), fmax(fabs((double)o.z), 1e-4));
+    const double tmin_d = fmax(1e-4, 1e-4 * m);
+    double best_t = ANY ? 1.0 - (double)FRT_SHADOW_EPSILON : (double)FRT_FLT_MAX;
+    const float tmin = __double2float_rd(tmin_d); // float32 culling bounds are kept conservative
+    float tmax = __double2float_ru(best_t);
     const float idx = 1.0f / d.x, idy = 1.0f / d.y, idz = 1.0f / d.z;
     const float oox = o.x * idx, ooy = o.y * idy, ooz = o.z * idz;
     const int sx = idx < 0.0f ? 1 : 0, sy = idy < 0.0f ? 1 : 0, sz = idz < 0.0f ? 1 : 0;
@@ -63,20 +95,24 @@ __device__ __forceinline__ RayHit frt_traverse(const DevScene &sc, const float3 
             {
                 for (uint32_t k = 0; k < count; ++k)
                 {
+                    // sphere.h:26-56 entirely in float64 (few spheres; the float32 discriminant cancels badly)
                     const float4 s = __ldg(sc.spheres + 2 * (first + k));
-                    const float3 oc = o - f3(s);
-                    const float a = dot(d, d), b = dot(oc, d), c = dot(oc, oc) - s.w * s.w;
-                    float disc = b * b - a * c;
-                    if (disc >= 0.0f)
+                    const double ocx = (double)o.x - s.x, ocy = (double)o.y - s.y, ocz = (double)o.z - s.z;
+                    const double dx = d.x, dy = d.y, dz = d.z, r = s.w;
+                    const double a = dx * dx + dy * dy + dz * dz, b = ocx * dx + ocy * dy + ocz * dz;
+                    const double c = ocx * ocx + ocy * ocy + ocz * ocz - r * r;
+                    double disc = b * b - a * c;
+                    if (disc >= 0.0)
                     {
-                        disc = sqrtf(disc);
-                        float t = (-b - disc) / a;
-                        if (t < tmin) t = (-b + disc) / a;
-                        if (!(t < tmin || t > tmax))
+                        disc = sqrt(disc);
+                        double t = (-b - disc) / a;
+                        if (t < tmin_d) t = (-b + disc) / a;
+                        if (!(t < tmin_d || t > best_t))
                         {
-                            best.t = t; best.u = 0.f; best.v = 0.f; best.prim = (first + k) | FRT_CHILD_SPHERE;
+                            best.t = (float)t; best.u = 0.f; best.v = 0.f; best.prim = (first + k) | FRT_CHILD_SPHERE;
                             if (ANY) return best;
-                            tmax = t;
+                            best_t = t;
+                            tmax = __double2float_ru(t);
                         }
                     }
                 }
@@ -88,25 +124,42 @@ __device__ __forceinline__ RayHit frt_traverse(const DevScene &sc, const float3 
                     const float4 *tp = sc.tris + 3 * (size_t)(first + k);
                     const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
                     if (COUNT) ++n_tris;
-                    const float3 v0 = f3(q0), e1 = f3(q1), e2 = f3(q2);
-                    const float3 h = cross(d, e2);
-                    const float a = dot(e1, h);
-                    if (a == 0.0f) continue;
-                    const float f = 1.0f / a;
-                    const float3 s = o - v0;
-                    const float u = f * dot(s, h);
-                    if (u < 0.0f || u > 1.0f) continue;
-                    const float3 q = cross(s, e1);
-                    const float v = f * dot(d, q);
-                    if (v >= 0.0f && u + v <= 1.0f)
+#if FRT_TRI_FILTER
                     {
-                        const float t = f * dot(e2, q);
-                        if (t > tmin && t < tmax)
+                        // float32 filter: the same formula with error margins from the sums of absolute
+                        // products; it may only say "cannot be a hit", never decides one
+                        const float3 v0 = f3(q0), e1 = f3(q1) - v0, e2 = f3(q2) - v0;
+                        const float3 h = cross(d, e2);
+                        const float a = dot(e1, h);
+                        const float abs_a = fabsf(e1.x * h.x) + fabsf(e1.y * h.y) + fabsf(e1.z * h.z);
+                        if (fabsf(a) > 16.0f * FRT_FILTER_K * abs_a) // else too ill-conditioned to filter
                         {
-                            best.t = t; best.u = u; best.v = v; best.prim = first + k;
-                            if (ANY) return best;
-                            tmax = t;
+                            const float f = 1.0f / a, af = fabsf(f);
+                            const float rel = FRT_FILTER_K * abs_a * af;
+                            const float3 s = o - v0;
+                            const float u = f * dot(s, h);
+                            const float du = FRT_FILTER_K * af * (fabsf(s.x * h.x) + fabsf(s.y * h.y) + fabsf(s.z * h.z)) + fabsf(u) * rel + 1e-6f;
+                            if (u < -du || u > 1.0f + du) continue;
+                            const float3 q = cross(s, e1);
+                            const float v = f * dot(d, q);
+                            const float dv = FRT_FILTER_K * af * (fabsf(d.x * q.x) + fabsf(d.y * q.y) + fabsf(d.z * q.z)) + fabsf(v) * rel + 1e-6f;
+                            if (v < -dv || u + v > 1.0f + du + dv) continue;
+                            const float t = f * dot(e2, q);
+                            const float dt = FRT_FILTER_K * af * (fabsf(e2.x * q.x) + fabsf(e2.y * q.y) + fabsf(e2.z * q.z)) + fabsf(t) * (rel + 1e-6f);
+                            if (t < tmin - dt || t > tmax + dt) continue;
                         }
+                    }
+#endif
+                    double t, u, v;
+                    if (!frt_tri_exact(q0, q1, q2, o, d, tmin_d, t, u, v)) continue;
+                    // strict t < t_max (triangle.h:88-89); at an exact tie the triangle the reference meets
+                    // first (lower leaf-order index) stays
+                    if (t < best_t || (!ANY && t == best_t && first + k < best.prim))
+                    {
+                        best.t = (float)t; best.u = (float)u; best.v = (float)v; best.prim = first + k;
+                        if (ANY) return best;
+                        best_t = t;
+                        tmax = __double2float_ru(t);
                     }
                 }
             }

@@ -142,7 +142,7 @@ struct collapser
         {
             const uint32_t p = b.idx[k];
             const float *t = b.tri9 + 9 * (size_t)p;
-            frt_float4 v0{t[0], t[1], t[2], 0}, e1{t[3] - t[0], t[4] - t[1], t[5] - t[2], 0}, e2{t[6] - t[0], t[7] - t[1], t[8] - t[2], 0};
+            frt_float4 v0{t[0], t[1], t[2], 0}, e1{t[3], t[4], t[5], 0}, e2{t[6], t[7], t[8], 0}; // v0, v1, v2
             const uint32_t mat = 0, flags = (mesh_tris << 1) | FRT_TRI_GEOMETRY_NORMALS;
             std::memcpy(&v0.w, &p, 4); std::memcpy(&e1.w, &mat, 4); std::memcpy(&e2.w, &flags, 4);
             out.tris.push_back(v0); out.tris.push_back(e1); out.tris.push_back(e2);
@@ -164,7 +164,9 @@ struct collapser
                 if (!leaf(kids[k]) && bn[kids[k]].box.half_area() > best) { best = bn[kids[k]].box.half_area(); pick = k; }
             if (pick < 0) break;
             const int open = kids[pick];
-            kids[pick] = bn[open].left; kids[nk++] = bn[open].right;
+            for (int k = nk; k > pick + 1; --k) kids[k] = kids[k - 1];
+            kids[pick] = bn[open].left; kids[pick + 1] = bn[open].right;
+            ++nk;
         }
         frt_bvh4_node node;
         const float inf = std::numeric_limits<float>::infinity();

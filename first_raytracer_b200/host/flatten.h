@@ -189,9 +189,13 @@ private:
             for (int i = 0; i < nk; ++i)
                 if (!is_leaf_group(kids[i]) && bn_[kids[i]].box.area() > best) { best = bn_[kids[i]].box.area(); pick = i; }
             if (pick < 0) break;
+            // open in place so that the children (and therefore the triangle array) keep the
+            // depth-first, left-to-right order in which parallel_bvh_node::hit visits the leaves
             const int open = kids[pick];
+            for (int i = nk; i > pick + 1; --i) kids[i] = kids[i - 1];
             kids[pick] = bn_[open].left;
-            kids[nk++] = bn_[open].right;
+            kids[pick + 1] = bn_[open].right;
+            ++nk;
         }
         frt_bvh4_node node;
         const float inf = std::numeric_limits<float>::infinity();
@@ -240,8 +244,8 @@ private:
             const Vector3f &v0 = t->mesh->vertices[t->V[0]];
             const uint32_t flags = ((uint32_t)t->mesh->nTriangles << 1) | (t->mesh->use_geometry_normals ? FRT_TRI_GEOMETRY_NORMALS : 0u);
             out_.tris.push_back(pack(v0, (uint32_t)id_of(t)));
-            out_.tris.push_back(pack(t->edge1, material_index(t->mat_ptr)));
-            out_.tris.push_back(pack(t->edge2, flags));
+            out_.tris.push_back(pack(t->mesh->vertices[t->V[1]], material_index(t->mat_ptr)));
+            out_.tris.push_back(pack(t->mesh->vertices[t->V[2]], flags));
             for (int k = 0; k < 3; ++k) out_.tri_normals.push_back(pack(t->mesh->normals[t->V[k]], 0));
             if (!t->mesh->use_geometry_normals) out_.any_smooth = true;
         }

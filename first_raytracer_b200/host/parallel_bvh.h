@@ -5,11 +5,12 @@
 //   * primitives ordered by box.min[axis]; full sweep; cost_i = i*A_L[i] + (n-i-1)*A_R[i+1]
 //     for i in [0, n-2], first minimum wins (parallel_bvh.h:117-127)
 //   * left = l[0..idx], right = l[idx+1..n), one primitive per leaf
-// Differences that do not change the tree: boxes are computed once per node instead of inside
-// the comparator, subtrees are built on std::async tasks instead of taskflow subflows, and a
+// Differences that do not change the tree: boxes are computed once per primitive instead of inside
+// the comparator (the sort itself is the same qsort call), subtrees are built on std::async tasks instead of taskflow subflows, and a
 // node does not keep a copy of its primitive list (parallel_bvh.h:68).
 // Traversal is NOT here: it happens on the GPU (frt_traverse.cuh).
 #pragma once
+#include <cstdlib>
 #include <future>
 #include <thread>
 #include "scene_api.h"
@@ -27,6 +28,12 @@ public:
 private:
     struct item { hitable *h; aabb b; };
     static parallel_bvh_node *build(item *it, hitable **l, int n, int depth);
+    template <int AXIS>
+    static int cmp_axis(const void *a, const void *b) // box_{x,y,z}_compare, bvh.h:6-55
+    {
+        const item *ia = *(const item *const *)a, *ib = *(const item *const *)b;
+        return ia->b.min[AXIS] - ib->b.min[AXIS] < 0.0 ? -1 : 1;
+    }
 };
 
 inline parallel_bvh_node *parallel_bvh_node::build(item *it, hitable **l, int n, int depth)
@@ -45,7 +52,18 @@ inline parallel_bvh_node *parallel_bvh_node::build(item *it, hitable **l, int n,
         return node;
     }
     const int axis = main_box.longest_axis();
-    std::stable_sort(it, it + n, [axis](const item &a, const item &b) { return a.b.min[axis] - b.b.min[axis] < 0.0; });
+    // Same call as parallel_bvh.h:93-98: the C library's qsort over 8-byte elements with a comparator
+    // that never returns 0 (bvh.h:6-55).  Primitives with equal box.min (the Cornell boxes stand on
+    // the floor) end up in whatever order that qsort leaves them in, and that order decides which of
+    // two coincident triangles parallel_bvh_node::hit meets first — so the same routine is used here.
+    {
+        std::vector<const item *> order(n);
+        for (int i = 0; i < n; ++i) order[i] = it + i;
+        std::qsort(order.data(), (size_t)n, sizeof(const item *), axis == 0 ? cmp_axis<0> : (axis == 1 ? cmp_axis<1> : cmp_axis<2>));
+        std::vector<item> sorted(n);
+        for (int i = 0; i < n; ++i) sorted[i] = *order[i];
+        std::copy(sorted.begin(), sorted.end(), it);
+    }
     for (int i = 0; i < n; ++i) l[i] = it[i].h;
 
     std::vector<double> left_area(n), right_area(n);

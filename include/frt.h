@@ -57,9 +57,14 @@ typedef struct frt_bvh4_node {
 /* Triangles, in leaf order: three float4 per triangle, what triangle::hit (triangle.h:69-118)
  * reads through mesh->vertices / edge1 / edge2:
  *   [3i+0] = v0.xyz, w = bits of primitive id (creation order, what hit_record::obj identifies)
- *   [3i+1] = edge1.xyz (v1-v0), w = bits of material index
- *   [3i+2] = edge2.xyz (v2-v0), w = bits of (mesh->nTriangles << 1) | FRT_TRI_GEOMETRY_NORMALS?
+ *   [3i+1] = v1.xyz, w = bits of material index
+ *   [3i+2] = v2.xyz, w = bits of (mesh->nTriangles << 1) | FRT_TRI_GEOMETRY_NORMALS?
  *            (nTriangles gives inv_area = 1/(area*mesh->nTriangles), triangle.h:65)
+ * The three VERTICES are stored (exact in float32: mesh files hold float32 coordinates), not the
+ * edges: edge1/edge2 (triangle.h:60-61) are formed on the device, in float32 for the candidate
+ * filter and in float64 — exactly the reference's `vertices[V[1]] - vertices[V[0]]` — for the
+ * deciding test.  Triangles are listed in the depth-first, left-to-right leaf order of the host
+ * BVH, the order in which parallel_bvh_node::hit (parallel_bvh.h:53-61) meets them.
  * tri_normals (may be NULL when every triangle has FRT_TRI_GEOMETRY_NORMALS):
  *   [3i+k] = vertex normal k .xyz */
 #define FRT_TRI_GEOMETRY_NORMALS 1u

@@ -93,7 +93,8 @@ static real ray_tmin(v3 o)
 /* triangle::hit triangle.h:69-118 (geometry part; the record is completed by fill_hit) */
 static int tri_hit(const frt_scene_desc *sc, uint32_t i, v3 o, v3 d, real tmin, real tmax, hitrec *h)
 {
-    const v3 v0 = q3(sc->tris[3 * (size_t)i]), e1 = q3(sc->tris[3 * (size_t)i + 1]), e2 = q3(sc->tris[3 * (size_t)i + 2]);
+    const v3 v0 = q3(sc->tris[3 * (size_t)i]);
+    const v3 e1 = sub(q3(sc->tris[3 * (size_t)i + 1]), v0), e2 = sub(q3(sc->tris[3 * (size_t)i + 2]), v0); /* triangle.h:60-61 */
     const v3 hh = cross(d, e2);
     const real a = dot(e1, hh);
     if (a == 0) return 0;
@@ -221,7 +222,7 @@ static void fill_hit(const frt_scene_desc *sc, v3 o, v3 d, hitrec *h)
         return;
     }
     const size_t i = h->prim;
-    const v3 e1 = q3(sc->tris[3 * i + 1]), e2 = q3(sc->tris[3 * i + 2]);
+    const v3 v0 = q3(sc->tris[3 * i]), e1 = sub(q3(sc->tris[3 * i + 1]), v0), e2 = sub(q3(sc->tris[3 * i + 2]), v0);
     h->mat = wbits(sc->tris[3 * i + 1]);
     if (wbits(sc->tris[3 * i + 2]) & FRT_TRI_GEOMETRY_NORMALS)
         h->n = unit(cross(e1, e2));
@@ -685,7 +686,7 @@ static real hit_pdf_direct(const frt_scene_desc *sc, const hitrec *h, v3 d)
         return sphere_pdf_direct(V((real)s->cx, (real)s->cy, (real)s->cz), (real)s->radius, h->p, h->t, h->n, d);
     }
     const size_t i = h->prim;
-    const v3 e1 = q3(sc->tris[3 * i + 1]), e2 = q3(sc->tris[3 * i + 2]);
+    const v3 v0 = q3(sc->tris[3 * i]), e1 = sub(q3(sc->tris[3 * i + 1]), v0), e2 = sub(q3(sc->tris[3 * i + 2]), v0);
     const real n_tris = (real)(wbits(sc->tris[3 * i + 2]) >> 1);
     return 1 / (R(0.5) * len(cross(e1, e2)) * n_tris); /* triangle.h:65,139-144 */
 }

@@ -44,8 +44,8 @@ def test_same_random_numbers_as_reference(built, name, nx, ny, spp):
     print(f"{name}: mean gpu {mean_gpu:.6f} ref {mean_ref:.6f}, pixels within 0.2%: {close.mean():.4f}, "
           f"relMSE {refutil.rel_mse(gpu, ref):.3e}, gpu rays {st['closest_rays']}+{st['shadow_rays']}, "
           f"ref rays {info['closest_rays']}+{info['shadow_rays']}")
-    assert abs(mean_gpu - mean_ref) / mean_ref < 5e-3
-    assert close.mean() > 0.97
+    assert abs(gpu[close].mean() - ref[close].mean()) / ref[close].mean() < 1e-4
+    assert close.mean() > 0.999
     # closest-ray counts must agree closely: same paths, same lengths
     assert abs(st["closest_rays"] - info["closest_rays"]) / info["closest_rays"] < 2e-3
 
@@ -62,8 +62,11 @@ def test_same_random_numbers_as_golden(built, name, nx, ny, spp):
     dm = abs(gpu.mean() - ref.mean()) / ref.mean()
     print(f"{name} {nx}x{ny}x{spp}: pixels within 0.2% {close.mean():.4f}, mean diff {dm:.2e}, "
           f"closest rays gpu {st['closest_rays']} ref {int(g['closest_rays'])}")
-    assert close.mean() > 0.95
-    assert dm < 5e-3 if nx * ny * spp > 100_000 else dm < 5e-2  # tiny fixtures: one flipped path moves the mean
+    # a path whose float32 shading flips a branch can carry an 800-radiance light sample (veach): such
+    # pixels are counted (< 0.1 %) and the mean is compared over the others
+    dm_close = abs(gpu[close].mean() - ref[close].mean()) / ref[close].mean()
+    assert close.mean() > 0.999 if nx * ny > 10_000 else close.mean() > 0.99
+    assert dm_close < 1e-4
     assert abs(st["closest_rays"] - int(g["closest_rays"])) / int(g["closest_rays"]) < 5e-3
 
 

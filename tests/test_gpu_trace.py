@@ -7,9 +7,10 @@ Checkers, strongest first:
   * the C restatement oracle/libfrt_oracle.so (float64) for scenes without a fixture (soup).
 Bars (BASELINE.json): primitive-id agreement >= 99.99 %, |t_gpu - t_ref| / t_ref <= 1e-5 on
 matching hits, any-hit agreement >= 99.99 %.  The device computes in float32, the reference in
-float64, on identical float32 ray and vertex data.  Id agreement is reported strictly and with
-exact geometric ties (coincident surfaces, e.g. the Cornell boxes standing on the floor) counted as
-agreement: there the reference's winner is set by its traversal order and last-bit rounding."""
+float64, on identical float32 ray and vertex data.  The device filters candidates in float32 and
+decides them with the reference's formula in float64; triangles are stored in the reference's
+depth-first leaf order so that exact ties (the Cornell boxes stand on the floor) fall the same way.
+Agreement is asserted strictly; the tie-adjusted figure is printed beside it."""
 import numpy as np
 import pytest
 
@@ -36,8 +37,8 @@ def _check_closest(scene, rays, hits, ref_prim, ref_t, label):
     print(f"{label}: id agreement strict {strict:.6f} / ties counted {adjusted:.6f}, rel t max {rel.max():.2e} "
           f"p99.99 {np.quantile(rel, 0.9999):.2e}, hits {both.sum()}")
     assert both.sum() > 1000
-    assert adjusted >= 0.9999           # BASELINE.json: >= 99.99 %
-    assert np.quantile(rel, 0.9999) <= 1e-5  # BASELINE.json: t within 1e-5 relative
+    assert strict >= 0.9999   # BASELINE.json: >= 99.99 % — strict, exact ties included
+    assert rel.max() <= 1e-5  # BASELINE.json: t within 1e-5 relative (float32 rounding of a float64 t: ~6e-8)
     return strict, adjusted
 
 
@@ -127,7 +128,7 @@ def test_trace_edge_cases(built):
     assert hits.shape == (0,)
     # outside pointing away; zero-length direction; straight at the back wall; axis-parallel downwards
     rays = np.zeros(4, dtype=api.RAY_DTYPE)
-    rays["o"] = [[0, 1, 10], [0, 1, 0.5], [0, 1, 3], [0.3, 0.7, 0.2]]
+    rays["o"] = [[0, 1, 10], [0, 1, 0.5], [0, 1.5, 3], [0.3, 0.7, 0.2]]
     rays["d"] = [[0, 0, 1], [0, 0, 0], [0, 0, -1], [0, -1, 0]]
     hits, _ = ctx.trace(rays)
     want = oracle_c.Oracle(scene).trace(rays)

@@ -47,15 +47,16 @@ def test_oracle_trace_matches_golden(built, name, aspect):
         # traversal order in the reference: counted separately, see Oracle.id_agreement
         strict, adjusted = oracle_c.Oracle(scene).id_agreement(rays, o["prim"], g["prim"], g["t"])
         assert adjusted >= 0.9999, f"{name} use_bvh={use_bvh}: strict {strict}, tie-adjusted {adjusted}"
-        assert strict >= 0.97
+        # triangles are listed in the reference's depth-first leaf order (host build = the same qsort),
+        # so even exact ties fall the reference's way
+        assert strict >= 0.9999, f"{name} use_bvh={use_bvh}: strict {strict}"
         both = agree & (g["prim"] >= 0)
-        # the description carries edge1/edge2 rounded to float32 (the reference keeps the float64
-        # difference of float32 vertices), which grazing rays amplify: bar = BASELINE's 1e-5
+        # same float32 vertices, same float64 formula: t agrees to rounding
         rel = np.abs(o["t"][both] - g["t"][both]) / g["t"][both]
-        assert rel.max() < 1e-5 and np.quantile(rel, 0.99) < 1e-6
+        assert rel.max() < 1e-11
         # barycentrics only exist for triangles (sphere::hit leaves hit_record::uv stale, sphere.h:26-56)
         tri = both & ~np.isin(g["prim"], scene.arrays()["spheres"]["prim_id"].astype(np.int64))
-        assert np.quantile(np.abs(o["u"][tri] - g["u"][tri]), 0.99) < 1e-5
+        assert np.abs(o["u"][tri] - g["u"][tri]).max() < 1e-9
     srays = np.zeros(g["segments"].shape[0], api.RAY_DTYPE)
     srays["o"], srays["d"] = g["segments"][:, :3], g["segments"][:, 3:]
     occ = oracle_c.Oracle(scene).trace(srays, any_hit=True)["prim"] >= 0
