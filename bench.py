@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--spp", type=int, default=SPP, help="debug only: a run with --spp != 1024 is not a bench value")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true", help="skip the per-kernel timing pass (profiling runs)")
     return ap.parse_args()
 
 
@@ -172,7 +173,7 @@ def run_frt(args):
     spp = args.spp
     s0, s1 = spp * rank // world, spp * (rank + 1) // world
 
-    scene = api.HostScene(SCENE, NX / NY, 4)
+    scene = api.HostScene(SCENE, NX / NY, int(os.environ.get("FRT_MAX_LEAF", "4")))
     ctx = api.Context(devices=[local])
     ctx.upload(scene)
     stream = torch.cuda.ExternalStream(ctx.stream_handle(0), device=dev)
@@ -292,7 +293,7 @@ def main():
     total_s = res["total_ms"] * 1e-3
     value = steps * NX * NY * spp / total_s / 1e6
     roof = cpu = e2e = None
-    if rank == 0:
+    if rank == 0 and not args.no_roofline:
         roof = roofline_pass(ctx, api, (0, max(1, spp // world)), peaks)
     ctx.close()
     if world > 1:

@@ -16,7 +16,7 @@
 #pragma once
 #include "frt_device.cuh"
 
-#define FRT_STACK_SIZE 96
+#define FRT_STACK_SIZE 64
 
 struct RayHit
 {
@@ -29,71 +29,126 @@ __device__ __forceinline__ uint32_t frt_pick(const uint4 &c, uint32_t i)
     return i == 0 ? c.x : (i == 1 ? c.y : (i == 2 ? c.z : c.w));
 }
 
-// triangle::hit (triangle.h:69-118) in float64 on float32 inputs; the caller applies the upper bound
-__device__ __forceinline__ bool frt_tri_exact(const float4 &q0, const float4 &q1, const float4 &q2, const float3 &o,
-                                              const float3 &d, const double tmin, double &t, double &u, double &v)
+// triangle::hit (triangle.h:69-118) in float64 on the exact float32 vertices of triangle `prim`;
+// t < 0 means "no hit" (hits have t > t_min > 0); the caller applies the upper bound.  Kept out of
+// line: it runs off the fast path (ambiguous candidates) and once per ray for the winner.
+struct ExactHit { double t; float u, v; };
+__device__ __noinline__ ExactHit frt_tri_exact(const float4 *tris, uint32_t prim, float ox, float oy, float oz, float dxf,
+                                               float dyf, float dzf, double tmin)
 {
+    const float4 *tp = tris + 3 * (size_t)prim;
+    const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+    ExactHit r;
+    r.t = -1.0; r.u = 0.f; r.v = 0.f;
     const double v0x = q0.x, v0y = q0.y, v0z = q0.z;
     const double e1x = (double)q1.x - v0x, e1y = (double)q1.y - v0y, e1z = (double)q1.z - v0z;
     const double e2x = (double)q2.x - v0x, e2y = (double)q2.y - v0y, e2z = (double)q2.z - v0z;
-    const double dx = d.x, dy = d.y, dz = d.z;
+    const double dx = dxf, dy = dyf, dz = dzf;
     const double hx = dy * e2z - dz * e2y, hy = dz * e2x - dx * e2z, hz = dx * e2y - dy * e2x;
     const double a = e1x * hx + e1y * hy + e1z * hz;
-    if (a == 0.0) return false;
+    if (a == 0.0) return r;
     const double f = 1.0 / a;
-    const double sx = (double)o.x - v0x, sy = (double)o.y - v0y, sz = (double)o.z - v0z;
-    u = f * (sx * hx + sy * hy + sz * hz);
-    if (u < 0.0 || u > 1.0) return false;
+    const double sx = (double)ox - v0x, sy = (double)oy - v0y, sz = (double)oz - v0z;
+    const double u = f * (sx * hx + sy * hy + sz * hz);
+    if (u < 0.0 || u > 1.0) return r;
     const double qx = sy * e1z - sz * e1y, qy = sz * e1x - sx * e1z, qz = sx * e1y - sy * e1x;
-    v = f * (dx * qx + dy * qy + dz * qz);
-    if (!(v >= 0.0 && u + v <= 1.0)) return false;
-    t = f * (e2x * qx + e2y * qy + e2z * qz);
-    return t > tmin;
+    const double v = f * (dx * qx + dy * qy + dz * qz);
+    if (!(v >= 0.0 && u + v <= 1.0)) return r;
+    const double t = f * (e2x * qx + e2y * qy + e2z * qz);
+    if (t > tmin) { r.t = t; r.u = (float)u; r.v = (float)v; }
+    return r;
 }
 
-#ifndef FRT_TRI_FILTER
-#define FRT_TRI_FILTER 1 // 0: every leaf triangle goes straight to the float64 test
-#endif
 #define FRT_FILTER_K 1e-5f // ~170 float32 ulps on each sum of absolute products
 
+// Closest hit so far.  A hit that the float32 test places clearly inside the triangle and clearly
+// in front of everything found so far is taken on its float32 interval [lo, hi] ("lazy"); float64
+// is evaluated only when two candidates' intervals overlap or a candidate sits on an edge / on the
+// t bounds, and once at the end for the winner (converged across the warp), which gives t, u, v.
+struct BestHit
+{
+    uint32_t prim;
+    float lo, hi; // bounds on t (the rounded float64 value once exact)
+    float u, v;
+    double t;     // valid iff exact
+    bool exact;
+};
+
 template <bool ANY, bool COUNT>
-__device__ __forceinline__ RayHit frt_traverse(const DevScene &sc, const float3 o, const float3 d, float tmax_unused,
+__device__ __forceinline__ RayHit frt_traverse(const DevScene &sc, const float3 o, const float3 d, float /*unused*/,
                                                unsigned int &n_nodes, unsigned int &n_tris)
 {
-    (void)tmax_unused;
-    RayHit best;
-    best.t = 0.f; best.u = 0.f; best.v = 0.f; best.prim = 0xFFFFFFFFu;
-    if (sc.n_nodes == 0) return best;
+    RayHit out;
+    out.t = 0.f; out.u = 0.f; out.v = 0.f; out.prim = 0xFFFFFFFFu;
+    if (sc.n_nodes == 0) return out;
 
     // parallel_bvh.h:46-51 in float64; path.cpp:10 passes FLT_MAX, path.cpp:50 passes 1 - SHADOW_EPSILON
     const double m = fmax(fmax(fabs((double)o.x), fabs((double)o.y)), fmax(fabs((double)o.z), 1e-4));
     const double tmin_d = fmax(1e-4, 1e-4 * m);
-    double best_t = ANY ? 1.0 - (double)FRT_SHADOW_EPSILON : (double)FRT_FLT_MAX;
-    const float tmin = __double2float_rd(tmin_d); // float32 culling bounds are kept conservative
-    float tmax = __double2float_ru(best_t);
+    const double tend_d = ANY ? 1.0 - (double)FRT_SHADOW_EPSILON : (double)FRT_FLT_MAX;
+    const float tmin = __double2float_rd(tmin_d), tmin_hi = __double2float_ru(tmin_d); // conservative float32 bounds
+    BestHit best;
+    best.prim = 0xFFFFFFFFu; best.u = best.v = 0.f; best.t = tend_d; best.exact = true;
+    best.lo = __double2float_rd(tend_d); best.hi = __double2float_ru(tend_d);
+    float tmax = best.hi; // culling bound
     const float idx = 1.0f / d.x, idy = 1.0f / d.y, idz = 1.0f / d.z;
     const float oox = o.x * idx, ooy = o.y * idy, ooz = o.z * idz;
     const int sx = idx < 0.0f ? 1 : 0, sy = idy < 0.0f ? 1 : 0, sz = idz < 0.0f ? 1 : 0;
 
-    uint32_t stack[FRT_STACK_SIZE];
+    uint32_t stack[FRT_STACK_SIZE]; // child reference
+    float stack_t[FRT_STACK_SIZE];  // its entry distance, to drop it at pop time once something closer was found
     int sp = 0;
     uint32_t cur = 0;
 
     while (true)
     {
-        if (cur == FRT_CHILD_EMPTY)
+        // ---- while-while, part 1: descend through inner nodes (EMPTY carries the leaf bit and ends the loop)
+        while (!(cur & FRT_CHILD_LEAF))
         {
-            if (sp == 0) break;
-            cur = stack[--sp];
-            continue;
+            // eight 128-bit loads, near/far planes picked by ray-direction sign
+            const float4 *n = sc.nodes + 8 * (size_t)cur;
+            if (COUNT) ++n_nodes;
+            const float4 nx = __ldg(n + (0 ^ sx)), fx = __ldg(n + (1 ^ sx));
+            const float4 ny = __ldg(n + (2 ^ sy)), fy = __ldg(n + (3 ^ sy));
+            const float4 nz = __ldg(n + (4 ^ sz)), fz = __ldg(n + (5 ^ sz));
+            const uint4 ch = __ldg(reinterpret_cast<const uint4 *>(n + 6));
+            // fmaxf / fminf drop a NaN operand, like aabb.h:24-25's `t0 > tmin ? t0 : tmin`
+            const float tn0 = fmaxf(fmaxf(nx.x * idx - oox, ny.x * idy - ooy), fmaxf(nz.x * idz - ooz, tmin));
+            const float tn1 = fmaxf(fmaxf(nx.y * idx - oox, ny.y * idy - ooy), fmaxf(nz.y * idz - ooz, tmin));
+            const float tn2 = fmaxf(fmaxf(nx.z * idx - oox, ny.z * idy - ooy), fmaxf(nz.z * idz - ooz, tmin));
+            const float tn3 = fmaxf(fmaxf(nx.w * idx - oox, ny.w * idy - ooy), fmaxf(nz.w * idz - ooz, tmin));
+            const float tf0 = fminf(fminf(fx.x * idx - oox, fy.x * idy - ooy), fminf(fz.x * idz - ooz, tmax));
+            const float tf1 = fminf(fminf(fx.y * idx - oox, fy.y * idy - ooy), fminf(fz.y * idz - ooz, tmax));
+            const float tf2 = fminf(fminf(fx.z * idx - oox, fy.z * idy - ooy), fminf(fz.z * idz - ooz, tmax));
+            const float tf3 = fminf(fminf(fx.w * idx - oox, fy.w * idy - ooy), fminf(fz.w * idz - ooz, tmax));
+            // sort the (up to four) intersected children near-to-far: key = quantised tnear | slot
+            uint32_t k0 = (tf0 >= tn0) ? ((__float_as_uint(tn0) & ~3u) | 0u) : 0xFFFFFFFFu;
+            uint32_t k1 = (tf1 >= tn1) ? ((__float_as_uint(tn1) & ~3u) | 1u) : 0xFFFFFFFFu;
+            uint32_t k2 = (tf2 >= tn2) ? ((__float_as_uint(tn2) & ~3u) | 2u) : 0xFFFFFFFFu;
+            uint32_t k3 = (tf3 >= tn3) ? ((__float_as_uint(tn3) & ~3u) | 3u) : 0xFFFFFFFFu;
+            uint32_t a, b;
+            a = min(k0, k1); b = max(k0, k1); k0 = a; k1 = b;
+            a = min(k2, k3); b = max(k2, k3); k2 = a; k3 = b;
+            a = min(k0, k2); b = max(k0, k2); k0 = a; k2 = b;
+            a = min(k1, k3); b = max(k1, k3); k1 = a; k3 = b;
+            a = min(k1, k2); b = max(k1, k2); k1 = a; k2 = b;
+            if (k3 != 0xFFFFFFFFu && sp < FRT_STACK_SIZE) { stack[sp] = frt_pick(ch, k3 & 3u); stack_t[sp++] = __uint_as_float(k3 & ~3u); }
+            if (k2 != 0xFFFFFFFFu && sp < FRT_STACK_SIZE) { stack[sp] = frt_pick(ch, k2 & 3u); stack_t[sp++] = __uint_as_float(k2 & ~3u); }
+            if (k1 != 0xFFFFFFFFu && sp < FRT_STACK_SIZE) { stack[sp] = frt_pick(ch, k1 & 3u); stack_t[sp++] = __uint_as_float(k1 & ~3u); }
+            cur = (k0 != 0xFFFFFFFFu) ? frt_pick(ch, k0 & 3u) : FRT_CHILD_EMPTY;
         }
-        if (cur & FRT_CHILD_LEAF)
+
+        // ---- part 2: one leaf
+        if (cur != FRT_CHILD_EMPTY)
         {
             const uint32_t first = cur & FRT_LEAF_FIRST_MASK;
             const uint32_t count = ((cur >> FRT_LEAF_COUNT_SHIFT) & 15u) + 1u;
-            if (cur & FRT_CHILD_SPHERE)
+            const bool is_sphere = cur & FRT_CHILD_SPHERE;
+            for (uint32_t k = 0; k < count; ++k)
             {
-                for (uint32_t k = 0; k < count; ++k)
+                const uint32_t prim = is_sphere ? ((first + k) | FRT_CHILD_SPHERE) : first + k;
+                ExactHit e;
+                if (is_sphere)
                 {
                     // sphere.h:26-56 entirely in float64 (few spheres; the float32 discriminant cancels badly)
                     const float4 s = __ldg(sc.spheres + 2 * (first + k));
@@ -102,105 +157,93 @@ __device__ __forceinline__ RayHit frt_traverse(const DevScene &sc, const float3 
                     const double a = dx * dx + dy * dy + dz * dz, b = ocx * dx + ocy * dy + ocz * dz;
                     const double c = ocx * ocx + ocy * ocy + ocz * ocz - r * r;
                     double disc = b * b - a * c;
-                    if (disc >= 0.0)
-                    {
-                        disc = sqrt(disc);
-                        double t = (-b - disc) / a;
-                        if (t < tmin_d) t = (-b + disc) / a;
-                        if (!(t < tmin_d || t > best_t))
-                        {
-                            best.t = (float)t; best.u = 0.f; best.v = 0.f; best.prim = (first + k) | FRT_CHILD_SPHERE;
-                            if (ANY) return best;
-                            best_t = t;
-                            tmax = __double2float_ru(t);
-                        }
-                    }
+                    if (!(disc >= 0.0)) continue;
+                    disc = sqrt(disc);
+                    double t = (-b - disc) / a;
+                    if (t < tmin_d) t = (-b + disc) / a;
+                    if (t < tmin_d || t > tend_d) continue;
+                    e.t = t; e.u = 0.f; e.v = 0.f;
                 }
-            }
-            else
-            {
-                for (uint32_t k = 0; k < count; ++k)
+                else
                 {
-                    const float4 *tp = sc.tris + 3 * (size_t)(first + k);
+                    const float4 *tp = sc.tris + 3 * (size_t)prim;
                     const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
                     if (COUNT) ++n_tris;
-#if FRT_TRI_FILTER
+                    // float32 pass: the same formula with error margins from the sums of absolute products
+                    const float3 v0 = f3(q0), e1 = f3(q1) - v0, e2 = f3(q2) - v0;
+                    const float3 h = cross(d, e2);
+                    const float a = dot(e1, h);
+                    const float abs_a = fabsf(e1.x * h.x) + fabsf(e1.y * h.y) + fabsf(e1.z * h.z);
+                    if (fabsf(a) > 16.0f * FRT_FILTER_K * abs_a) // else too ill-conditioned for float32: decide exactly
                     {
-                        // float32 filter: the same formula with error margins from the sums of absolute
-                        // products; it may only say "cannot be a hit", never decides one
-                        const float3 v0 = f3(q0), e1 = f3(q1) - v0, e2 = f3(q2) - v0;
-                        const float3 h = cross(d, e2);
-                        const float a = dot(e1, h);
-                        const float abs_a = fabsf(e1.x * h.x) + fabsf(e1.y * h.y) + fabsf(e1.z * h.z);
-                        if (fabsf(a) > 16.0f * FRT_FILTER_K * abs_a) // else too ill-conditioned to filter
+                        const float f = 1.0f / a, af = fabsf(f);
+                        const float rel = FRT_FILTER_K * abs_a * af;
+                        const float3 s = o - v0;
+                        const float uf = f * dot(s, h);
+                        const float du = FRT_FILTER_K * af * (fabsf(s.x * h.x) + fabsf(s.y * h.y) + fabsf(s.z * h.z)) + fabsf(uf) * rel + 1e-6f;
+                        if (uf < -du || uf > 1.0f + du) continue;
+                        const float3 q = cross(s, e1);
+                        const float vf = f * dot(d, q);
+                        const float dv = FRT_FILTER_K * af * (fabsf(d.x * q.x) + fabsf(d.y * q.y) + fabsf(d.z * q.z)) + fabsf(vf) * rel + 1e-6f;
+                        if (vf < -dv || uf + vf > 1.0f + du + dv) continue;
+                        const float tf = f * dot(e2, q);
+                        const float dt = FRT_FILTER_K * af * (fabsf(e2.x * q.x) + fabsf(e2.y * q.y) + fabsf(e2.z * q.z)) + fabsf(tf) * (rel + 1e-6f);
+                        if (tf < tmin - dt || tf > tmax + dt) continue; // certainly outside (t_min, closest so far)
+                        if (uf > du && vf > dv && uf + vf < 1.0f - du - dv && tf - dt > tmin_hi && tf + dt < best.lo)
                         {
-                            const float f = 1.0f / a, af = fabsf(f);
-                            const float rel = FRT_FILTER_K * abs_a * af;
-                            const float3 s = o - v0;
-                            const float u = f * dot(s, h);
-                            const float du = FRT_FILTER_K * af * (fabsf(s.x * h.x) + fabsf(s.y * h.y) + fabsf(s.z * h.z)) + fabsf(u) * rel + 1e-6f;
-                            if (u < -du || u > 1.0f + du) continue;
-                            const float3 q = cross(s, e1);
-                            const float v = f * dot(d, q);
-                            const float dv = FRT_FILTER_K * af * (fabsf(d.x * q.x) + fabsf(d.y * q.y) + fabsf(d.z * q.z)) + fabsf(v) * rel + 1e-6f;
-                            if (v < -dv || u + v > 1.0f + du + dv) continue;
-                            const float t = f * dot(e2, q);
-                            const float dt = FRT_FILTER_K * af * (fabsf(e2.x * q.x) + fabsf(e2.y * q.y) + fabsf(e2.z * q.z)) + fabsf(t) * (rel + 1e-6f);
-                            if (t < tmin - dt || t > tmax + dt) continue;
+                            // certainly a hit and certainly the closest so far
+                            if (ANY) { out.t = tf; out.prim = prim; return out; }
+                            best.prim = prim; best.lo = tf - dt; best.hi = tf + dt; best.u = uf; best.v = vf; best.exact = false;
+                            tmax = best.hi;
+                            continue;
                         }
                     }
-#endif
-                    double t, u, v;
-                    if (!frt_tri_exact(q0, q1, q2, o, d, tmin_d, t, u, v)) continue;
-                    // strict t < t_max (triangle.h:88-89); at an exact tie the triangle the reference meets
-                    // first (lower leaf-order index) stays
-                    if (t < best_t || (!ANY && t == best_t && first + k < best.prim))
-                    {
-                        best.t = (float)t; best.u = (float)u; best.v = (float)v; best.prim = first + k;
-                        if (ANY) return best;
-                        best_t = t;
-                        tmax = __double2float_ru(t);
-                    }
+                    e = frt_tri_exact(sc.tris, prim, o.x, o.y, o.z, d.x, d.y, d.z, tmin_d);
+                    if (e.t < 0.0) continue;
+                }
+                // float64 decision: strict t < t_max for triangles (triangle.h:88-89), t <= t_max for spheres
+                // (sphere.h:41); at an exact tie the triangle the reference meets first (lower index) stays
+                if (ANY)
+                {
+                    if (is_sphere || e.t < tend_d) { out.t = (float)e.t; out.prim = prim; return out; }
+                    continue;
+                }
+                if (!best.exact) // the closest so far was taken on its float32 interval: pin it down now
+                {
+                    const ExactHit b = frt_tri_exact(sc.tris, best.prim, o.x, o.y, o.z, d.x, d.y, d.z, tmin_d);
+                    if (b.t >= 0.0) { best.t = b.t; best.u = b.u; best.v = b.v; }
+                    else best.t = 0.5 * ((double)best.lo + (double)best.hi); // not reachable while the margins hold
+                    best.exact = true;
+                }
+                const bool closer = is_sphere ? !(e.t > best.t) : (e.t < best.t || (e.t == best.t && prim < best.prim));
+                if (closer)
+                {
+                    best.prim = prim; best.t = e.t; best.exact = true; best.u = e.u; best.v = e.v;
+                    best.lo = __double2float_rd(e.t); best.hi = __double2float_ru(e.t);
+                    tmax = best.hi;
                 }
             }
-            cur = FRT_CHILD_EMPTY;
-            continue;
         }
 
-        // inner node: eight 128-bit loads, near/far planes picked by ray-direction sign
-        const float4 *n = sc.nodes + 8 * (size_t)cur;
-        if (COUNT) ++n_nodes;
-        const float4 nx = __ldg(n + (0 ^ sx)), fx = __ldg(n + (1 ^ sx));
-        const float4 ny = __ldg(n + (2 ^ sy)), fy = __ldg(n + (3 ^ sy));
-        const float4 nz = __ldg(n + (4 ^ sz)), fz = __ldg(n + (5 ^ sz));
-        const uint4 ch = __ldg(reinterpret_cast<const uint4 *>(n + 6));
-
-        // fmaxf / fminf drop a NaN operand, like aabb.h:24-25's `t0 > tmin ? t0 : tmin`
-        const float tn0 = fmaxf(fmaxf(nx.x * idx - oox, ny.x * idy - ooy), fmaxf(nz.x * idz - ooz, tmin));
-        const float tn1 = fmaxf(fmaxf(nx.y * idx - oox, ny.y * idy - ooy), fmaxf(nz.y * idz - ooz, tmin));
-        const float tn2 = fmaxf(fmaxf(nx.z * idx - oox, ny.z * idy - ooy), fmaxf(nz.z * idz - ooz, tmin));
-        const float tn3 = fmaxf(fmaxf(nx.w * idx - oox, ny.w * idy - ooy), fmaxf(nz.w * idz - ooz, tmin));
-        const float tf0 = fminf(fminf(fx.x * idx - oox, fy.x * idy - ooy), fminf(fz.x * idz - ooz, tmax));
-        const float tf1 = fminf(fminf(fx.y * idx - oox, fy.y * idy - ooy), fminf(fz.y * idz - ooz, tmax));
-        const float tf2 = fminf(fminf(fx.z * idx - oox, fy.z * idy - ooy), fminf(fz.z * idz - ooz, tmax));
-        const float tf3 = fminf(fminf(fx.w * idx - oox, fy.w * idy - ooy), fminf(fz.w * idz - ooz, tmax));
-
-        // sort the (up to four) intersected children near-to-far: key = quantised tnear | slot
-        uint32_t k0 = (tf0 >= tn0) ? ((__float_as_uint(tn0) & ~3u) | 0u) : 0xFFFFFFFFu;
-        uint32_t k1 = (tf1 >= tn1) ? ((__float_as_uint(tn1) & ~3u) | 1u) : 0xFFFFFFFFu;
-        uint32_t k2 = (tf2 >= tn2) ? ((__float_as_uint(tn2) & ~3u) | 2u) : 0xFFFFFFFFu;
-        uint32_t k3 = (tf3 >= tn3) ? ((__float_as_uint(tn3) & ~3u) | 3u) : 0xFFFFFFFFu;
-        uint32_t a, b;
-        a = min(k0, k1); b = max(k0, k1); k0 = a; k1 = b;
-        a = min(k2, k3); b = max(k2, k3); k2 = a; k3 = b;
-        a = min(k0, k2); b = max(k0, k2); k0 = a; k2 = b;
-        a = min(k1, k3); b = max(k1, k3); k1 = a; k3 = b;
-        a = min(k1, k2); b = max(k1, k2); k1 = a; k2 = b;
-
-        if (k3 != 0xFFFFFFFFu && sp < FRT_STACK_SIZE) stack[sp++] = frt_pick(ch, k3 & 3u);
-        if (k2 != 0xFFFFFFFFu && sp < FRT_STACK_SIZE) stack[sp++] = frt_pick(ch, k2 & 3u);
-        if (k1 != 0xFFFFFFFFu && sp < FRT_STACK_SIZE) stack[sp++] = frt_pick(ch, k1 & 3u);
-        cur = (k0 != 0xFFFFFFFFu) ? frt_pick(ch, k0 & 3u) : FRT_CHILD_EMPTY;
+        // ---- pop the nearest postponed child that can still hold something closer
+        bool more = false;
+        while (sp > 0)
+        {
+            --sp;
+            if (stack_t[sp] <= tmax) { cur = stack[sp]; more = true; break; }
+        }
+        if (!more) break;
     }
-    return best;
+
+    if (best.prim != 0xFFFFFFFFu)
+    {
+        if (!best.exact) // one float64 evaluation per ray, outside the loop: t, u, v of the winner
+        {
+            const ExactHit b = frt_tri_exact(sc.tris, best.prim, o.x, o.y, o.z, d.x, d.y, d.z, tmin_d);
+            if (b.t >= 0.0) { best.t = b.t; best.u = b.u; best.v = b.v; }
+            else best.t = 0.5 * ((double)best.lo + (double)best.hi);
+        }
+        out.t = (float)best.t; out.u = best.u; out.v = best.v; out.prim = best.prim;
+    }
+    return out;
 }
