@@ -18,6 +18,7 @@ REPO_DIR = PKG_DIR.parent
 FRT_OK = 0
 FRT_FLAG_COUNTERS = 1
 FRT_FLAG_KERNEL_TIMERS = 2
+FRT_FLAG_STREAMED_POOL = 4
 
 # every exported symbol of include/frt.h and include/frt_host.h (tests check the libraries export them)
 FRT_SYMBOLS = [

@@ -32,6 +32,8 @@ int frt_create(frt_ctx **out, const int *devices, int n)
     c->dev.resize(n);
     if (const char *s = getenv("FRT_POOL_SLOTS")) c->n_slots = (unsigned int)std::max(1024ll, atoll(s));
     if (const char *s = getenv("FRT_POLL_EVERY")) c->poll_every = std::max(1, atoi(s));
+    if (const char *s = getenv("FRT_WF_SLOTS"))
+        c->wf_slots = (unsigned int)std::min(1536, std::max(FRT_WF_THREADS, atoi(s) / FRT_WF_THREADS * FRT_WF_THREADS));
     for (int i = 0; i < n; ++i)
     {
         Device &d = c->dev[i];
@@ -60,6 +62,16 @@ int frt_create(frt_ctx **out, const int *devices, int n)
         d.blocks_connect = std::max(1, per_sm) * d.sms;
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<false, false>, 128, 0));
         d.blocks_trace = std::max(1, per_sm) * d.sms;
+        const size_t wf_smem = (size_t)c->wf_slots * FRT_WF_SLOT_BYTES;
+        CU(cudaFuncSetAttribute(k_wavefront<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
+        CU(cudaFuncSetAttribute(k_wavefront<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wavefront<false>, FRT_WF_THREADS, wf_smem));
+        if (per_sm < 1)
+        {
+            delete c;
+            return fail(nullptr, FRT_ERR_CUDA, "frt_create: k_wavefront does not fit an SM with %u slots per CTA", c->wf_slots);
+        }
+        d.blocks_wavefront = per_sm * d.sms;
     }
     // peer access for the in-process film reduction
     for (int i = 1; i < n; ++i)

@@ -9,6 +9,7 @@
 #include <string>
 #include <vector>
 #include "frt_shade.cuh"
+#include "frt_wavefront.cuh"
 
 namespace {
 
@@ -38,7 +39,8 @@ struct Device
     float *d_film_peer = nullptr; // staging when peer access is unavailable
     size_t film_floats = 0;
     int sms = 0;
-    int blocks_extend = 0, blocks_connect = 0, blocks_trace = 0;
+    int blocks_extend = 0, blocks_connect = 0, blocks_trace = 0, blocks_wavefront = 0;
+    unsigned int wf_ctas_launched = 0;
     bool rendered = false;
     // per-render bookkeeping
     bool done = true;
@@ -57,7 +59,8 @@ struct frt_ctx
     bool peer_ok = true;
     DevScene host_view{}; // counts + camera; pointers filled per device
     uint32_t nx = 0, ny = 0;
-    unsigned int n_slots = 1u << 20;
+    unsigned int n_slots = 1u << 20; // streamed (global-memory) pool
+    unsigned int wf_slots = 768;     // CTA-resident pool: slots per CTA (multiple of FRT_WF_THREADS)
     int poll_every = 16;
     frt_stats stats{};
 };
@@ -136,6 +139,12 @@ __global__ void k_reset_pool(PathPool pool, Counters *ctr, unsigned long long to
         ctr->n_shadow = 0;
         ctr->extend_next = ctr->connect_next = 0;
     }
+}
+
+__global__ void k_reset_tile(Counters *ctr, unsigned long long total)
+{
+    ctr->next_sample = 0;
+    ctr->total_samples = total;
 }
 
 // Sum the other devices' films into device 0's over NVLink peer loads (one pass, no staging).

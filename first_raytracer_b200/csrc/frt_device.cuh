@@ -33,7 +33,8 @@ struct Counters // one per device, device memory; mirrored to pinned host memory
     unsigned int n_free[2];           // ping-pong free-slot queue lengths
     unsigned int n_shadow;            // shadow queue length of this iteration
     unsigned int extend_next, connect_next, trace_next; // persistent-warp work cursors
-    unsigned int pad;
+    unsigned int wf_iterations;       // CTA-resident wavefront: most iterations any CTA ran
+    unsigned long long stage_ns[4];   // CTA-resident wavefront: generate, extend, shade, connect time summed over CTAs
 };
 
 __device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }

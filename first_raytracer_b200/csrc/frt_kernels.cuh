@@ -63,6 +63,44 @@ __device__ __forceinline__ unsigned int warp_append(bool pred, unsigned int *cou
 // ---------------------------------------------------------------------------------------------
 // generate: path.cpp:129-133 + camera::get_ray camera.h:30-35 + random_in_unit_disk util.h:21-41
 // ---------------------------------------------------------------------------------------------
+// Camera path number `idx` of the tile (sample idx / npix of pixel idx % npix) into slot `slot`.
+__device__ __forceinline__ void frt_generate_path(const KernelArgs &a, const PathPool &pool, const unsigned int slot,
+                                                  const unsigned long long idx)
+{
+    const unsigned int npix = a.tile.w * a.tile.h;
+    const unsigned int s = a.tile.spp_begin + (unsigned int)(idx / npix);
+    const unsigned int pix = (unsigned int)(idx % npix);
+    const unsigned int px = a.tile.x0 + pix % a.tile.w, py = a.tile.y0 + pix / a.tile.w;
+    const unsigned int pixel = py * a.tile.nx + px;
+
+    const float4 r = frt_rng_block(a.tile.seed, pixel, s, 0);
+    const float u = ((float)px + r.x) / (float)a.tile.nx;
+    const float v = ((float)py + r.y) / (float)a.tile.ny;
+    const frt_camera &c = a.sc.cam;
+    float rdx = 0.0f, rdy = 0.0f;
+    if (c.lens_radius != 0.0f)
+    {
+        const float ax = r.z * 2.0f - 1.0f, ay = r.w * 2.0f - 1.0f;
+        if (!(ax == 0.0f && ay == 0.0f))
+        {
+            float phi, rr;
+            if (ax * ax > ay * ay) { rr = ax; phi = (FRT_PI / 4.0f) * (ay / ax); }
+            else { rr = ay; phi = (FRT_PI / 2.0f) - (FRT_PI / 4.0f) * (ax / ay); }
+            rdx = c.lens_radius * rr * cosf(phi);
+            rdy = c.lens_radius * rr * sinf(phi);
+        }
+    }
+    const float3 offset = arr3(c.u) * rdx + arr3(c.v) * rdy;
+    const float3 o = arr3(c.origin) + offset;
+    const float3 d = arr3(c.lower_left_corner) + u * arr3(c.horizontal) + v * arr3(c.vertical) - arr3(c.origin) - offset;
+
+    pool.ray_o[slot] = make_float4(o.x, o.y, o.z, 0.0f);
+    pool.ray_d[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(FRT_FLAG_ALIVE));
+    pool.thr[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(pixel));
+    pool.rad[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(s));
+    pool.prev_p[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+}
+
 __global__ void __launch_bounds__(256) k_generate(const KernelArgs a, const int parity)
 {
     Counters *ctr = a.ctr;
@@ -76,7 +114,6 @@ __global__ void __launch_bounds__(256) k_generate(const KernelArgs a, const int 
         ctr->connect_next = 0;
     }
     const unsigned long long total = ctr->total_samples;
-    const unsigned int npix = a.tile.w * a.tile.h;
     for (unsigned int i = tid; i < ((n_free + 31u) & ~31u); i += gridDim.x * blockDim.x)
     {
         const bool want = i < n_free;
@@ -94,39 +131,7 @@ __global__ void __launch_bounds__(256) k_generate(const KernelArgs a, const int 
             atomicAdd(&ctr->samples_started, (unsigned long long)started);
         }
         if (!start) continue;
-
-        const unsigned int slot = a.pool.free_q[parity][i];
-        const unsigned int s = a.tile.spp_begin + (unsigned int)(idx / npix);
-        const unsigned int pix = (unsigned int)(idx % npix);
-        const unsigned int px = a.tile.x0 + pix % a.tile.w, py = a.tile.y0 + pix / a.tile.w;
-        const unsigned int pixel = py * a.tile.nx + px;
-
-        const float4 r = frt_rng_block(a.tile.seed, pixel, s, 0);
-        const float u = ((float)px + r.x) / (float)a.tile.nx;
-        const float v = ((float)py + r.y) / (float)a.tile.ny;
-        const frt_camera &c = a.sc.cam;
-        float rdx = 0.0f, rdy = 0.0f;
-        if (c.lens_radius != 0.0f)
-        {
-            const float ax = r.z * 2.0f - 1.0f, ay = r.w * 2.0f - 1.0f;
-            if (!(ax == 0.0f && ay == 0.0f))
-            {
-                float phi, rr;
-                if (ax * ax > ay * ay) { rr = ax; phi = (FRT_PI / 4.0f) * (ay / ax); }
-                else { rr = ay; phi = (FRT_PI / 2.0f) - (FRT_PI / 4.0f) * (ax / ay); }
-                rdx = c.lens_radius * rr * cosf(phi);
-                rdy = c.lens_radius * rr * sinf(phi);
-            }
-        }
-        const float3 offset = arr3(c.u) * rdx + arr3(c.v) * rdy;
-        const float3 o = arr3(c.origin) + offset;
-        const float3 d = arr3(c.lower_left_corner) + u * arr3(c.horizontal) + v * arr3(c.vertical) - arr3(c.origin) - offset;
-
-        a.pool.ray_o[slot] = make_float4(o.x, o.y, o.z, 0.0f);
-        a.pool.ray_d[slot] = make_float4(d.x, d.y, d.z, __uint_as_float(FRT_FLAG_ALIVE));
-        a.pool.thr[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(pixel));
-        a.pool.rad[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(s));
-        a.pool.prev_p[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        frt_generate_path(a, a.pool, a.pool.free_q[parity][i], idx);
     }
 }
 

@@ -40,11 +40,6 @@ int ensure_film(frt_ctx *ctx, uint32_t nx, uint32_t ny)
             d.film_floats = n;
             CU(cudaMemsetAsync(d.d_film, 0, n * sizeof(float), d.stream));
         }
-        if (d.pool.n_slots != ctx->n_slots)
-        {
-            int rc = alloc_pool(ctx, d, ctx->n_slots);
-            if (rc != FRT_OK) return rc;
-        }
     }
     ctx->nx = nx; ctx->ny = ny;
     return FRT_OK;
@@ -86,6 +81,7 @@ int frt_clear_film(frt_ctx *ctx)
         if (d.d_film) CU(cudaMemsetAsync(d.d_film, 0, d.film_floats * sizeof(float), d.stream));
         CU(cudaMemsetAsync(d.d_ctr, 0, sizeof(Counters), d.stream));
         d.iterations = d.launches = 0;
+        d.wf_ctas_launched = 0;
         d.rendered = false;
         for (double &m : d.timers.ms) m = 0;
     }
@@ -106,6 +102,8 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
 
     const int nd = (int)ctx->dev.size();
     const uint32_t spp = t->spp_end - t->spp_begin;
+    const bool streamed = ctx->flags & FRT_FLAG_STREAMED_POOL;
+    const bool count = ctx->flags & FRT_FLAG_COUNTERS;
     std::vector<KernelArgs> args(nd);
     for (int i = 0; i < nd; ++i)
     {
@@ -126,13 +124,36 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
         if (d.done) continue;
         if (!d.rendered) CU(cudaEventRecord(d.ev_begin, d.stream));
         d.rendered = true;
+        if (!streamed)
+        {
+            // CTA-resident pool: the whole tile is one persistent launch; nothing to poll
+            const size_t smem = (size_t)ctx->wf_slots * FRT_WF_SLOT_BYTES;
+            // no more CTAs than can be kept busy: one CTA-iteration consumes up to wf_slots samples
+            const unsigned long long want = (total + ctx->wf_slots - 1) / ctx->wf_slots;
+            const unsigned int grid = (unsigned int)std::min<unsigned long long>((unsigned long long)d.blocks_wavefront, want);
+            k_reset_tile<<<1, 1, 0, d.stream>>>(d.d_ctr, total);
+            if (count) k_wavefront<true><<<grid, FRT_WF_THREADS, smem, d.stream>>>(a, ctx->wf_slots);
+            else k_wavefront<false><<<grid, FRT_WF_THREADS, smem, d.stream>>>(a, ctx->wf_slots);
+            CU(cudaGetLastError());
+            CU(cudaEventRecord(d.ev_end, d.stream));
+            d.launches += 2;
+            d.wf_ctas_launched += grid;
+            d.done = true;
+            continue;
+        }
+        if (d.pool.n_slots != ctx->n_slots)
+        {
+            int prc = alloc_pool(ctx, d, ctx->n_slots);
+            if (prc != FRT_OK) return prc;
+            a.pool = d.pool;
+        }
         d.tile_iter = 0; // queue parity restarts with the pool reset
         k_reset_pool<<<(d.pool.n_slots + 255) / 256, 256, 0, d.stream>>>(d.pool, d.d_ctr, total);
         d.launches += 1;
     }
-    // lock-step issue across devices; a device is polled every poll_every iterations
-    const bool count = ctx->flags & FRT_FLAG_COUNTERS;
-    bool all_done = false;
+    // streamed pool: lock-step issue across devices; a device is polled every poll_every iterations
+    bool all_done = true;
+    for (int i = 0; i < nd; ++i) all_done = all_done && ctx->dev[i].done;
     while (!all_done)
     {
         for (int it = 0; it < ctx->poll_every; ++it)
@@ -208,7 +229,7 @@ int frt_readback(frt_ctx *ctx, float *rgb_sum, size_t n_floats, frt_stats *stats
         st.shadow_rays += d.h_ctr->shadow_rays;
         st.node_visits += d.h_ctr->node_visits;
         st.tri_tests += d.h_ctr->tri_tests;
-        st.iterations = std::max<uint64_t>(st.iterations, d.iterations);
+        st.iterations = std::max<uint64_t>(st.iterations, d.iterations + d.h_ctr->wf_iterations);
         st.kernel_launches += d.launches;
         if (d.rendered)
         {
@@ -216,10 +237,11 @@ int frt_readback(frt_ctx *ctx, float *rgb_sum, size_t n_floats, frt_stats *stats
             CU(cudaEventElapsedTime(&ms, d.ev_begin, d.ev_end));
             st.render_ms = std::max<double>(st.render_ms, ms);
         }
-        st.generate_ms = std::max(st.generate_ms, d.timers.ms[0]);
-        st.extend_ms = std::max(st.extend_ms, d.timers.ms[1]);
-        st.shade_ms = std::max(st.shade_ms, d.timers.ms[2]);
-        st.connect_ms = std::max(st.connect_ms, d.timers.ms[3]);
+        const double per_cta = d.wf_ctas_launched ? 1e-6 / d.wf_ctas_launched : 0.0; // ns summed over CTAs -> mean ms
+        st.generate_ms = std::max(st.generate_ms, d.timers.ms[0] + d.h_ctr->stage_ns[0] * per_cta);
+        st.extend_ms = std::max(st.extend_ms, d.timers.ms[1] + d.h_ctr->stage_ns[1] * per_cta);
+        st.shade_ms = std::max(st.shade_ms, d.timers.ms[2] + d.h_ctr->stage_ns[2] * per_cta);
+        st.connect_ms = std::max(st.connect_ms, d.timers.ms[3] + d.h_ctr->stage_ns[3] * per_cta);
     }
     // in-process multi-GPU: device 0 sums its peers' films (P2P loads over NVLink when enabled)
     if (ctx->dev.size() > 1)

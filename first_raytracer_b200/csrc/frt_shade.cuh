@@ -67,8 +67,8 @@ __device__ __forceinline__ float sphere_pdf_direct(float3 c, float radius, float
     return (1.0f / solid_angle) * fabsf(dot(to_light, rec_n)) / d2;
 }
 
-__device__ __forceinline__ void end_path(const KernelArgs &a, unsigned int slot, float3 rad, unsigned int pixel,
-                                         unsigned int &nonfinite)
+__device__ __forceinline__ void end_path(const KernelArgs &a, const PathPool &pool, unsigned int slot, float3 rad,
+                                         unsigned int pixel, unsigned int &nonfinite)
 {
     if (isfinite(rad.x) && isfinite(rad.y) && isfinite(rad.z))
     {
@@ -79,31 +79,34 @@ __device__ __forceinline__ void end_path(const KernelArgs &a, unsigned int slot,
     }
     else
         ++nonfinite;
-    a.pool.ray_d[slot].w = __uint_as_float(0u);
+    pool.ray_d[slot].w = __uint_as_float(0u);
 }
 
-__global__ void __launch_bounds__(128) k_shade(const KernelArgs a, const int parity_out)
+// One path vertex of slot `slot` of `pool` (global memory for the streamed pool, shared memory for
+// the CTA-resident pool): bit 0 of the result = the path ended here (splatted, slot dead), bit 1 =
+// a shadow ray was written to sh_a / sh_b / sh_c.  A dead slot returns 0.
+#define FRT_SHADE_TERMINATED 1u
+#define FRT_SHADE_SHADOW 2u
+#define FRT_SHADE_WAS_ALIVE 4u
+__device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, const PathPool &pool, const unsigned int slot,
+                                                         unsigned int &nonfinite)
 {
-    const unsigned int n = a.pool.n_slots;
-    unsigned int nonfinite = 0;
-    int ended = 0;
-    const unsigned int n_round = (n + 31u) & ~31u;
-    for (unsigned int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_round; slot += gridDim.x * blockDim.x)
-    {
         bool terminated = false, want_shadow = false;
-        float4 dw = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (slot < n) dw = a.pool.ray_d[slot];
+        const float4 dw = pool.ray_d[slot];
         const unsigned int flags = __float_as_uint(dw.w);
         if (flags & FRT_FLAG_ALIVE)
         {
-            const float4 ow = a.pool.ray_o[slot];
-            const float4 hw = a.pool.hit[slot];
-            float4 tw = a.pool.thr[slot];
-            float4 rw = a.pool.rad[slot];
+            const float4 ow = pool.ray_o[slot];
+            float4 hw = pool.hit[slot];
+            float4 tw = pool.thr[slot];
+            float4 rw = pool.rad[slot];
             const float3 o = f3(ow), d = f3(dw);
             const float prev_pdf = ow.w;
             const unsigned int depth = flags >> FRT_DEPTH_SHIFT;
-            const unsigned int prim = __float_as_uint(hw.w);
+            unsigned int prim = __float_as_uint(hw.w);
+            // a winner taken on its float32 interval gets the reference's float64 t, u, v here, where the
+            // warp is converged (the CTA-resident wavefront defers it out of the divergent traversal)
+            if (prim != 0xFFFFFFFFu && (prim & FRT_HIT_INEXACT)) frt_resolve_hit(a.sc, o, d, hw.x, hw.y, hw.z, prim);
             const unsigned int pixel = __float_as_uint(tw.w), sample = __float_as_uint(rw.w);
             float3 thr = f3(tw), rad = f3(rw);
 
@@ -111,7 +114,7 @@ __global__ void __launch_bounds__(128) k_shade(const KernelArgs a, const int par
             {
                 // path.cpp:115 — constant environment (material.h:219-232 over constant_texture)
                 rad = rad + thr * arr3(a.sc.env);
-                end_path(a, slot, rad, pixel, nonfinite);
+                end_path(a, pool, slot, rad, pixel, nonfinite);
                 terminated = true;
             }
             else
@@ -166,7 +169,7 @@ __global__ void __launch_bounds__(128) k_shade(const KernelArgs a, const int par
                     else
                     {
                         const float cos_wo = dot(h.n, -unit_vector(d));
-                        const float3 dp = h.p - f3(a.pool.prev_p[slot]);
+                        const float3 dp = h.p - f3(pool.prev_p[slot]);
                         float dist2 = dot(dp, dp);
                         if (dist2 <= FRT_EPSILON) dist2 = FRT_EPSILON;
                         float pdf_area;
@@ -177,7 +180,7 @@ __global__ void __launch_bounds__(128) k_shade(const KernelArgs a, const int par
                         const float light_pdf = pdf_area * dist2 / fabsf(cos_wo);
                         rad = rad + thr * Le * mi_weight(prev_pdf, light_pdf);
                     }
-                    end_path(a, slot, rad, pixel, nonfinite);
+                    end_path(a, pool, slot, rad, pixel, nonfinite);
                     terminated = true;
                 }
                 else if (depth < a.tile.max_depth && mtype != FRT_MAT_DIFFUSE_LIGHT)
@@ -214,7 +217,7 @@ __global__ void __launch_bounds__(128) k_shade(const KernelArgs a, const int par
 
                     if (pdf == 0.0f)
                     {
-                        end_path(a, slot, rad, pixel, nonfinite);
+                        end_path(a, pool, slot, rad, pixel, nonfinite);
                         terminated = true;
                     }
                     else
@@ -253,9 +256,9 @@ __global__ void __launch_bounds__(128) k_shade(const KernelArgs a, const int par
                             if (nonzero(contrib) || !(isfinite(contrib.x) && isfinite(contrib.y) && isfinite(contrib.z)))
                             {
                                 want_shadow = true;
-                                a.pool.sh_a[slot] = make_float4(so.x, so.y, so.z, ls.to_light.x);
-                                a.pool.sh_b[slot] = make_float4(ls.to_light.y, ls.to_light.z, contrib.x, contrib.y);
-                                a.pool.sh_c[slot] = contrib.z;
+                                pool.sh_a[slot] = make_float4(so.x, so.y, so.z, ls.to_light.x);
+                                pool.sh_b[slot] = make_float4(ls.to_light.y, ls.to_light.z, contrib.x, contrib.y);
+                                pool.sh_c[slot] = contrib.z;
                             }
                         }
                         // ---- continue the path: L = Le + f * Li(next) [* cos] / pdf ----
@@ -263,20 +266,34 @@ __global__ void __launch_bounds__(128) k_shade(const KernelArgs a, const int par
                         unsigned int nf = FRT_FLAG_ALIVE | ((depth + 1) << FRT_DEPTH_SHIFT);
                         if (mtype == FRT_MAT_PHONG || mtype == FRT_MAT_METAL || mtype == FRT_MAT_DIELECTRIC)
                             nf |= FRT_FLAG_PREV_UNWEIGHTED;
-                        a.pool.ray_o[slot] = make_float4(next_o.x, next_o.y, next_o.z, pdf);
-                        a.pool.ray_d[slot] = make_float4(next_d.x, next_d.y, next_d.z, __uint_as_float(nf));
-                        a.pool.thr[slot] = make_float4(thr.x, thr.y, thr.z, tw.w);
-                        a.pool.prev_p[slot] = make_float4(h.p.x, h.p.y, h.p.z, 0.0f);
+                        pool.ray_o[slot] = make_float4(next_o.x, next_o.y, next_o.z, pdf);
+                        pool.ray_d[slot] = make_float4(next_d.x, next_d.y, next_d.z, __uint_as_float(nf));
+                        pool.thr[slot] = make_float4(thr.x, thr.y, thr.z, tw.w);
+                        pool.prev_p[slot] = make_float4(h.p.x, h.p.y, h.p.z, 0.0f);
                     }
                 }
                 else
                 {
                     // path.cpp:112 — depth cap reached, or the back of a light: returns Le == 0
-                    end_path(a, slot, rad, pixel, nonfinite);
+                    end_path(a, pool, slot, rad, pixel, nonfinite);
                     terminated = true;
                 }
             }
         }
+        return (terminated ? FRT_SHADE_TERMINATED : 0u) | (want_shadow ? FRT_SHADE_SHADOW : 0u) |
+               ((flags & FRT_FLAG_ALIVE) ? FRT_SHADE_WAS_ALIVE : 0u);
+}
+
+__global__ void __launch_bounds__(128) k_shade(const KernelArgs a, const int parity_out)
+{
+    const unsigned int n = a.pool.n_slots;
+    unsigned int nonfinite = 0;
+    int ended = 0;
+    const unsigned int n_round = (n + 31u) & ~31u;
+    for (unsigned int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_round; slot += gridDim.x * blockDim.x)
+    {
+        const unsigned int r = slot < n ? frt_shade_vertex(a, a.pool, slot, nonfinite) : 0u;
+        const bool terminated = r & FRT_SHADE_TERMINATED, want_shadow = r & FRT_SHADE_SHADOW;
         // queue compaction: warp ballot + one atomic per warp per queue
         const unsigned int qi = warp_append(want_shadow, &a.ctr->n_shadow);
         if (want_shadow) a.pool.shadow_q[qi] = slot;

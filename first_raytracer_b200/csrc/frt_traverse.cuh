@@ -17,6 +17,9 @@
 #include "frt_device.cuh"
 
 #define FRT_STACK_SIZE 64
+// Closest hit whose t, u, v are still the float32 estimate carries this bit in RayHit::prim; the
+// consumer (shade, with the whole warp converged) calls frt_resolve_hit before using them.
+#define FRT_HIT_INEXACT 0x20000000u
 
 struct RayHit
 {
@@ -33,6 +36,12 @@ __device__ __forceinline__ uint32_t frt_pick(const uint4 &c, uint32_t i)
 // t < 0 means "no hit" (hits have t > t_min > 0); the caller applies the upper bound.  Kept out of
 // line: it runs off the fast path (ambiguous candidates) and once per ray for the winner.
 struct ExactHit { double t; float u, v; };
+// parallel_bvh.h:46-51 (the caller passed EPSILON): t_min = max(1e-4, 1e-4 * max(|o.x|, |o.y|, |o.z|))
+__device__ __forceinline__ double frt_tmin_exact(const float3 o)
+{
+    const double m = fmax(fmax(fabs((double)o.x), fabs((double)o.y)), fmax(fabs((double)o.z), 1e-4));
+    return fmax(1e-4, 1e-4 * m);
+}
 __device__ __noinline__ ExactHit frt_tri_exact(const float4 *tris, uint32_t prim, float ox, float oy, float oz, float dxf,
                                                float dyf, float dzf, double tmin)
 {
@@ -74,33 +83,48 @@ struct BestHit
     bool exact;
 };
 
+// One ray's traversal state.  begin() sets the ray up, round() runs ONE while-while round (descend
+// to a leaf, test its primitives, pop the next postponed child), finish() gives the hit.  Splitting
+// the loop this way lets a persistent warp look at its lanes between rounds and hand finished
+// lanes a new ray (dynamic fetch) instead of idling until the slowest lane is done.
 template <bool ANY, bool COUNT>
-__device__ __forceinline__ RayHit frt_traverse(const DevScene &sc, const float3 o, const float3 d, float /*unused*/,
-                                               unsigned int &n_nodes, unsigned int &n_tris)
+struct Walker
 {
-    RayHit out;
-    out.t = 0.f; out.u = 0.f; out.v = 0.f; out.prim = 0xFFFFFFFFu;
-    if (sc.n_nodes == 0) return out;
-
-    // parallel_bvh.h:46-51 in float64; path.cpp:10 passes FLT_MAX, path.cpp:50 passes 1 - SHADOW_EPSILON
-    const double m = fmax(fmax(fabs((double)o.x), fabs((double)o.y)), fmax(fabs((double)o.z), 1e-4));
-    const double tmin_d = fmax(1e-4, 1e-4 * m);
-    const double tend_d = ANY ? 1.0 - (double)FRT_SHADOW_EPSILON : (double)FRT_FLT_MAX;
-    const float tmin = __double2float_rd(tmin_d), tmin_hi = __double2float_ru(tmin_d); // conservative float32 bounds
+    float3 o, d;
+    float idx, idy, idz, oox, ooy, ooz;
+    int sx, sy, sz;
+    float tmin, tmin_hi, tmax;
     BestHit best;
-    best.prim = 0xFFFFFFFFu; best.u = best.v = 0.f; best.t = tend_d; best.exact = true;
-    best.lo = __double2float_rd(tend_d); best.hi = __double2float_ru(tend_d);
-    float tmax = best.hi; // culling bound
-    const float idx = 1.0f / d.x, idy = 1.0f / d.y, idz = 1.0f / d.z;
-    const float oox = o.x * idx, ooy = o.y * idy, ooz = o.z * idz;
-    const int sx = idx < 0.0f ? 1 : 0, sy = idy < 0.0f ? 1 : 0, sz = idz < 0.0f ? 1 : 0;
-
+    uint32_t cur;
+    int sp;
+    bool active;
     uint32_t stack[FRT_STACK_SIZE]; // child reference
     float stack_t[FRT_STACK_SIZE];  // its entry distance, to drop it at pop time once something closer was found
-    int sp = 0;
-    uint32_t cur = 0;
 
-    while (true)
+    __device__ __forceinline__ double tend_d() const { return ANY ? 1.0 - (double)FRT_SHADOW_EPSILON : (double)FRT_FLT_MAX; }
+    __device__ __forceinline__ double tmin_exact() const { return frt_tmin_exact(o); }
+
+    __device__ __forceinline__ void begin(const DevScene &sc, const float3 o_, const float3 d_)
+    {
+        o = o_; d = d_;
+        // parallel_bvh.h:46-51: t_min = max(1e-4, 1e-4 * max|o_i|) in double.  The traversal keeps float32
+        // brackets of it (1e-4f < 1e-4 < next float; products rounded outwards); the double itself is
+        // formed only where a decision is made in float64 (tmin_exact()).
+        const float m = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
+        tmin = fmaxf(9.99999974737875e-05f, __fmul_rd(9.99999974737875e-05f, m));
+        tmin_hi = fmaxf(1.00000004749745e-04f, __fmul_ru(1.00000004749745e-04f, m));
+        best.prim = 0xFFFFFFFFu; best.u = best.v = 0.f; best.t = tend_d(); best.exact = true;
+        best.lo = __double2float_rd(tend_d()); best.hi = __double2float_ru(tend_d());
+        tmax = best.hi; // culling bound
+        idx = 1.0f / d.x; idy = 1.0f / d.y; idz = 1.0f / d.z;
+        oox = o.x * idx; ooy = o.y * idy; ooz = o.z * idz;
+        sx = idx < 0.0f ? 1 : 0; sy = idy < 0.0f ? 1 : 0; sz = idz < 0.0f ? 1 : 0;
+        sp = 0;
+        cur = 0;
+        active = sc.n_nodes != 0;
+    }
+
+    __device__ __forceinline__ void round(const DevScene &sc, unsigned int &n_nodes, unsigned int &n_tris)
     {
         // ---- while-while, part 1: descend through inner nodes (EMPTY carries the leaf bit and ends the loop)
         while (!(cur & FRT_CHILD_LEAF))
@@ -160,8 +184,9 @@ __device__ __forceinline__ RayHit frt_traverse(const DevScene &sc, const float3 
                     if (!(disc >= 0.0)) continue;
                     disc = sqrt(disc);
                     double t = (-b - disc) / a;
+                    const double tmin_d = tmin_exact();
                     if (t < tmin_d) t = (-b + disc) / a;
-                    if (t < tmin_d || t > tend_d) continue;
+                    if (t < tmin_d || t > tend_d()) continue;
                     e.t = t; e.u = 0.f; e.v = 0.f;
                 }
                 else
@@ -192,25 +217,25 @@ __device__ __forceinline__ RayHit frt_traverse(const DevScene &sc, const float3 
                         if (uf > du && vf > dv && uf + vf < 1.0f - du - dv && tf - dt > tmin_hi && tf + dt < best.lo)
                         {
                             // certainly a hit and certainly the closest so far
-                            if (ANY) { out.t = tf; out.prim = prim; return out; }
                             best.prim = prim; best.lo = tf - dt; best.hi = tf + dt; best.u = uf; best.v = vf; best.exact = false;
                             tmax = best.hi;
+                            if (ANY) { active = false; return; }
                             continue;
                         }
                     }
-                    e = frt_tri_exact(sc.tris, prim, o.x, o.y, o.z, d.x, d.y, d.z, tmin_d);
+                    e = frt_tri_exact(sc.tris, prim, o.x, o.y, o.z, d.x, d.y, d.z, tmin_exact());
                     if (e.t < 0.0) continue;
                 }
                 // float64 decision: strict t < t_max for triangles (triangle.h:88-89), t <= t_max for spheres
                 // (sphere.h:41); at an exact tie the triangle the reference meets first (lower index) stays
                 if (ANY)
                 {
-                    if (is_sphere || e.t < tend_d) { out.t = (float)e.t; out.prim = prim; return out; }
+                    if (is_sphere || e.t < tend_d()) { best.prim = prim; best.t = e.t; best.exact = true; active = false; return; }
                     continue;
                 }
                 if (!best.exact) // the closest so far was taken on its float32 interval: pin it down now
                 {
-                    const ExactHit b = frt_tri_exact(sc.tris, best.prim, o.x, o.y, o.z, d.x, d.y, d.z, tmin_d);
+                    const ExactHit b = frt_tri_exact(sc.tris, best.prim, o.x, o.y, o.z, d.x, d.y, d.z, tmin_exact());
                     if (b.t >= 0.0) { best.t = b.t; best.u = b.u; best.v = b.v; }
                     else best.t = 0.5 * ((double)best.lo + (double)best.hi); // not reachable while the margins hold
                     best.exact = true;
@@ -226,24 +251,58 @@ __device__ __forceinline__ RayHit frt_traverse(const DevScene &sc, const float3 
         }
 
         // ---- pop the nearest postponed child that can still hold something closer
-        bool more = false;
+        active = false;
         while (sp > 0)
         {
             --sp;
-            if (stack_t[sp] <= tmax) { cur = stack[sp]; more = true; break; }
+            if (stack_t[sp] <= tmax) { cur = stack[sp]; active = true; break; }
         }
-        if (!more) break;
     }
 
-    if (best.prim != 0xFFFFFFFFu)
+    // t, u, v of the winner: one float64 evaluation per ray, outside the loop (closest hit only;
+    // an any-hit query reports just the occluder's index)
+    __device__ __forceinline__ RayHit finish(const DevScene &sc)
     {
-        if (!best.exact) // one float64 evaluation per ray, outside the loop: t, u, v of the winner
+        RayHit out;
+        out.t = 0.f; out.u = 0.f; out.v = 0.f; out.prim = best.prim;
+        if (best.prim == 0xFFFFFFFFu) return out;
+        if (ANY) { out.t = best.exact ? (float)best.t : 0.5f * (best.lo + best.hi); return out; }
+        if (!best.exact)
         {
-            const ExactHit b = frt_tri_exact(sc.tris, best.prim, o.x, o.y, o.z, d.x, d.y, d.z, tmin_d);
+            const ExactHit b = frt_tri_exact(sc.tris, best.prim, o.x, o.y, o.z, d.x, d.y, d.z, tmin_exact());
             if (b.t >= 0.0) { best.t = b.t; best.u = b.u; best.v = b.v; }
             else best.t = 0.5 * ((double)best.lo + (double)best.hi);
         }
-        out.t = (float)best.t; out.u = best.u; out.v = best.v; out.prim = best.prim;
+        out.t = (float)best.t; out.u = best.u; out.v = best.v;
+        return out;
     }
-    return out;
+
+    // The same without the float64 evaluation: an inexact winner is flagged for frt_resolve_hit.
+    __device__ __forceinline__ RayHit finish_lazy() const
+    {
+        RayHit out;
+        out.prim = best.prim;
+        if (best.prim == 0xFFFFFFFFu || best.exact) { out.t = (float)best.t; out.u = best.u; out.v = best.v; return out; }
+        out.t = 0.5f * (best.lo + best.hi); out.u = best.u; out.v = best.v;
+        out.prim = best.prim | FRT_HIT_INEXACT;
+        return out;
+    }
+};
+
+__device__ __forceinline__ void frt_resolve_hit(const DevScene &sc, const float3 o, const float3 d, float &t, float &u, float &v,
+                                                uint32_t &prim)
+{
+    prim &= ~FRT_HIT_INEXACT;
+    const ExactHit b = frt_tri_exact(sc.tris, prim, o.x, o.y, o.z, d.x, d.y, d.z, frt_tmin_exact(o));
+    if (b.t >= 0.0) { t = (float)b.t; u = b.u; v = b.v; }
+}
+
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ RayHit frt_traverse(const DevScene &sc, const float3 o, const float3 d, float /*unused*/,
+                                               unsigned int &n_nodes, unsigned int &n_tris)
+{
+    Walker<ANY, COUNT> w;
+    w.begin(sc, o, d);
+    while (w.active) w.round(sc, n_nodes, n_tris);
+    return w.finish(sc);
 }

@@ -1,0 +1,237 @@
+// CTA-resident wavefront: the whole generate → extend → shade → connect pipeline of one tile in ONE
+// persistent kernel.  Every CTA owns a private pool of P path slots that lives in SHARED MEMORY for
+// the whole render (144 B per slot: 8 float4 SoA arrays + shadow contribution + three queues), so
+// path state never touches HBM; the only global traffic is scene fetches (L1/L2 resident for the
+// reference's scenes), one sample-counter atomic per CTA iteration and the film splats.
+//
+//   generate : one global atomic hands the CTA a run of consecutive camera samples for the slots
+//              the last shade stage freed (path.cpp:129-133, camera.h:30-35)
+//   trace    : persistent warps pull rays from the CTA's extension queue, then from its shadow
+//              queue (smem cursors), one ray per lane; a lane whose ray finishes takes the next
+//              queue entry as soon as enough lanes of its warp are idle (dynamic fetch), so a warp
+//              is not held by its slowest ray (path.cpp:10 and :50)
+//   shade    : everything path::Li does at a vertex (path.cpp:11-115); continuing / ended /
+//              shadow-casting slots are compacted into the three queues by warp ballot + one
+//              shared-memory atomic per warp
+// CTAs run unsynchronised: while one is in its (latency-bound) shade stage its SM neighbour is
+// usually in its (issue-bound) trace stage.
+#pragma once
+#include "frt_shade.cuh"
+
+#define FRT_WF_THREADS 256
+#define FRT_WF_MIN_BLOCKS 2
+#define FRT_WF_SLOT_BYTES 144u
+#ifndef FRT_WF_REFILL_BELOW
+#define FRT_WF_REFILL_BELOW 24 // fetch new rays once this many lanes or fewer are still traversing
+#endif
+
+struct WfShared
+{
+    unsigned long long base; // first sample index of this iteration's run
+    unsigned int n_ext, n_free, n_shadow, n_new, cur_ext, cur_shadow, exhausted, pad;
+};
+
+__device__ __forceinline__ unsigned long long frt_globaltimer()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// Persistent-warp ray casting over one shared-memory queue of slot indices.
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ void wf_trace_queue(const DevScene &sc, const PathPool &lp, const unsigned int *q,
+                                               const unsigned int n_items, unsigned int *cursor, unsigned int &n_rays,
+                                               unsigned int &n_nodes, unsigned int &n_tris)
+{
+    if (n_items == 0) return;
+    const unsigned int lane = lane_id();
+    Walker<ANY, COUNT> w;
+    w.active = false;
+    bool pending = false, more = true;
+    unsigned int slot = 0;
+    while (true)
+    {
+        if (more)
+        {
+            // hand every idle lane the next queue entry: one shared-memory atomic per warp
+            const unsigned int idle = __ballot_sync(0xFFFFFFFFu, !w.active);
+            unsigned int base = 0;
+            if (lane == 0) base = atomicAdd(cursor, (unsigned int)__popc(idle));
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            const unsigned int my = base + __popc(idle & ((1u << lane) - 1u));
+            if (!w.active && my < n_items)
+            {
+                slot = q[my];
+                float3 o, d;
+                if (ANY)
+                {
+                    const float4 sa = lp.sh_a[slot], sb = lp.sh_b[slot];
+                    o = f3(sa); d = f3(sa.w, sb.x, sb.y);
+                }
+                else
+                {
+                    o = f3(lp.ray_o[slot]); d = f3(lp.ray_d[slot]);
+                }
+                w.begin(sc, o, d);
+                pending = true;
+                ++n_rays;
+            }
+            more = base + __popc(idle) < n_items;
+        }
+        unsigned int act = __ballot_sync(0xFFFFFFFFu, w.active);
+        while (act)
+        {
+            if (w.active) w.round(sc, n_nodes, n_tris);
+            act = __ballot_sync(0xFFFFFFFFu, w.active);
+            if (more && __popc(act) <= FRT_WF_REFILL_BELOW) break;
+        }
+        if (pending && !w.active)
+        {
+            if (ANY)
+            {
+                // path.cpp:73 — the contribution shade computed is committed when nothing is in the way
+                if (w.best.prim == 0xFFFFFFFFu)
+                {
+                    const float4 sb = lp.sh_b[slot];
+                    float4 r = lp.rad[slot];
+                    r.x += sb.z; r.y += sb.w; r.z += lp.sh_c[slot];
+                    lp.rad[slot] = r;
+                }
+            }
+            else
+            {
+                const RayHit h = w.finish_lazy();
+                lp.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
+            }
+            pending = false;
+        }
+        if (!more && act == 0) break;
+    }
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(FRT_WF_THREADS, FRT_WF_MIN_BLOCKS) k_wavefront(const KernelArgs a, const unsigned int P)
+{
+    extern __shared__ float4 wf_smem[];
+    __shared__ WfShared sh;
+    PathPool lp;
+    lp.n_slots = P;
+    lp.ray_o = wf_smem; lp.ray_d = lp.ray_o + P; lp.hit = lp.ray_d + P; lp.thr = lp.hit + P; lp.rad = lp.thr + P;
+    lp.prev_p = lp.rad + P; lp.sh_a = lp.prev_p + P; lp.sh_b = lp.sh_a + P;
+    lp.sh_c = reinterpret_cast<float *>(lp.sh_b + P);
+    unsigned int *ext_q = reinterpret_cast<unsigned int *>(lp.sh_c + P), *free_q = ext_q + P, *shadow_q = free_q + P;
+    lp.free_q[0] = free_q; lp.free_q[1] = free_q; lp.shadow_q = shadow_q;
+
+    const unsigned int tid = threadIdx.x;
+    for (unsigned int i = tid; i < P; i += FRT_WF_THREADS)
+    {
+        lp.ray_d[i] = make_float4(0.f, 0.f, 0.f, 0.f); // dead
+        free_q[i] = i;
+    }
+    if (tid == 0)
+    {
+        sh.n_ext = 0; sh.n_free = P; sh.n_shadow = 0; sh.n_new = 0; sh.exhausted = 0;
+    }
+    __syncthreads();
+
+    const unsigned long long total = a.ctr->total_samples;
+    unsigned int n_closest = 0, n_shadow_rays = 0, n_nodes = 0, n_tris = 0, nonfinite = 0, n_started = 0, n_iter = 0;
+    unsigned long long t_gen = 0, t_ext = 0, t_con = 0, t_shade = 0, t0 = 0;
+    if (tid == 0) t0 = frt_globaltimer();
+
+    while (true)
+    {
+        // ---- generate -------------------------------------------------------------------------
+        if (tid == 0)
+        {
+            const unsigned int want = sh.n_free;
+            unsigned long long base = total;
+            if (want && !sh.exhausted)
+            {
+                base = atomicAdd(&a.ctr->next_sample, (unsigned long long)want);
+                if (base + want >= total) sh.exhausted = 1;
+            }
+            sh.base = base;
+            sh.n_new = base < total ? (unsigned int)min((unsigned long long)want, total - base) : 0u;
+            sh.cur_ext = 0; sh.cur_shadow = 0;
+        }
+        __syncthreads();
+        const unsigned int n_new = sh.n_new, n_bounce = sh.n_ext, n_sh = sh.n_shadow;
+        const unsigned long long base = sh.base;
+        for (unsigned int i = tid; i < n_new; i += FRT_WF_THREADS)
+        {
+            const unsigned int slot = free_q[i];
+            frt_generate_path(a, lp, slot, base + i);
+            ext_q[n_bounce + i] = slot; // bounce rays first (the long ones), camera rays after them
+            ++n_started;
+        }
+        const unsigned int n_ext = n_bounce + n_new;
+        if (n_ext == 0) break; // nothing in flight and no samples left: this CTA is done
+        __syncthreads();
+        if (tid == 0) { const unsigned long long t = frt_globaltimer(); t_gen += t - t0; t0 = t; }
+
+        // ---- extend + connect -----------------------------------------------------------------
+        wf_trace_queue<false, COUNT>(a.sc, lp, ext_q, n_ext, &sh.cur_ext, n_closest, n_nodes, n_tris);
+        if (tid == 0) { const unsigned long long t = frt_globaltimer(); t_ext += t - t0; t0 = t; }
+        wf_trace_queue<true, COUNT>(a.sc, lp, shadow_q, n_sh, &sh.cur_shadow, n_shadow_rays, n_nodes, n_tris);
+        __syncthreads();
+        if (tid == 0)
+        {
+            sh.n_ext = 0; sh.n_free = 0; sh.n_shadow = 0;
+            const unsigned long long t = frt_globaltimer(); t_con += t - t0; t0 = t;
+        }
+        __syncthreads();
+
+        // ---- shade + queue compaction -----------------------------------------------------------
+        for (unsigned int s0 = 0; s0 < P; s0 += FRT_WF_THREADS)
+        {
+            const unsigned int slot = s0 + tid; // P is a multiple of the CTA size
+            const unsigned int r = frt_shade_vertex(a, lp, slot, nonfinite);
+            const bool ended = r & FRT_SHADE_TERMINATED, goes_on = (r & FRT_SHADE_WAS_ALIVE) && !ended;
+            const unsigned int ei = warp_append(goes_on, &sh.n_ext);
+            if (goes_on) ext_q[ei] = slot;
+            const unsigned int fi = warp_append(ended, &sh.n_free);
+            if (ended) free_q[fi] = slot;
+            const unsigned int si = warp_append(r & FRT_SHADE_SHADOW, &sh.n_shadow);
+            if (r & FRT_SHADE_SHADOW) shadow_q[si] = slot;
+        }
+        __syncthreads();
+        if (tid == 0) { const unsigned long long t = frt_globaltimer(); t_shade += t - t0; t0 = t; }
+        ++n_iter;
+    }
+
+    // ---- statistics: one set of atomics per warp ------------------------------------------------
+    for (int off = 16; off > 0; off >>= 1)
+    {
+        n_closest += __shfl_down_sync(0xFFFFFFFFu, n_closest, off);
+        n_shadow_rays += __shfl_down_sync(0xFFFFFFFFu, n_shadow_rays, off);
+        n_started += __shfl_down_sync(0xFFFFFFFFu, n_started, off);
+        nonfinite += __shfl_down_sync(0xFFFFFFFFu, nonfinite, off);
+        if (COUNT)
+        {
+            n_nodes += __shfl_down_sync(0xFFFFFFFFu, n_nodes, off);
+            n_tris += __shfl_down_sync(0xFFFFFFFFu, n_tris, off);
+        }
+    }
+    if (lane_id() == 0)
+    {
+        if (n_closest) atomicAdd(&a.ctr->closest_rays, (unsigned long long)n_closest);
+        if (n_shadow_rays) atomicAdd(&a.ctr->shadow_rays, (unsigned long long)n_shadow_rays);
+        if (n_started) atomicAdd(&a.ctr->samples_started, (unsigned long long)n_started);
+        if (nonfinite) atomicAdd(&a.ctr->nonfinite, (unsigned long long)nonfinite);
+        if (COUNT)
+        {
+            atomicAdd(&a.ctr->node_visits, (unsigned long long)n_nodes);
+            atomicAdd(&a.ctr->tri_tests, (unsigned long long)n_tris);
+        }
+    }
+    if (tid == 0)
+    {
+        atomicAdd(&a.ctr->stage_ns[0], t_gen);
+        atomicAdd(&a.ctr->stage_ns[1], t_ext);
+        atomicAdd(&a.ctr->stage_ns[2], t_shade);
+        atomicAdd(&a.ctr->stage_ns[3], t_con);
+        atomicMax(&a.ctr->wf_iterations, n_iter);
+    }
+}

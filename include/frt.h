@@ -144,7 +144,8 @@ typedef struct frt_stats {
     uint64_t iterations;     /* wavefront iterations */
     uint64_t kernel_launches;
     double render_ms;        /* device time between first and last kernel, max over devices */
-    double extend_ms, shade_ms, connect_ms, generate_ms; /* only with FRT_FLAG_KERNEL_TIMERS */
+    double extend_ms, shade_ms, connect_ms, generate_ms; /* per stage: mean over CTAs (CTA-resident pool), or
+                                                            CUDA events with FRT_FLAG_KERNEL_TIMERS (streamed pool) */
 } frt_stats;
 
 typedef struct frt_ray { float ox, oy, oz, dx, dy, dz; } frt_ray; /* ray.h:6-17, d not normalised */
@@ -154,7 +155,10 @@ typedef struct frt_hit {
 } frt_hit;
 
 #define FRT_FLAG_COUNTERS 1u      /* count node visits / triangle tests (slower) */
-#define FRT_FLAG_KERNEL_TIMERS 2u /* per-kernel CUDA-event timing (serialises the loop) */
+#define FRT_FLAG_KERNEL_TIMERS 2u /* streamed pool only: per-kernel CUDA-event timing (serialises the loop) */
+#define FRT_FLAG_STREAMED_POOL 4u /* path state in a global-memory pool, four kernels per wavefront iteration
+                                     (the first implementation, kept for A/B measurements); default is the
+                                     CTA-resident pool: one persistent kernel, path state in shared memory */
 
 /* Create a context on `n` CUDA devices (ordinals in `devices`, NULL = device 0..n-1). */
 FRT_API int frt_create(frt_ctx **out, const int *devices, int n);
