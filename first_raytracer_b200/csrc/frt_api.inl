@@ -32,8 +32,9 @@ int frt_create(frt_ctx **out, const int *devices, int n)
     c->dev.resize(n);
     if (const char *s = getenv("FRT_POOL_SLOTS")) c->n_slots = (unsigned int)std::max(1024ll, atoll(s));
     if (const char *s = getenv("FRT_POLL_EVERY")) c->poll_every = std::max(1, atoi(s));
-    if (const char *s = getenv("FRT_WF_SLOTS"))
-        c->wf_slots = (unsigned int)std::min(1536, std::max(FRT_WF_THREADS, atoi(s) / FRT_WF_THREADS * FRT_WF_THREADS));
+    if (const char *s = getenv("FRT_WF_SLOTS")) c->wf_slots = (unsigned int)std::min(1568, std::max(32, atoi(s) / 32 * 32));
+    if (const char *s = getenv("FRT_WF_CONFIG")) c->wf_config = std::min(n_wf_configs - 1, std::max(0, atoi(s)));
+    if (const char *s = getenv("FRT_WF_REFILL")) c->wf_refill = std::min(31, std::max(0, atoi(s)));
     for (int i = 0; i < n; ++i)
     {
         Device &d = c->dev[i];
@@ -63,9 +64,10 @@ int frt_create(frt_ctx **out, const int *devices, int n)
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<false, false>, 128, 0));
         d.blocks_trace = std::max(1, per_sm) * d.sms;
         const size_t wf_smem = (size_t)c->wf_slots * FRT_WF_SLOT_BYTES;
-        CU(cudaFuncSetAttribute(k_wavefront<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
-        CU(cudaFuncSetAttribute(k_wavefront<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wavefront<false>, FRT_WF_THREADS, wf_smem));
+        const WfConfig &wc = wf_configs[c->wf_config];
+        CU(cudaFuncSetAttribute(wc.plain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
+        CU(cudaFuncSetAttribute(wc.counting, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wc.plain, wc.threads, wf_smem));
         if (per_sm < 1)
         {
             delete c;
@@ -118,11 +120,19 @@ static int validate_scene(frt_ctx *ctx, const frt_scene_desc *s)
     if (s->n_tris > FRT_LEAF_FIRST_MASK || s->n_spheres > FRT_LEAF_FIRST_MASK)
         return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: too many primitives");
     if ((s->n_tris || s->n_spheres) && s->n_nodes == 0) return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: primitives without nodes");
+    std::vector<uint8_t> level(s->n_nodes, 1); // inner levels above and including node i (children follow parents)
     for (uint32_t i = 0; i < s->n_nodes; ++i)
         for (int k = 0; k < 4; ++k)
         {
             const uint32_t c = s->nodes[i].child[k];
             if (c == FRT_CHILD_EMPTY) continue;
+            if (!(c & FRT_CHILD_LEAF) && c < s->n_nodes && c > i)
+            {
+                // the traversal pushes at most three children per inner level on a FRT_STACK_SIZE-entry stack
+                if (3u * (level[i] + 1u) > FRT_STACK_SIZE)
+                    return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: tree deeper than %d inner levels", FRT_STACK_SIZE / 3);
+                level[c] = std::max<uint8_t>(level[c], (uint8_t)(level[i] + 1));
+            }
             if (c & FRT_CHILD_LEAF)
             {
                 const uint32_t first = c & FRT_LEAF_FIRST_MASK, count = ((c >> FRT_LEAF_COUNT_SHIFT) & 15u) + 1u;

@@ -60,7 +60,9 @@ struct frt_ctx
     DevScene host_view{}; // counts + camera; pointers filled per device
     uint32_t nx = 0, ny = 0;
     unsigned int n_slots = 1u << 20; // streamed (global-memory) pool
-    unsigned int wf_slots = 768;     // CTA-resident pool: slots per CTA (multiple of FRT_WF_THREADS)
+    unsigned int wf_slots = 512;     // CTA-resident pool: slots per CTA (multiple of 32)
+    int wf_config = 0;               // index into wf_configs[]
+    int wf_refill = 24;              // dynamic fetch threshold (lanes still traversing)
     int poll_every = 16;
     frt_stats stats{};
 };
@@ -199,6 +201,19 @@ __global__ void __launch_bounds__(128) k_trace(DevScene sc, Counters *ctr, const
         }
     }
 }
+
+// Launch shapes of k_wavefront compiled into the library (threads per CTA, CTAs per SM the register
+// budget is cut for); FRT_WF_CONFIG picks one, the default is the measured best.
+struct WfConfig
+{
+    int threads, min_blocks;
+    void (*plain)(const KernelArgs, const unsigned int, const int);
+    void (*counting)(const KernelArgs, const unsigned int, const int);
+};
+#define WF_CFG(T, B) {T, B, k_wavefront<false, T, B>, k_wavefront<true, T, B>}
+const WfConfig wf_configs[] = {WF_CFG(256, 2), WF_CFG(128, 4), WF_CFG(128, 5), WF_CFG(256, 3), WF_CFG(512, 1), WF_CFG(128, 3),
+                               WF_CFG(192, 3), WF_CFG(160, 4), WF_CFG(320, 2), WF_CFG(224, 3), WF_CFG(288, 2)};
+const int n_wf_configs = (int)(sizeof wf_configs / sizeof wf_configs[0]);
 
 DevScene device_view(const frt_ctx *ctx, const Device &d)
 {

@@ -16,7 +16,7 @@
 #pragma once
 #include "frt_device.cuh"
 
-#define FRT_STACK_SIZE 64
+#define FRT_STACK_SIZE 64 // 3 pushes per level: trees up to 21 levels deep
 // Closest hit whose t, u, v are still the float32 estimate carries this bit in RayHit::prim; the
 // consumer (shade, with the whole warp converged) calls frt_resolve_hit before using them.
 #define FRT_HIT_INEXACT 0x20000000u
@@ -69,6 +69,11 @@ __device__ __noinline__ ExactHit frt_tri_exact(const float4 *tris, uint32_t prim
 }
 
 #define FRT_FILTER_K 1e-5f // ~170 float32 ulps on each sum of absolute products
+// sum of |a_i * b_i| as one multiply and two fused multiply-adds (the absolute values are operand modifiers)
+__device__ __forceinline__ float frt_absdot(const float3 a, const float3 b)
+{
+    return fmaf(fabsf(a.z), fabsf(b.z), fmaf(fabsf(a.y), fabsf(b.y), fabsf(a.x) * fabsf(b.x)));
+}
 
 // Closest hit so far.  A hit that the float32 test places clearly inside the triangle and clearly
 // in front of everything found so far is taken on its float32 interval [lo, hi] ("lazy"); float64
@@ -98,8 +103,10 @@ struct Walker
     uint32_t cur;
     int sp;
     bool active;
-    uint32_t stack[FRT_STACK_SIZE]; // child reference
-    float stack_t[FRT_STACK_SIZE];  // its entry distance, to drop it at pop time once something closer was found
+    // The short stack is NOT a member: a dynamically indexed array inside the struct would put every
+    // member in local memory.  The caller declares `uint2 stk[FRT_STACK_SIZE]` (x = child reference,
+    // y = bits of its entry distance, to drop it at pop time once something closer was found) and
+    // hands it to round().  frt_upload_scene rejects trees deeper than the stack can serve.
 
     __device__ __forceinline__ double tend_d() const { return ANY ? 1.0 - (double)FRT_SHADOW_EPSILON : (double)FRT_FLT_MAX; }
     __device__ __forceinline__ double tmin_exact() const { return frt_tmin_exact(o); }
@@ -124,7 +131,7 @@ struct Walker
         active = sc.n_nodes != 0;
     }
 
-    __device__ __forceinline__ void round(const DevScene &sc, unsigned int &n_nodes, unsigned int &n_tris)
+    __device__ __forceinline__ void round(const DevScene &sc, uint2 *stk, unsigned int &n_nodes, unsigned int &n_tris)
     {
         // ---- while-while, part 1: descend through inner nodes (EMPTY carries the leaf bit and ends the loop)
         while (!(cur & FRT_CHILD_LEAF))
@@ -156,9 +163,10 @@ struct Walker
             a = min(k0, k2); b = max(k0, k2); k0 = a; k2 = b;
             a = min(k1, k3); b = max(k1, k3); k1 = a; k3 = b;
             a = min(k1, k2); b = max(k1, k2); k1 = a; k2 = b;
-            if (k3 != 0xFFFFFFFFu && sp < FRT_STACK_SIZE) { stack[sp] = frt_pick(ch, k3 & 3u); stack_t[sp++] = __uint_as_float(k3 & ~3u); }
-            if (k2 != 0xFFFFFFFFu && sp < FRT_STACK_SIZE) { stack[sp] = frt_pick(ch, k2 & 3u); stack_t[sp++] = __uint_as_float(k2 & ~3u); }
-            if (k1 != 0xFFFFFFFFu && sp < FRT_STACK_SIZE) { stack[sp] = frt_pick(ch, k1 & 3u); stack_t[sp++] = __uint_as_float(k1 & ~3u); }
+            // invalid keys sort last: push the far ones (farthest first), continue with the nearest
+            if (k3 != 0xFFFFFFFFu) stk[sp++] = make_uint2(frt_pick(ch, k3 & 3u), k3 & ~3u);
+            if (k2 != 0xFFFFFFFFu) stk[sp++] = make_uint2(frt_pick(ch, k2 & 3u), k2 & ~3u);
+            if (k1 != 0xFFFFFFFFu) stk[sp++] = make_uint2(frt_pick(ch, k1 & 3u), k1 & ~3u);
             cur = (k0 != 0xFFFFFFFFu) ? frt_pick(ch, k0 & 3u) : FRT_CHILD_EMPTY;
         }
 
@@ -194,34 +202,37 @@ struct Walker
                     const float4 *tp = sc.tris + 3 * (size_t)prim;
                     const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
                     if (COUNT) ++n_tris;
-                    // float32 pass: the same formula with error margins from the sums of absolute products
+                    // float32 pass: the same formula with error margins from the sums of absolute products,
+                    // evaluated without branches (a warp almost always has a lane that needs every term) and
+                    // classified once: certainly missed / certainly the closest hit so far / decide in float64
                     const float3 v0 = f3(q0), e1 = f3(q1) - v0, e2 = f3(q2) - v0;
                     const float3 h = cross(d, e2);
                     const float a = dot(e1, h);
-                    const float abs_a = fabsf(e1.x * h.x) + fabsf(e1.y * h.y) + fabsf(e1.z * h.z);
-                    if (fabsf(a) > 16.0f * FRT_FILTER_K * abs_a) // else too ill-conditioned for float32: decide exactly
+                    const float abs_a = frt_absdot(e1, h);
+                    const float f = __fdividef(1.0f, a), af = fabsf(f); // 2 ulp: far inside the margins
+                    const float kf = FRT_FILTER_K * af;
+                    const float rel = kf * abs_a + 1e-6f;
+                    const float3 s = o - v0;
+                    const float uf = f * dot(s, h);
+                    const float du = fmaf(kf, frt_absdot(s, h), fmaf(fabsf(uf), rel, 1e-6f));
+                    const float3 q = cross(s, e1);
+                    const float vf = f * dot(d, q);
+                    const float dv = fmaf(kf, frt_absdot(d, q), fmaf(fabsf(vf), rel, 1e-6f));
+                    const float tf = f * dot(e2, q);
+                    const float dt = fmaf(kf, frt_absdot(e2, q), fabsf(tf) * rel);
+                    const float wf = uf + vf, dw = du + dv;
+                    // too ill-conditioned for float32 (or a == 0): neither verdict, decide exactly
+                    const bool conditioned = fabsf(a) > 16.0f * FRT_FILTER_K * abs_a;
+                    const bool missed = uf < -du || uf > 1.0f + du || vf < -dv || wf > 1.0f + dw // outside the triangle
+                                        || tf < tmin - dt || tf > tmax + dt;                  // outside (t_min, closest so far)
+                    if (conditioned && missed) continue;
+                    if (conditioned && uf > du && vf > dv && wf < 1.0f - dw && tf - dt > tmin_hi && tf + dt < best.lo)
                     {
-                        const float f = 1.0f / a, af = fabsf(f);
-                        const float rel = FRT_FILTER_K * abs_a * af;
-                        const float3 s = o - v0;
-                        const float uf = f * dot(s, h);
-                        const float du = FRT_FILTER_K * af * (fabsf(s.x * h.x) + fabsf(s.y * h.y) + fabsf(s.z * h.z)) + fabsf(uf) * rel + 1e-6f;
-                        if (uf < -du || uf > 1.0f + du) continue;
-                        const float3 q = cross(s, e1);
-                        const float vf = f * dot(d, q);
-                        const float dv = FRT_FILTER_K * af * (fabsf(d.x * q.x) + fabsf(d.y * q.y) + fabsf(d.z * q.z)) + fabsf(vf) * rel + 1e-6f;
-                        if (vf < -dv || uf + vf > 1.0f + du + dv) continue;
-                        const float tf = f * dot(e2, q);
-                        const float dt = FRT_FILTER_K * af * (fabsf(e2.x * q.x) + fabsf(e2.y * q.y) + fabsf(e2.z * q.z)) + fabsf(tf) * (rel + 1e-6f);
-                        if (tf < tmin - dt || tf > tmax + dt) continue; // certainly outside (t_min, closest so far)
-                        if (uf > du && vf > dv && uf + vf < 1.0f - du - dv && tf - dt > tmin_hi && tf + dt < best.lo)
-                        {
-                            // certainly a hit and certainly the closest so far
-                            best.prim = prim; best.lo = tf - dt; best.hi = tf + dt; best.u = uf; best.v = vf; best.exact = false;
-                            tmax = best.hi;
-                            if (ANY) { active = false; return; }
-                            continue;
-                        }
+                        // certainly a hit and certainly the closest so far
+                        best.prim = prim; best.lo = tf - dt; best.hi = tf + dt; best.u = uf; best.v = vf; best.exact = false;
+                        tmax = best.hi;
+                        if (ANY) { active = false; return; }
+                        continue;
                     }
                     e = frt_tri_exact(sc.tris, prim, o.x, o.y, o.z, d.x, d.y, d.z, tmin_exact());
                     if (e.t < 0.0) continue;
@@ -254,8 +265,8 @@ struct Walker
         active = false;
         while (sp > 0)
         {
-            --sp;
-            if (stack_t[sp] <= tmax) { cur = stack[sp]; active = true; break; }
+            const uint2 e = stk[--sp];
+            if (__uint_as_float(e.y) <= tmax) { cur = e.x; active = true; break; }
         }
     }
 
@@ -302,7 +313,8 @@ __device__ __forceinline__ RayHit frt_traverse(const DevScene &sc, const float3 
                                                unsigned int &n_nodes, unsigned int &n_tris)
 {
     Walker<ANY, COUNT> w;
+    uint2 stk[FRT_STACK_SIZE];
     w.begin(sc, o, d);
-    while (w.active) w.round(sc, n_nodes, n_tris);
+    while (w.active) w.round(sc, stk, n_nodes, n_tris);
     return w.finish(sc);
 }

@@ -18,12 +18,7 @@
 #pragma once
 #include "frt_shade.cuh"
 
-#define FRT_WF_THREADS 256
-#define FRT_WF_MIN_BLOCKS 2
 #define FRT_WF_SLOT_BYTES 144u
-#ifndef FRT_WF_REFILL_BELOW
-#define FRT_WF_REFILL_BELOW 24 // fetch new rays once this many lanes or fewer are still traversing
-#endif
 
 struct WfShared
 {
@@ -41,12 +36,13 @@ __device__ __forceinline__ unsigned long long frt_globaltimer()
 // Persistent-warp ray casting over one shared-memory queue of slot indices.
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ void wf_trace_queue(const DevScene &sc, const PathPool &lp, const unsigned int *q,
-                                               const unsigned int n_items, unsigned int *cursor, unsigned int &n_rays,
-                                               unsigned int &n_nodes, unsigned int &n_tris)
+                                               const unsigned int n_items, unsigned int *cursor, const int refill_below,
+                                               unsigned int &n_rays, unsigned int &n_nodes, unsigned int &n_tris)
 {
     if (n_items == 0) return;
     const unsigned int lane = lane_id();
     Walker<ANY, COUNT> w;
+    uint2 stk[FRT_STACK_SIZE];
     w.active = false;
     bool pending = false, more = true;
     unsigned int slot = 0;
@@ -82,9 +78,9 @@ __device__ __forceinline__ void wf_trace_queue(const DevScene &sc, const PathPoo
         unsigned int act = __ballot_sync(0xFFFFFFFFu, w.active);
         while (act)
         {
-            if (w.active) w.round(sc, n_nodes, n_tris);
+            if (w.active) w.round(sc, stk, n_nodes, n_tris);
             act = __ballot_sync(0xFFFFFFFFu, w.active);
-            if (more && __popc(act) <= FRT_WF_REFILL_BELOW) break;
+            if (more && __popc(act) <= refill_below) break;
         }
         if (pending && !w.active)
         {
@@ -110,8 +106,10 @@ __device__ __forceinline__ void wf_trace_queue(const DevScene &sc, const PathPoo
     }
 }
 
-template <bool COUNT>
-__global__ void __launch_bounds__(FRT_WF_THREADS, FRT_WF_MIN_BLOCKS) k_wavefront(const KernelArgs a, const unsigned int P)
+// P = slots per CTA (a multiple of 32); refill_below = a warp fetches new rays once this many lanes or
+// fewer are still traversing.
+template <bool COUNT, int THREADS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelArgs a, const unsigned int P, const int refill_below)
 {
     extern __shared__ float4 wf_smem[];
     __shared__ WfShared sh;
@@ -124,7 +122,7 @@ __global__ void __launch_bounds__(FRT_WF_THREADS, FRT_WF_MIN_BLOCKS) k_wavefront
     lp.free_q[0] = free_q; lp.free_q[1] = free_q; lp.shadow_q = shadow_q;
 
     const unsigned int tid = threadIdx.x;
-    for (unsigned int i = tid; i < P; i += FRT_WF_THREADS)
+    for (unsigned int i = tid; i < P; i += THREADS)
     {
         lp.ray_d[i] = make_float4(0.f, 0.f, 0.f, 0.f); // dead
         free_q[i] = i;
@@ -159,7 +157,7 @@ __global__ void __launch_bounds__(FRT_WF_THREADS, FRT_WF_MIN_BLOCKS) k_wavefront
         __syncthreads();
         const unsigned int n_new = sh.n_new, n_bounce = sh.n_ext, n_sh = sh.n_shadow;
         const unsigned long long base = sh.base;
-        for (unsigned int i = tid; i < n_new; i += FRT_WF_THREADS)
+        for (unsigned int i = tid; i < n_new; i += THREADS)
         {
             const unsigned int slot = free_q[i];
             frt_generate_path(a, lp, slot, base + i);
@@ -172,9 +170,9 @@ __global__ void __launch_bounds__(FRT_WF_THREADS, FRT_WF_MIN_BLOCKS) k_wavefront
         if (tid == 0) { const unsigned long long t = frt_globaltimer(); t_gen += t - t0; t0 = t; }
 
         // ---- extend + connect -----------------------------------------------------------------
-        wf_trace_queue<false, COUNT>(a.sc, lp, ext_q, n_ext, &sh.cur_ext, n_closest, n_nodes, n_tris);
+        wf_trace_queue<false, COUNT>(a.sc, lp, ext_q, n_ext, &sh.cur_ext, refill_below, n_closest, n_nodes, n_tris);
         if (tid == 0) { const unsigned long long t = frt_globaltimer(); t_ext += t - t0; t0 = t; }
-        wf_trace_queue<true, COUNT>(a.sc, lp, shadow_q, n_sh, &sh.cur_shadow, n_shadow_rays, n_nodes, n_tris);
+        wf_trace_queue<true, COUNT>(a.sc, lp, shadow_q, n_sh, &sh.cur_shadow, refill_below, n_shadow_rays, n_nodes, n_tris);
         __syncthreads();
         if (tid == 0)
         {
@@ -184,9 +182,10 @@ __global__ void __launch_bounds__(FRT_WF_THREADS, FRT_WF_MIN_BLOCKS) k_wavefront
         __syncthreads();
 
         // ---- shade + queue compaction -----------------------------------------------------------
-        for (unsigned int s0 = 0; s0 < P; s0 += FRT_WF_THREADS)
+        for (unsigned int s0 = 0; s0 < P; s0 += THREADS)
         {
-            const unsigned int slot = s0 + tid; // P is a multiple of the CTA size
+            const unsigned int slot = s0 + tid; // P is a multiple of 32: whole warps fall off the end together
+            if (slot >= P) break;
             const unsigned int r = frt_shade_vertex(a, lp, slot, nonfinite);
             const bool ended = r & FRT_SHADE_TERMINATED, goes_on = (r & FRT_SHADE_WAS_ALIVE) && !ended;
             const unsigned int ei = warp_append(goes_on, &sh.n_ext);
