@@ -175,7 +175,7 @@ def run_frt(args):
     spp = args.spp
     s0, s1 = spp * rank // world, spp * (rank + 1) // world
 
-    scene = api.HostScene(SCENE, NX / NY, int(os.environ.get("FRT_MAX_LEAF", "4")))
+    scene = api.HostScene(SCENE, NX / NY, int(os.environ.get("FRT_MAX_LEAF", "2")))
     ctx = api.Context(devices=[local])
     ctx.upload(scene)
     base_flags = api.FRT_FLAG_STREAMED_POOL if args.streamed_pool else 0

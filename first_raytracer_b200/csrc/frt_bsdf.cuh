@@ -183,7 +183,7 @@ __device__ __forceinline__ float2 sample_visible_11(float thetaI, float sx, floa
         {
             const float r = sqrtf(-logf(1.0f - sx));
             float sp, cp;
-            sincosf(2.0f * FRT_PI * sy, &sp, &cp);
+            sincospif(2.0f * sy, &sp, &cp);
             return make_float2(r * cp, r * sp);
         }
         const float tanThetaI = tanf(thetaI), cotThetaI = 1.0f / tanThetaI;
@@ -211,7 +211,7 @@ __device__ __forceinline__ float2 sample_visible_11(float thetaI, float sx, floa
     {
         const float r = safe_sqrt(sx / (1.0f - sx));
         float sp, cp;
-        sincosf(2.0f * FRT_PI * sy, &sp, &cp);
+        sincospif(2.0f * sy, &sp, &cp);
         return make_float2(r * cp, r * sp);
     }
     const float tanThetaI = tanf(thetaI);
@@ -277,7 +277,7 @@ __device__ __forceinline__ void mat_scatter(const frt_material &m, const Surface
         const float sinAlpha = sqrtf(1.0f - powf(s1, 2.0f / (e + 1.0f)));
         const float cosAlpha = powf(s1, 1.0f / (e + 1.0f));
         float sp, cp;
-        sincosf(2.0f * FRT_PI * s0, &sp, &cp);
+        sincospif(2.0f * s0, &sp, &cp);
         srec.dir = Onb(R).from_local(f3(sinAlpha * cp, sinAlpha * sp, cosAlpha));
         break;
     }

@@ -46,7 +46,8 @@ __device__ __forceinline__ float3 operator*(float3 a, float3 b) { return f3(a.x 
 __device__ __forceinline__ float3 operator/(float3 a, float3 b) { return f3(a.x / b.x, a.y / b.y, a.z / b.z); }
 __device__ __forceinline__ float3 operator*(float3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
 __device__ __forceinline__ float3 operator*(float s, float3 a) { return f3(a.x * s, a.y * s, a.z * s); }
-__device__ __forceinline__ float3 operator/(float3 a, float s) { return f3(a.x / s, a.y / s, a.z / s); }
+// one IEEE reciprocal and three multiplies instead of three IEEE divisions (differs by <= 1 ulp per component)
+__device__ __forceinline__ float3 operator/(float3 a, float s) { const float inv = 1.0f / s; return f3(a.x * inv, a.y * inv, a.z * inv); }
 __device__ __forceinline__ float dot(float3 a, float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 __device__ __forceinline__ float3 cross(float3 a, float3 b)
 {

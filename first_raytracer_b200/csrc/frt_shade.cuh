@@ -36,7 +36,7 @@ __device__ __forceinline__ LightSample light_sample_direct(const frt_light &L, f
         const float z = 1.0f - 2.0f * u0;
         const float r = sqrtf(fmaxf(0.0f, 1.0f - z * z));
         float sp, cp;
-        sincosf(2.0f * FRT_PI * u1, &sp, &cp);
+        sincospif(2.0f * u1, &sp, &cp);
         const float3 p = c + radius * f3(r * cp, r * sp, z);
         ls.n = unit_vector(c - p);
         ls.to_light = p - o;
@@ -45,7 +45,7 @@ __device__ __forceinline__ LightSample light_sample_direct(const frt_light &L, f
     // random_to_sphere pdf.h:46-56 pushed through the un-normalised basis (sphere.h:84-85,100)
     const float z = 1.0f + u1 * (sqrtf(1.0f - radius * radius / d2) - 1.0f);
     float sp, cp;
-    sincosf(2.0f * FRT_PI * u0, &sp, &cp);
+    sincospif(2.0f * u0, &sp, &cp);
     const float s = sqrtf(1.0f - z * z);
     const float3 p = Onb(direction).from_local(f3(cp * s, sp * s, z));
     ls.n = unit_vector(p);
@@ -208,7 +208,7 @@ __device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, co
                         // cosine_pdf::generate pdf.h:91-94 + hemisphere_to_cosine_direction pdf.h:13-23
                         const float r = sqrtf(r2.z);
                         float sp, cp;
-                        sincosf(2.0f * FRT_PI * r2.w, &sp, &cp);
+                        sincospif(2.0f * r2.w, &sp, &cp);
                         next_d = Onb(h.n).from_local(f3(r * cp, r * sp, sqrtf(1.0f - r2.z)));
                         next_o = h.p + FRT_EPSILON * h.n;
                         pdf = mat_pdf_value(m, h, next_d);

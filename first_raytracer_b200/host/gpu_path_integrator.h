@@ -21,7 +21,7 @@ struct gpu_path_integrator
     int n_gpus = 1;
     uint32_t seed = 1;
     uint32_t max_depth = 34;
-    int max_leaf = 4;
+    int max_leaf = 2; // triangles per wide-BVH leaf (measured best on B200 for the reference scenes)
     uint32_t flags = 0;
     frt_stats stats{};
     const std::unordered_map<const hitable *, int> *prim_ids = nullptr;
