@@ -279,6 +279,9 @@ def roofline_pass(ctx, api, spp_range, peaks, base_flags, stream):
         "stage_share": {k: v / max(1e-9, sum(kms.values())) for k, v in kms.items()},
         "nodes_per_ray": per_nodes, "tris_per_ray": per_tris, "bytes_per_ray": b_ray,
         "wavefront_iterations": st["iterations"],
+        # one ncu --set full capture of a 1080p x 8 spp launch (profiles/r01_ncu_wavefront.txt): DRAM bytes of that
+        # launch next to its algorithmic bytes; the scene and the path pool never leave L1/L2/shared memory
+        "traffic_ncu_8spp_launch": {"dram_bytes": 25.35e6 + 5.72e6, "algorithmic_bytes": 111.2e6 * b_ray},
         "note": "scene (36 triangles) is L1/L2 resident: the HBM fraction is reported as the contract asks; "
                 "the binding resource is SM issue slots (profiles/)",
     }

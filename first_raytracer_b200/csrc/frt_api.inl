@@ -34,6 +34,7 @@ int frt_create(frt_ctx **out, const int *devices, int n)
     if (const char *s = getenv("FRT_POLL_EVERY")) c->poll_every = std::max(1, atoi(s));
     if (const char *s = getenv("FRT_WF_SLOTS")) c->wf_slots = (unsigned int)std::min(1568, std::max(32, atoi(s) / 32 * 32));
     if (const char *s = getenv("FRT_WF_CONFIG")) c->wf_config = std::min(n_wf_configs - 1, std::max(0, atoi(s)));
+    if (const char *s = getenv("FRT_WF_SORT")) c->wf_sort = atoi(s) != 0;
     if (const char *s = getenv("FRT_WF_REFILL")) c->wf_refill = std::min(31, std::max(0, atoi(s)));
     for (int i = 0; i < n; ++i)
     {

@@ -60,9 +60,10 @@ struct frt_ctx
     DevScene host_view{}; // counts + camera; pointers filled per device
     uint32_t nx = 0, ny = 0;
     unsigned int n_slots = 1u << 20; // streamed (global-memory) pool
-    unsigned int wf_slots = 512;     // CTA-resident pool: slots per CTA (multiple of 32)
-    int wf_config = 0;               // index into wf_configs[]
+    unsigned int wf_slots = 1024;    // CTA-resident pool: slots per CTA (multiple of 32)
+    int wf_config = 4;               // index into wf_configs[]: 512 threads, one CTA per SM (measured best)
     int wf_refill = 24;              // dynamic fetch threshold (lanes still traversing)
+    int wf_sort = 1;                 // bin queued rays by where they start
     int poll_every = 16;
     frt_stats stats{};
 };
@@ -207,8 +208,8 @@ __global__ void __launch_bounds__(128) k_trace(DevScene sc, Counters *ctr, const
 struct WfConfig
 {
     int threads, min_blocks;
-    void (*plain)(const KernelArgs, const unsigned int, const int);
-    void (*counting)(const KernelArgs, const unsigned int, const int);
+    void (*plain)(const KernelArgs, const unsigned int, const int, const int);
+    void (*counting)(const KernelArgs, const unsigned int, const int, const int);
 };
 #define WF_CFG(T, B) {T, B, k_wavefront<false, T, B>, k_wavefront<true, T, B>}
 const WfConfig wf_configs[] = {WF_CFG(256, 2), WF_CFG(128, 4), WF_CFG(128, 5), WF_CFG(256, 3), WF_CFG(512, 1), WF_CFG(128, 3),

@@ -88,9 +88,13 @@ __device__ __forceinline__ void end_path(const KernelArgs &a, const PathPool &po
 #define FRT_SHADE_TERMINATED 1u
 #define FRT_SHADE_SHADOW 2u
 #define FRT_SHADE_WAS_ALIVE 4u
+// Bits 8.. of the result = the primitive the vertex lies on (leaf-order index), a spatial key for
+// binning the rays that leave it.
+#define FRT_SHADE_PRIM_SHIFT 3
 __device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, const PathPool &pool, const unsigned int slot,
                                                          unsigned int &nonfinite)
 {
+        unsigned int origin_prim = 0;
         bool terminated = false, want_shadow = false;
         const float4 dw = pool.ray_d[slot];
         const unsigned int flags = __float_as_uint(dw.w);
@@ -107,6 +111,7 @@ __device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, co
             // a winner taken on its float32 interval gets the reference's float64 t, u, v here, where the
             // warp is converged (the CTA-resident wavefront defers it out of the divergent traversal)
             if (prim != 0xFFFFFFFFu && (prim & FRT_HIT_INEXACT)) frt_resolve_hit(a.sc, o, d, hw.x, hw.y, hw.z, prim);
+            origin_prim = prim & FRT_LEAF_FIRST_MASK;
             const unsigned int pixel = __float_as_uint(tw.w), sample = __float_as_uint(rw.w);
             float3 thr = f3(tw), rad = f3(rw);
 
@@ -281,7 +286,7 @@ __device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, co
             }
         }
         return (terminated ? FRT_SHADE_TERMINATED : 0u) | (want_shadow ? FRT_SHADE_SHADOW : 0u) |
-               ((flags & FRT_FLAG_ALIVE) ? FRT_SHADE_WAS_ALIVE : 0u);
+               ((flags & FRT_FLAG_ALIVE) ? FRT_SHADE_WAS_ALIVE : 0u) | (origin_prim << FRT_SHADE_PRIM_SHIFT);
 }
 
 __global__ void __launch_bounds__(128) k_shade(const KernelArgs a, const int parity_out)

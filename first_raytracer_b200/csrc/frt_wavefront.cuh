@@ -18,10 +18,12 @@
 #pragma once
 #include "frt_shade.cuh"
 
-#define FRT_WF_SLOT_BYTES 144u
+#define FRT_WF_SLOT_BYTES 145u // + one key byte per slot for the origin binning
 
+#define FRT_WF_BINS 64
 struct WfShared
 {
+    unsigned int hist_ext[FRT_WF_BINS], hist_sh[FRT_WF_BINS]; // ray-origin bins: counts, then write offsets
     unsigned long long base; // first sample index of this iteration's run
     unsigned int n_ext, n_free, n_shadow, n_new, cur_ext, cur_shadow, exhausted, pad;
 };
@@ -109,7 +111,8 @@ __device__ __forceinline__ void wf_trace_queue(const DevScene &sc, const PathPoo
 // P = slots per CTA (a multiple of 32); refill_below = a warp fetches new rays once this many lanes or
 // fewer are still traversing.
 template <bool COUNT, int THREADS, int MIN_BLOCKS>
-__global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelArgs a, const unsigned int P, const int refill_below)
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelArgs a, const unsigned int P, const int refill_below,
+                                                                   const int sort_rays)
 {
     extern __shared__ float4 wf_smem[];
     __shared__ WfShared sh;
@@ -182,6 +185,58 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelA
         __syncthreads();
 
         // ---- shade + queue compaction -----------------------------------------------------------
+        if (sort_rays)
+        {
+            // Rays are queued binned by where they start (the leaf-order index of the primitive the vertex
+            // lies on is a spatial key), so a warp of the next trace stage pulls rays that leave the same
+            // part of the scene: counting sort in shared memory, hist -> exclusive scan -> scatter.
+            unsigned char *key = reinterpret_cast<unsigned char *>(shadow_q + P); // P bytes: bin | 0x80 shadow, 0xFF = not queued
+            if (tid < FRT_WF_BINS) { sh.hist_ext[tid] = 0; sh.hist_sh[tid] = 0; }
+            __syncthreads();
+            const unsigned int bin_div = (max(a.sc.n_tris, a.sc.n_spheres) + FRT_WF_BINS - 1) / FRT_WF_BINS;
+            for (unsigned int s0 = 0; s0 < P; s0 += THREADS)
+            {
+                const unsigned int slot = s0 + tid;
+                if (slot >= P) break;
+                const unsigned int r = frt_shade_vertex(a, lp, slot, nonfinite);
+                const bool ended = r & FRT_SHADE_TERMINATED, goes_on = (r & FRT_SHADE_WAS_ALIVE) && !ended;
+                const unsigned int fi = warp_append(ended, &sh.n_free);
+                if (ended) free_q[fi] = slot;
+                unsigned int k = 0xFFu;
+                if (goes_on)
+                {
+                    k = min((r >> FRT_SHADE_PRIM_SHIFT) / max(bin_div, 1u), FRT_WF_BINS - 1u);
+                    atomicAdd(&sh.hist_ext[k], 1u);
+                    if (r & FRT_SHADE_SHADOW) { atomicAdd(&sh.hist_sh[k], 1u); k |= 0x80u; }
+                }
+                key[slot] = (unsigned char)k;
+            }
+            __syncthreads();
+            if (tid < 32)
+            {
+                // exclusive scan of both histograms by one warp (two bins per lane)
+                unsigned int e0 = sh.hist_ext[2 * tid], e1 = sh.hist_ext[2 * tid + 1];
+                unsigned int h0 = sh.hist_sh[2 * tid], h1 = sh.hist_sh[2 * tid + 1];
+                unsigned int es = e0 + e1, hs = h0 + h1;
+                for (int off = 1; off < 32; off <<= 1)
+                {
+                    const unsigned int ev = __shfl_up_sync(0xFFFFFFFFu, es, off), hv = __shfl_up_sync(0xFFFFFFFFu, hs, off);
+                    if ((int)tid >= off) { es += ev; hs += hv; }
+                }
+                sh.hist_ext[2 * tid] = es - e0 - e1; sh.hist_ext[2 * tid + 1] = es - e1;
+                sh.hist_sh[2 * tid] = hs - h0 - h1; sh.hist_sh[2 * tid + 1] = hs - h1;
+                if (tid == 31) { sh.n_ext = es; sh.n_shadow = hs; }
+            }
+            __syncthreads();
+            for (unsigned int slot = tid; slot < P; slot += THREADS)
+            {
+                const unsigned int k = key[slot];
+                if (k == 0xFFu) continue;
+                ext_q[atomicAdd(&sh.hist_ext[k & 0x7Fu], 1u)] = slot;
+                if (k & 0x80u) shadow_q[atomicAdd(&sh.hist_sh[k & 0x7Fu], 1u)] = slot;
+            }
+        }
+        else
         for (unsigned int s0 = 0; s0 < P; s0 += THREADS)
         {
             const unsigned int slot = s0 + tid; // P is a multiple of 32: whole warps fall off the end together
