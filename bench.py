@@ -172,8 +172,9 @@ def run_frt(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    from first_raytracer_b200 import sharding
     spp = args.spp
-    s0, s1 = spp * rank // world, spp * (rank + 1) // world
+    s0, s1 = sharding.spp_share(0, spp, rank, world)
 
     scene = api.HostScene(SCENE, NX / NY, int(os.environ.get("FRT_MAX_LEAF", "2")))
     ctx = api.Context(devices=[local])
@@ -200,7 +201,7 @@ def run_frt(args):
                 p, n = ctx.film_device_ptr(0)
                 film_t = torch.as_tensor(_DevBuf(p, n), device=dev)
             with torch.cuda.stream(stream):
-                dist.reduce(film_t, dst=0)  # the one collective of the path: sum of partial films
+                sharding.reduce_film(film_t, dst=0)  # the one collective of the path: sum of partial films
         e1.record(stream)
         e1.synchronize()
         _, st = ctx.readback(want_image=False)
