@@ -24,7 +24,7 @@ FRT_FLAG_STREAMED_POOL = 4
 FRT_SYMBOLS = [
     "frt_create", "frt_destroy", "frt_last_error", "frt_set_flags", "frt_device_count",
     "frt_upload_scene", "frt_render_tile", "frt_clear_film", "frt_readback", "frt_film_device_ptr",
-    "frt_trace_rays", "frt_trace_rays_device", "frt_stream_handle",
+    "frt_trace_rays", "frt_trace_rays_device", "frt_stream_handle", "frt_get_counters",
 ]
 FRTH_SYMBOLS = [
     "frth_last_error", "frth_scene_create", "frth_scene_create_soup", "frth_scene_destroy",
@@ -120,6 +120,7 @@ def load_libs():
             "frt_render_tile": (i32, [vp, C.POINTER(frt_tile)]),
             "frt_clear_film": (i32, [vp]),
             "frt_readback": (i32, [vp, vp, sz, C.POINTER(frt_stats)]),
+            "frt_get_counters": (i32, [vp, C.POINTER(frt_stats)]),
             "frt_film_device_ptr": (i32, [vp, i32, C.POINTER(vp), C.POINTER(sz)]),
             "frt_stream_handle": (i32, [vp, i32, C.POINTER(vp)]),
             "frt_trace_rays": (i32, [vp, vp, sz, vp, i32, C.POINTER(dbl)]),
@@ -298,6 +299,11 @@ class Context:
         else:
             self._check(self._frt.frt_readback(self.handle, None, 0, C.byref(st)), "frt_readback")
         return out, st.as_dict()
+
+    def counters(self) -> dict:
+        st = frt_stats()
+        self._check(self._frt.frt_get_counters(self.handle, C.byref(st)), "frt_get_counters")
+        return st.as_dict()
 
     def film_device_ptr(self, dev: int = 0):
         p, n = C.c_void_p(), C.c_size_t()

@@ -191,6 +191,25 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
     return FRT_OK;
 }
 
+int frt_get_counters(frt_ctx *ctx, frt_stats *stats)
+{
+    if (!ctx || !stats) return FRT_ERR_INVALID;
+    memset(stats, 0, sizeof *stats);
+    for (Device &d : ctx->dev)
+    {
+        CU(cudaSetDevice(d.ordinal));
+        CU(cudaMemcpyAsync(d.h_ctr, d.d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
+        CU(cudaStreamSynchronize(d.stream));
+        stats->samples += d.h_ctr->samples_started;
+        stats->closest_rays += d.h_ctr->closest_rays;
+        stats->shadow_rays += d.h_ctr->shadow_rays;
+        stats->node_visits += d.h_ctr->node_visits;
+        stats->tri_tests += d.h_ctr->tri_tests;
+        stats->kernel_launches += d.launches;
+    }
+    return FRT_OK;
+}
+
 int frt_film_device_ptr(frt_ctx *ctx, int dev, void **ptr, size_t *n_floats)
 {
     if (!ctx || dev < 0 || dev >= (int)ctx->dev.size() || !ptr) return FRT_ERR_INVALID;

@@ -182,6 +182,11 @@ FRT_API int frt_clear_film(frt_ctx *ctx);
  * `rgb_sum` (may be NULL to only synchronise) and fills `stats` (may be NULL). */
 FRT_API int frt_readback(frt_ctx *ctx, float *rgb_sum, size_t n_floats, frt_stats *stats);
 
+/* Counters only (rays, node visits, triangle tests since the last frt_clear_film), summed over the
+ * devices; synchronises.  Works without a film, i.e. after frt_trace_rays alone: the integrator's
+ * statistics block (integrator.h:33-43) for a pure ray-cast run. */
+FRT_API int frt_get_counters(frt_ctx *ctx, frt_stats *stats);
+
 /* Device address of device `dev`'s film (nx*ny*3 float32) so that a multi-process launcher can
  * reduce it in place with its own communicator before frt_readback.  Synchronises `dev`. */
 FRT_API int frt_film_device_ptr(frt_ctx *ctx, int dev, void **ptr, size_t *n_floats);
