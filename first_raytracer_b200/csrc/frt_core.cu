@@ -213,7 +213,8 @@ struct WfConfig
 };
 #define WF_CFG(T, B) {T, B, k_wavefront<false, T, B>, k_wavefront<true, T, B>}
 const WfConfig wf_configs[] = {WF_CFG(256, 2), WF_CFG(128, 4), WF_CFG(128, 5), WF_CFG(256, 3), WF_CFG(512, 1), WF_CFG(128, 3),
-                               WF_CFG(192, 3), WF_CFG(160, 4), WF_CFG(320, 2), WF_CFG(224, 3), WF_CFG(288, 2)};
+                               WF_CFG(192, 3), WF_CFG(160, 4), WF_CFG(320, 2), WF_CFG(224, 3), WF_CFG(288, 2),
+                               WF_CFG(384, 1), WF_CFG(448, 1), WF_CFG(192, 2)};
 const int n_wf_configs = (int)(sizeof wf_configs / sizeof wf_configs[0]);
 
 DevScene device_view(const frt_ctx *ctx, const Device &d)

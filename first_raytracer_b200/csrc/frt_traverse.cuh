@@ -152,6 +152,18 @@ struct Walker
             const float tf1 = fminf(fminf(fx.y * idx - oox, fy.y * idy - ooy), fminf(fz.y * idz - ooz, tmax));
             const float tf2 = fminf(fminf(fx.z * idx - oox, fy.z * idy - ooy), fminf(fz.z * idz - ooz, tmax));
             const float tf3 = fminf(fminf(fx.w * idx - oox, fy.w * idy - ooy), fminf(fz.w * idz - ooz, tmax));
+            if (ANY)
+            {
+                // an occlusion query looks at every child the segment enters unless an occluder turns up
+                // first, so the order is free: no sort, no entry distances on the stack
+                uint32_t next = FRT_CHILD_EMPTY;
+                if (tf3 >= tn3) next = ch.w;
+                if (tf2 >= tn2) { if (next != FRT_CHILD_EMPTY) stk[sp++] = make_uint2(next, 0u); next = ch.z; }
+                if (tf1 >= tn1) { if (next != FRT_CHILD_EMPTY) stk[sp++] = make_uint2(next, 0u); next = ch.y; }
+                if (tf0 >= tn0) { if (next != FRT_CHILD_EMPTY) stk[sp++] = make_uint2(next, 0u); next = ch.x; }
+                cur = next;
+                continue;
+            }
             // sort the (up to four) intersected children near-to-far: key = quantised tnear | slot
             uint32_t k0 = (tf0 >= tn0) ? ((__float_as_uint(tn0) & ~3u) | 0u) : 0xFFFFFFFFu;
             uint32_t k1 = (tf1 >= tn1) ? ((__float_as_uint(tn1) & ~3u) | 1u) : 0xFFFFFFFFu;
