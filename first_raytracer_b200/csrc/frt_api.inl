@@ -64,6 +64,8 @@ int frt_create(frt_ctx **out, const int *devices, int n)
         d.blocks_connect = std::max(1, per_sm) * d.sms;
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<false, false>, 128, 0));
         d.blocks_trace = std::max(1, per_sm) * d.sms;
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<true, false>, 128, 0));
+        d.blocks_trace_any = std::max(1, per_sm) * d.sms;
         const size_t wf_smem = (size_t)c->wf_slots * FRT_WF_SLOT_BYTES;
         const WfConfig &wc = wf_configs[c->wf_config];
         CU(cudaFuncSetAttribute(wc.plain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));

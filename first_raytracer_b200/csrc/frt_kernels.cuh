@@ -63,6 +63,58 @@ __device__ __forceinline__ unsigned int warp_append(bool pred, unsigned int *cou
 // ---------------------------------------------------------------------------------------------
 // generate: path.cpp:129-133 + camera::get_ray camera.h:30-35 + random_in_unit_disk util.h:21-41
 // ---------------------------------------------------------------------------------------------
+// Persistent-warp ray casting over a queue of `n_items` work items behind an atomic cursor (shared or
+// global memory).  One ray per lane; between traversal rounds the warp ballots its lanes and, once
+// `refill_below` or fewer are still traversing, hands every idle lane the next item (dynamic fetch, one
+// atomic per warp), so a warp is not held by its slowest ray.  (Letting lanes run several rounds between two
+// looks at the warp was measured: no gain.)  Io::load(item, o, d) fetches a ray,
+// Io::store(sc, walker) consumes the finished traversal; both run for the lanes of one refill together.
+template <bool ANY, bool COUNT, class Io>
+__device__ __forceinline__ void frt_persistent_trace(const DevScene &sc, Io &io, const unsigned int n_items, unsigned int *cursor,
+                                                     const int refill_below, unsigned int &n_rays, unsigned int &n_nodes,
+                                                     unsigned int &n_tris)
+{
+    if (n_items == 0) return;
+    const unsigned int lane = lane_id();
+    Walker<ANY, COUNT> w;
+    uint2 stk[FRT_STACK_SIZE];
+    w.active = false;
+    bool pending = false, more = true;
+    while (true)
+    {
+        if (more)
+        {
+            const unsigned int idle = __ballot_sync(0xFFFFFFFFu, !w.active);
+            unsigned int base = 0;
+            if (lane == 0) base = atomicAdd(cursor, (unsigned int)__popc(idle));
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            const unsigned int my = base + __popc(idle & ((1u << lane) - 1u));
+            if (!w.active && my < n_items)
+            {
+                float3 o, d;
+                io.load(my, o, d);
+                w.begin(sc, o, d);
+                pending = true;
+                ++n_rays;
+            }
+            more = base + __popc(idle) < n_items;
+        }
+        unsigned int act = __ballot_sync(0xFFFFFFFFu, w.active);
+        while (act)
+        {
+            if (w.active) w.round(sc, stk, n_nodes, n_tris);
+            act = __ballot_sync(0xFFFFFFFFu, w.active);
+            if (more && __popc(act) <= refill_below) break;
+        }
+        if (pending && !w.active)
+        {
+            io.store(sc, w);
+            pending = false;
+        }
+        if (!more && act == 0) break;
+    }
+}
+
 // Camera path number `idx` of the tile (sample idx / npix of pixel idx % npix) into slot `slot`.
 __device__ __forceinline__ void frt_generate_path(const KernelArgs &a, const PathPool &pool, const unsigned int slot,
                                                   const unsigned long long idx)

@@ -320,13 +320,13 @@ int frt_trace_rays_device(frt_ctx *ctx, int dev, const void *d_rays, size_t n, v
     frt_hit *h = (frt_hit *)d_hits;
     if (any_hit)
     {
-        if (count) k_trace<true, true><<<d.blocks_trace, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, (unsigned int)n);
-        else k_trace<true, false><<<d.blocks_trace, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, (unsigned int)n);
+        if (count) k_trace<true, true><<<d.blocks_trace_any, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, (unsigned int)n, ctx->wf_refill);
+        else k_trace<true, false><<<d.blocks_trace_any, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, (unsigned int)n, ctx->wf_refill);
     }
     else
     {
-        if (count) k_trace<false, true><<<d.blocks_trace, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, (unsigned int)n);
-        else k_trace<false, false><<<d.blocks_trace, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, (unsigned int)n);
+        if (count) k_trace<false, true><<<d.blocks_trace, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, (unsigned int)n, ctx->wf_refill);
+        else k_trace<false, false><<<d.blocks_trace, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, (unsigned int)n, ctx->wf_refill);
     }
     CU(cudaEventRecord(e1, d.stream));
     CU(cudaEventSynchronize(e1));

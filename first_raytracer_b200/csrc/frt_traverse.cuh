@@ -240,10 +240,12 @@ struct Walker
                     if (conditioned && missed) continue;
                     if (conditioned && uf > du && vf > dv && wf < 1.0f - dw && tf - dt > tmin_hi && tf + dt < best.lo)
                     {
-                        // certainly a hit and certainly the closest so far
-                        best.prim = prim; best.lo = tf - dt; best.hi = tf + dt; best.u = uf; best.v = vf; best.exact = false;
-                        tmax = best.hi;
+                        // certainly a hit and certainly the closest so far (an occlusion query keeps only the
+                        // occluder's index: its Walker carries no hit interval, t, u, v between rounds)
+                        best.prim = prim;
                         if (ANY) { active = false; return; }
+                        best.lo = tf - dt; best.hi = tf + dt; best.u = uf; best.v = vf; best.exact = false;
+                        tmax = best.hi;
                         continue;
                     }
                     e = frt_tri_exact(sc.tris, prim, o.x, o.y, o.z, d.x, d.y, d.z, tmin_exact());
@@ -253,7 +255,7 @@ struct Walker
                 // (sphere.h:41); at an exact tie the triangle the reference meets first (lower index) stays
                 if (ANY)
                 {
-                    if (is_sphere || e.t < tend_d()) { best.prim = prim; best.t = e.t; best.exact = true; active = false; return; }
+                    if (is_sphere || e.t < tend_d()) { best.prim = prim; active = false; return; }
                     continue;
                 }
                 if (!best.exact) // the closest so far was taken on its float32 interval: pin it down now
@@ -289,7 +291,7 @@ struct Walker
         RayHit out;
         out.t = 0.f; out.u = 0.f; out.v = 0.f; out.prim = best.prim;
         if (best.prim == 0xFFFFFFFFu) return out;
-        if (ANY) { out.t = best.exact ? (float)best.t : 0.5f * (best.lo + best.hi); return out; }
+        if (ANY) return out; // only "occluded by prim" is meaningful (path.cpp:50)
         if (!best.exact)
         {
             const ExactHit b = frt_tri_exact(sc.tris, best.prim, o.x, o.y, o.z, d.x, d.y, d.z, tmin_exact());

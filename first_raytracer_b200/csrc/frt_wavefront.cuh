@@ -35,77 +35,55 @@ __device__ __forceinline__ unsigned long long frt_globaltimer()
     return t;
 }
 
-// Persistent-warp ray casting over one shared-memory queue of slot indices.
+// Ray source / hit sink of the CTA-resident pool: queue entry -> slot -> ray; result -> slot.
+template <bool ANY>
+struct WfQueueIo
+{
+    const PathPool &lp;
+    const unsigned int *q;
+    unsigned int slot;
+    __device__ __forceinline__ void load(const unsigned int item, float3 &o, float3 &d)
+    {
+        slot = q[item];
+        if (ANY)
+        {
+            const float4 sa = lp.sh_a[slot], sb = lp.sh_b[slot];
+            o = f3(sa); d = f3(sa.w, sb.x, sb.y);
+        }
+        else
+        {
+            o = f3(lp.ray_o[slot]); d = f3(lp.ray_d[slot]);
+        }
+    }
+    template <class W>
+    __device__ __forceinline__ void store(const DevScene &, W &w)
+    {
+        if (ANY)
+        {
+            // path.cpp:73 — the contribution shade computed is committed when nothing is in the way
+            if (w.best.prim == 0xFFFFFFFFu)
+            {
+                const float4 sb = lp.sh_b[slot];
+                float4 r = lp.rad[slot];
+                r.x += sb.z; r.y += sb.w; r.z += lp.sh_c[slot];
+                lp.rad[slot] = r;
+            }
+        }
+        else
+        {
+            const RayHit h = w.finish_lazy(); // float64 t, u, v are resolved in shade, with the warp converged
+            lp.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
+        }
+    }
+};
+
 template <bool ANY, bool COUNT>
 __device__ __forceinline__ void wf_trace_queue(const DevScene &sc, const PathPool &lp, const unsigned int *q,
                                                const unsigned int n_items, unsigned int *cursor, const int refill_below,
                                                unsigned int &n_rays, unsigned int &n_nodes, unsigned int &n_tris)
 {
-    if (n_items == 0) return;
-    const unsigned int lane = lane_id();
-    Walker<ANY, COUNT> w;
-    uint2 stk[FRT_STACK_SIZE];
-    w.active = false;
-    bool pending = false, more = true;
-    unsigned int slot = 0;
-    while (true)
-    {
-        if (more)
-        {
-            // hand every idle lane the next queue entry: one shared-memory atomic per warp
-            const unsigned int idle = __ballot_sync(0xFFFFFFFFu, !w.active);
-            unsigned int base = 0;
-            if (lane == 0) base = atomicAdd(cursor, (unsigned int)__popc(idle));
-            base = __shfl_sync(0xFFFFFFFFu, base, 0);
-            const unsigned int my = base + __popc(idle & ((1u << lane) - 1u));
-            if (!w.active && my < n_items)
-            {
-                slot = q[my];
-                float3 o, d;
-                if (ANY)
-                {
-                    const float4 sa = lp.sh_a[slot], sb = lp.sh_b[slot];
-                    o = f3(sa); d = f3(sa.w, sb.x, sb.y);
-                }
-                else
-                {
-                    o = f3(lp.ray_o[slot]); d = f3(lp.ray_d[slot]);
-                }
-                w.begin(sc, o, d);
-                pending = true;
-                ++n_rays;
-            }
-            more = base + __popc(idle) < n_items;
-        }
-        unsigned int act = __ballot_sync(0xFFFFFFFFu, w.active);
-        while (act)
-        {
-            if (w.active) w.round(sc, stk, n_nodes, n_tris);
-            act = __ballot_sync(0xFFFFFFFFu, w.active);
-            if (more && __popc(act) <= refill_below) break;
-        }
-        if (pending && !w.active)
-        {
-            if (ANY)
-            {
-                // path.cpp:73 — the contribution shade computed is committed when nothing is in the way
-                if (w.best.prim == 0xFFFFFFFFu)
-                {
-                    const float4 sb = lp.sh_b[slot];
-                    float4 r = lp.rad[slot];
-                    r.x += sb.z; r.y += sb.w; r.z += lp.sh_c[slot];
-                    lp.rad[slot] = r;
-                }
-            }
-            else
-            {
-                const RayHit h = w.finish_lazy();
-                lp.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
-            }
-            pending = false;
-        }
-        if (!more && act == 0) break;
-    }
+    WfQueueIo<ANY> io{lp, q, 0u};
+    frt_persistent_trace<ANY, COUNT>(sc, io, n_items, cursor, refill_below, n_rays, n_nodes, n_tris);
 }
 
 // P = slots per CTA (a multiple of 32); refill_below = a warp fetches new rays once this many lanes or
