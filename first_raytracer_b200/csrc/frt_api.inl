@@ -34,7 +34,7 @@ int frt_create(frt_ctx **out, const int *devices, int n)
     if (const char *s = getenv("FRT_POLL_EVERY")) c->poll_every = std::max(1, atoi(s));
     if (const char *s = getenv("FRT_WF_SLOTS")) c->wf_slots = (unsigned int)std::min(1568, std::max(32, atoi(s) / 32 * 32));
     if (const char *s = getenv("FRT_WF_CONFIG")) c->wf_config = std::min(n_wf_configs - 1, std::max(0, atoi(s)));
-    if (const char *s = getenv("FRT_WF_SORT")) c->wf_sort = atoi(s) != 0;
+    if (const char *s = getenv("FRT_WF_SORT")) c->wf_sort = atoi(s) & 3;
     if (const char *s = getenv("FRT_WF_REFILL")) c->wf_refill = std::min(31, std::max(0, atoi(s)));
     for (int i = 0; i < n; ++i)
     {
@@ -188,6 +188,10 @@ int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *s)
         if ((rc = upload_array(ctx, &d.d_mats, s->materials, s->n_materials)) != FRT_OK) return rc;
         if ((rc = upload_array(ctx, &d.d_lights, s->lights, s->n_lights)) != FRT_OK) return rc;
     }
+    uint32_t bsdf_types = 0;
+    for (uint32_t i = 0; i < s->n_materials; ++i)
+        if (s->materials[i].type != FRT_MAT_DIFFUSE_LIGHT) bsdf_types |= 1u << s->materials[i].type;
+    ctx->multi_bsdf = (bsdf_types & (bsdf_types - 1)) != 0;
     ctx->have_scene = true;
     return FRT_OK;
 }

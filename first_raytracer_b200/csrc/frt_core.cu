@@ -63,7 +63,9 @@ struct frt_ctx
     unsigned int wf_slots = 1024;    // CTA-resident pool: slots per CTA (multiple of 32)
     int wf_config = 4;               // index into wf_configs[]: 512 threads, one CTA per SM (measured best)
     int wf_refill = 24;              // dynamic fetch threshold (lanes still traversing)
-    int wf_sort = 1;                 // bin queued rays by where they start
+    int wf_sort = -1;                // bit 0: bin queued rays by where they start; bit 1: shade grouped by material;
+                                     // -1 = bit 0 always, bit 1 when the scene has more than one BSDF type
+    bool multi_bsdf = false;
     int poll_every = 16;
     frt_stats stats{};
 };

@@ -133,7 +133,8 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
             const unsigned int grid = (unsigned int)std::min<unsigned long long>((unsigned long long)d.blocks_wavefront, want);
             k_reset_tile<<<1, 1, 0, d.stream>>>(d.d_ctr, total);
             const WfConfig &wc = wf_configs[ctx->wf_config];
-            (count ? wc.counting : wc.plain)<<<grid, wc.threads, smem, d.stream>>>(a, ctx->wf_slots, ctx->wf_refill, ctx->wf_sort);
+            (count ? wc.counting : wc.plain)<<<grid, wc.threads, smem, d.stream>>>(a, ctx->wf_slots, ctx->wf_refill,
+                                                                                     ctx->wf_sort >= 0 ? ctx->wf_sort : (ctx->multi_bsdf ? 3 : 1));
             CU(cudaGetLastError());
             CU(cudaEventRecord(d.ev_end, d.stream));
             d.launches += 2;

@@ -18,12 +18,13 @@
 #pragma once
 #include "frt_shade.cuh"
 
-#define FRT_WF_SLOT_BYTES 145u // + one key byte per slot for the origin binning
+#define FRT_WF_SLOT_BYTES 148u // + origin-bin key (1 B), material key (1 B), shade order (2 B) per slot
 
 #define FRT_WF_BINS 64
 struct WfShared
 {
     unsigned int hist_ext[FRT_WF_BINS], hist_sh[FRT_WF_BINS]; // ray-origin bins: counts, then write offsets
+    unsigned int hist_mat[8];                                 // shade order: miss + the six material types
     unsigned long long base; // first sample index of this iteration's run
     unsigned int n_ext, n_free, n_shadow, n_new, cur_ext, cur_shadow, exhausted, pad;
 };
@@ -169,14 +170,74 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelA
             // lies on is a spatial key), so a warp of the next trace stage pulls rays that leave the same
             // part of the scene: counting sort in shared memory, hist -> exclusive scan -> scatter.
             unsigned char *key = reinterpret_cast<unsigned char *>(shadow_q + P); // P bytes: bin | 0x80 shadow, 0xFF = not queued
+            unsigned char *mkey = key + P;                                        // P bytes: what the path hit (material type)
+            unsigned short *order = reinterpret_cast<unsigned short *>(mkey + P); // P entries: slots in shading order
+            const bool by_material = sort_rays & 2;
             if (tid < FRT_WF_BINS) { sh.hist_ext[tid] = 0; sh.hist_sh[tid] = 0; }
-            __syncthreads();
-            const unsigned int bin_div = (max(a.sc.n_tris, a.sc.n_spheres) + FRT_WF_BINS - 1) / FRT_WF_BINS;
-            for (unsigned int s0 = 0; s0 < P; s0 += THREADS)
+            if (by_material)
             {
-                const unsigned int slot = s0 + tid;
-                if (slot >= P) break;
-                const unsigned int r = frt_shade_vertex(a, lp, slot, nonfinite);
+                // Scenes with several BSDFs: shade the slots grouped by the material they hit, so a warp runs one
+                // BSDF's code (veach_mi: conductor plates + lambertian floor + lights ran at 8/32 lanes before).
+                // Counting sort over 8 keys, one shared-memory atomic per distinct key per warp (match.any).
+                if (tid < 8) sh.hist_mat[tid] = 0;
+                for (unsigned int slot = tid; slot < P; slot += THREADS) key[slot] = 0xFFu;
+                __syncthreads();
+                const unsigned int n32 = (n_ext + 31u) & ~31u;
+                for (int pass = 0; pass < 2; ++pass)
+                {
+                    for (unsigned int i = tid; i < n32; i += THREADS)
+                    {
+                        unsigned int k = 0xFFu, slot = 0;
+                        if (i < n_ext)
+                        {
+                            slot = ext_q[i];
+                            if (pass == 0)
+                            {
+                                const unsigned int prim = __float_as_uint(lp.hit[slot].w);
+                                k = 0;
+                                if (prim != 0xFFFFFFFFu)
+                                {
+                                    const unsigned int idx = prim & FRT_LEAF_FIRST_MASK;
+                                    const unsigned int mat = (prim & FRT_CHILD_SPHERE)
+                                                                 ? __float_as_uint(__ldg(a.sc.spheres + 2 * idx + 1).x)
+                                                                 : __float_as_uint(__ldg(a.sc.tris + 3 * (size_t)idx + 1).w);
+                                    k = 1u + min(a.sc.materials[mat].type, 6u);
+                                }
+                                mkey[slot] = (unsigned char)k;
+                            }
+                            else
+                                k = mkey[slot];
+                        }
+                        const unsigned int peers = __match_any_sync(0xFFFFFFFFu, k);
+                        const unsigned int leader = __ffs(peers) - 1, rank = __popc(peers & ((1u << lane_id()) - 1u));
+                        unsigned int base_k = 0;
+                        if (k != 0xFFu && lane_id() == leader) base_k = atomicAdd(&sh.hist_mat[k], (unsigned int)__popc(peers));
+                        base_k = __shfl_sync(0xFFFFFFFFu, base_k, leader);
+                        if (pass == 1 && k != 0xFFu) order[base_k + rank] = (unsigned short)slot;
+                    }
+                    __syncthreads();
+                    if (pass == 0)
+                    {
+                        if (tid == 0)
+                        {
+                            unsigned int run = 0;
+                            for (int b = 0; b < 8; ++b) { const unsigned int c = sh.hist_mat[b]; sh.hist_mat[b] = run; run += c; }
+                        }
+                        __syncthreads();
+                    }
+                }
+            }
+            else
+                __syncthreads();
+            const unsigned int bin_div = (max(a.sc.n_tris, a.sc.n_spheres) + FRT_WF_BINS - 1) / FRT_WF_BINS;
+            const unsigned int n_shade = by_material ? ((n_ext + 31u) & ~31u) : P;
+            for (unsigned int s0 = 0; s0 < n_shade; s0 += THREADS)
+            {
+                const unsigned int idx = s0 + tid; // bounds are multiples of 32: whole warps fall off the end together
+                if (idx >= n_shade) break;
+                const bool valid = !by_material || idx < n_ext;
+                const unsigned int slot = by_material ? (valid ? order[idx] : 0u) : idx;
+                const unsigned int r = valid ? frt_shade_vertex(a, lp, slot, nonfinite) : 0u;
                 const bool ended = r & FRT_SHADE_TERMINATED, goes_on = (r & FRT_SHADE_WAS_ALIVE) && !ended;
                 const unsigned int fi = warp_append(ended, &sh.n_free);
                 if (ended) free_q[fi] = slot;
@@ -187,7 +248,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelA
                     atomicAdd(&sh.hist_ext[k], 1u);
                     if (r & FRT_SHADE_SHADOW) { atomicAdd(&sh.hist_sh[k], 1u); k |= 0x80u; }
                 }
-                key[slot] = (unsigned char)k;
+                if (valid) key[slot] = (unsigned char)k;
             }
             __syncthreads();
             if (tid < 32)
