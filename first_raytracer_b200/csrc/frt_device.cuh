@@ -54,6 +54,7 @@ __device__ __forceinline__ float3 cross(float3 a, float3 b)
     return f3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
 }
 __device__ __forceinline__ float length(float3 a) { return sqrtf(dot(a, a)); }
-__device__ __forceinline__ float3 unit_vector(float3 a) { return a / length(a); } // geometry.h:445
+// geometry.h:445 (v / v.length()) as one reciprocal square root and three multiplies: within 2 ulp per component
+__device__ __forceinline__ float3 unit_vector(float3 a) { return a * rsqrtf(dot(a, a)); }
 __device__ __forceinline__ bool nonzero(float3 a) { return a.x != 0.f || a.y != 0.f || a.z != 0.f; }
 __device__ __forceinline__ float3 arr3(const float *p) { return f3(p[0], p[1], p[2]); }
