@@ -321,8 +321,13 @@ def main():
     if rank == 0 and not args.no_roofline:
         roof = roofline_pass(ctx, api, (0, max(1, spp // world)), peaks, base_flags, stream)
     ctx.close()
+    # The end-to-end leg runs renderer<gpu_path_integrator> with n_gpus = world inside rank 0's process; the other
+    # ranks must leave their GPUs idle meanwhile, so they wait on a CPU (gloo) barrier: an NCCL barrier spins a
+    # kernel on the waiting GPU.
+    cpu_group = dist.new_group(backend="gloo") if world > 1 else None
     if world > 1:
-        dist.barrier()
+        torch.cuda.synchronize()
+        dist.barrier(group=cpu_group)
     if rank == 0 and not args.no_e2e:
         e2e_val, e2e_mean, e2e_s = e2e_pass(scene, max(1, min(steps, 3)), world, spp)
         e2e = {"value": e2e_val, "unit": "Msamples/s", "h2d_bytes_per_step": scene_bytes(scene),
@@ -330,7 +335,7 @@ def main():
                "mean_radiance": e2e_mean,
                "call": "renderer<gpu_path_integrator>::Render via frth_render (host scene in, host film out)"}
     if world > 1:
-        dist.barrier()
+        dist.barrier(group=cpu_group)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             probe, cores = cpu_reference_sample(spp=1, ystep=16)
