@@ -309,7 +309,10 @@ struct Walker
         out.prim = best.prim;
         if (best.prim == 0xFFFFFFFFu || best.exact) { out.t = (float)best.t; out.u = best.u; out.v = best.v; return out; }
         out.t = 0.5f * (best.lo + best.hi); out.u = best.u; out.v = best.v;
-        out.prim = best.prim | FRT_HIT_INEXACT;
+        // The interval is the conservative margin (1e-5-scale), at least ten times the real float32 error: when
+        // it is below 1e-4 t the float32 t, u, v are within ~1e-6 of the float64 ones, which is all shading
+        // needs (it continues in float32 anyway).  Only wider intervals are resolved in float64.
+        if (best.hi - best.lo > 1e-4f * best.lo) out.prim = best.prim | FRT_HIT_INEXACT;
         return out;
     }
 };
