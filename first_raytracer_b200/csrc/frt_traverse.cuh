@@ -123,7 +123,9 @@ struct Walker
         best.prim = 0xFFFFFFFFu; best.u = best.v = 0.f; best.t = tend_d(); best.exact = true;
         best.lo = __double2float_rd(tend_d()); best.hi = __double2float_ru(tend_d());
         tmax = best.hi; // culling bound
-        idx = 1.0f / d.x; idy = 1.0f / d.y; idz = 1.0f / d.z;
+        // correctly rounded reciprocals (the library is built with -prec-div=false): the padding of the float32
+        // boxes (host/flatten.h) is sized for a slab test whose only error is rounding
+        idx = __frcp_rn(d.x); idy = __frcp_rn(d.y); idz = __frcp_rn(d.z);
         oox = o.x * idx; ooy = o.y * idy; ooz = o.z * idz;
         sx = idx < 0.0f ? 1 : 0; sy = idy < 0.0f ? 1 : 0; sz = idz < 0.0f ? 1 : 0;
         sp = 0;
