@@ -7,6 +7,7 @@
 #pragma once
 #include <stdexcept>
 #include <algorithm>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -35,7 +36,38 @@ struct gpu_path_integrator
 
     constexpr static bool using_custom_viewer = false;
 
+    // The device context (streams, counters, peer access between the GPUs) is kept between renders of one
+    // process: creating it costs more than a 1080p x 128 spp share of an 8-GPU render.  Scene and film are
+    // per render.  Call this before exit (frt_main does) to give the devices back explicitly.
+    static void release_cached_context()
+    {
+        std::lock_guard<std::mutex> lock(cache().mutex);
+        if (cache().ctx) frt_destroy(cache().ctx);
+        cache().ctx = nullptr;
+    }
+
 private:
+    struct ctx_cache { std::mutex mutex; frt_ctx *ctx = nullptr; int n_gpus = 0; };
+    static ctx_cache &cache() { static ctx_cache c; return c; }
+    static frt_ctx *acquire(int n)
+    {
+        std::lock_guard<std::mutex> lock(cache().mutex);
+        frt_ctx *ctx = cache().ctx;
+        cache().ctx = nullptr;
+        if (ctx && cache().n_gpus == n) return ctx;
+        if (ctx) frt_destroy(ctx);
+        ctx = nullptr;
+        check(nullptr, frt_create(&ctx, nullptr, n), "frt_create");
+        return ctx;
+    }
+    static void give_back(frt_ctx *ctx, int n)
+    {
+        std::lock_guard<std::mutex> lock(cache().mutex);
+        if (cache().ctx) { frt_destroy(ctx); return; } // another render finished first: keep one
+        cache().ctx = ctx;
+        cache().n_gpus = n;
+    }
+
     static void check(frt_ctx *ctx, int rc, const char *what)
     {
         if (rc == FRT_OK) return;
@@ -49,9 +81,9 @@ private:
         frt_flattener flattener(prim_ids, max_leaf);
         const frt_flat_scene flat = flattener.flatten(scene);
         const frt_scene_desc desc = flat.desc();
-        frt_ctx *ctx = nullptr;
-        check(nullptr, frt_create(&ctx, nullptr, n_gpus), "frt_create");
+        frt_ctx *ctx = acquire(n_gpus);
         check(ctx, frt_set_flags(ctx, flags), "frt_set_flags");
+        check(ctx, frt_clear_film(ctx), "frt_clear_film");
         check(ctx, frt_upload_scene(ctx, &desc), "frt_upload_scene");
         frt_tile tile;
         tile.nx = (uint32_t)film->nx; tile.ny = (uint32_t)film->ny;
@@ -61,7 +93,7 @@ private:
         check(ctx, frt_render_tile(ctx, &tile), "frt_render_tile");
         std::vector<float> sums((size_t)film->nx * film->ny * 3);
         check(ctx, frt_readback(ctx, sums.data(), sums.size(), &stats), "frt_readback");
-        frt_destroy(ctx);
+        give_back(ctx, n_gpus);
         // path.cpp:143 / viewer.cpp:109-132: the film divides the sum by ns and tonemaps.  As in the
         // reference every pixel is written by exactly one thread; rows are dealt to the host cores
         // (the per-pixel pow/exp of the tonemap is ~0.1 s for a 1080p film on one core).

@@ -59,6 +59,7 @@ int main(int argc, const char **argv)
                   << " shadow rays in " << st.render_ms << " ms device time = "
                   << (st.closest_rays + st.shadow_rays) / (st.render_ms * 1e3) << " Mrays/s" << std::endl;
         film_viewer.save_and_destroy(out + "_" + std::to_string(render_time) + "s");
+        gpu_path_integrator::release_cached_context();
     }
     catch (const std::exception &e)
     {

@@ -99,3 +99,32 @@ def test_split_spp_ranges_sum_to_whole(built):
     ctx.close()
     assert np.allclose(whole, parts, rtol=1e-4, atol=1e-5)
     assert whole.sum() > 0
+
+
+def test_in_process_multi_gpu_matches_single(built):
+    """frt_create(n > 1): the sample range is split over the devices and the films are summed on
+    device 0 with peer loads — same image as one device (same samples, different summation order)."""
+    import torch
+    n = min(torch.cuda.device_count(), 4)
+    if n < 2:
+        pytest.skip("needs at least two GPUs")
+    scene = api.HostScene("cornell", 1.0, 2)
+    one, st1, _ = scene.render(96, 96, 10, seed=11, n_gpus=1)
+    many, stn, _ = scene.render(96, 96, 10, seed=11, n_gpus=n)
+    again, _, _ = scene.render(96, 96, 10, seed=11, n_gpus=n)  # cached context, film cleared
+    assert stn["samples"] == st1["samples"] == 96 * 96 * 10
+    assert stn["closest_rays"] == st1["closest_rays"]
+    assert np.allclose(one, many, rtol=1e-4, atol=1e-6)
+    assert np.allclose(many, again, rtol=1e-4, atol=1e-6)
+
+
+def test_repeated_renders_reuse_the_context(built):
+    """renderer<gpu_path_integrator> keeps its device context between renders: a second render of another
+    size and scene must not see the first one's film or scene."""
+    a = api.HostScene("cornell", 1.0, 2)
+    b = api.HostScene("veach", 1.5, 2)
+    img_a, _, _ = a.render(64, 64, 4, seed=3)
+    img_b, _, _ = b.render(96, 64, 4, seed=3)
+    img_a2, _, _ = a.render(64, 64, 4, seed=3)
+    assert img_b.shape == (64, 96, 3) and np.isfinite(img_b).all() and img_b.mean() > 0
+    assert np.allclose(img_a, img_a2, rtol=1e-4, atol=1e-6)
