@@ -196,9 +196,11 @@ struct TraceIo
 // frt_trace_rays.  Closest hit: persistent warps over a global cursor with dynamic fetch
 // (frt_persistent_trace): on the 10M-triangle soup 308 -> 467 Mrays/s.  Occlusion queries end early and
 // carry little state; for them plain batches of 32 rays measured faster (357 vs 333 Mrays/s), kept.
+// Register budget: closest hit 4 CTAs / SM (no spills); occlusion queries 8 (64 registers; measured on the soup:
+// 351 -> 386 Mrays/s; for closest hit 5 / 6 / 8 CTAs measured within 3 % of 4).
 template <bool ANY, bool COUNT>
-__global__ void __launch_bounds__(128) k_trace(DevScene sc, Counters *ctr, const float2 *rays, frt_hit *hits, unsigned int n,
-                                               int refill_below)
+__global__ void __launch_bounds__(128, ANY ? 8 : 4) k_trace(DevScene sc, Counters *ctr, const float2 *rays, frt_hit *hits,
+                                                                    unsigned int n, int refill_below)
 {
     unsigned int n_rays = 0, n_nodes = 0, n_tris = 0;
     TraceIo io{rays, hits, 0u};

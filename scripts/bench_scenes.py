@@ -52,7 +52,7 @@ def morton_order(o):
 def soup():
     n_tri = int(float(os.environ.get("SOUP_TRIS", "1e7"))); n_rays = int(os.environ.get("SOUP_RAYS", str(2 ** 26)))
     t0 = time.time(); tri = api.soup_triangles(n_tri); t1 = time.time()
-    scene = api.HostScene(soup=tri, fast_bvh=True, max_leaf=int(os.environ.get("SOUP_LEAF", "4"))); t2 = time.time()
+    scene = api.HostScene(soup=tri, fast_bvh=True, max_leaf=int(os.environ.get("SOUP_LEAF", "2"))); t2 = time.time()
     info = scene.info() if callable(scene.info) else scene.info
     ctx = api.Context(devices=[0]); ctx.upload(scene); t3 = time.time()
     dev = torch.device("cuda", 0)
