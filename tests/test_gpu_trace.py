@@ -60,6 +60,33 @@ def test_closest_hit_matches_reference(built, name, aspect, max_leaf):
     ctx.close()
 
 
+@pytest.mark.parametrize("name,aspect", [("cornell", 16 / 9), ("teapot", 16 / 9)])
+def test_one_million_ray_set(built, name, aspect):
+    """BASELINE.json's first correctness check at its full size: a fixed 2^20-ray set (half camera rays over
+    a stratified pixel grid, half incoherent), primitive ids >= 99.99 % equal to the reference's
+    hitable::hit and t within 1e-5 relative — with the shipping leaf size (2)."""
+    if not refutil.have_ref():
+        pytest.skip("oracle/_ref not built")
+    scene = api.HostScene(name, aspect, 2)
+    info = scene.info
+    cam = scene.camera_rays(1024, 512)
+    rnd = refutil.random_rays((1 << 20) - cam.shape[0], np.array(info["bounds_lo"]), np.array(info["bounds_hi"]), seed=0x5EED)
+    rays = np.concatenate([cam, rnd])
+    assert rays.shape[0] == 1 << 20
+    ctx = api.Context()
+    ctx.upload(scene)
+    hits, ms = ctx.trace(rays)
+    ref, _ = refutil.ref_trace(name, aspect, rays)
+    _check_closest(scene, rays, hits, ref["prim"], ref["t"], f"{name} 2^20 rays leaf=2 ({ms:.3f} ms)")
+    segs = refutil.segment_rays(1 << 20, np.array(info["bounds_lo"]), np.array(info["bounds_hi"]), seed=0x5EEE)
+    occ, _ = ctx.trace(segs, any_hit=True)
+    ref_occ, _ = refutil.ref_trace(name, aspect, segs, shadow=True)
+    agree = ((occ["prim_id"] >= 0) == (ref_occ["prim"] >= 0)).mean()
+    print(f"{name} 2^20 shadow segments: any-hit agreement {agree:.6f}")
+    assert agree >= 0.9999
+    ctx.close()
+
+
 @pytest.mark.parametrize("name,aspect", SCENES)
 def test_closest_and_any_hit_match_golden(built, name, aspect):
     g = np.load(refutil.GOLDEN / f"trace_{name}.npz")
