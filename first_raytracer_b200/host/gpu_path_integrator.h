@@ -7,6 +7,9 @@
 #pragma once
 #include <stdexcept>
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -78,10 +81,21 @@ private:
 
     void run(Scene *scene, viewer *film)
     {
+        using clk = std::chrono::steady_clock;
+        const bool timing = std::getenv("FRT_HOST_TIMING") != nullptr;
+        auto t_prev = clk::now();
+        auto lap = [&](const char *what) {
+            if (!timing) return;
+            const auto now = clk::now();
+            std::fprintf(stderr, "[frt host] %-10s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_prev).count());
+            t_prev = now;
+        };
         frt_flattener flattener(prim_ids, max_leaf);
         const frt_flat_scene flat = flattener.flatten(scene);
         const frt_scene_desc desc = flat.desc();
+        lap("flatten");
         frt_ctx *ctx = acquire(n_gpus);
+        lap("context");
         check(ctx, frt_set_flags(ctx, flags), "frt_set_flags");
         check(ctx, frt_clear_film(ctx), "frt_clear_film");
         check(ctx, frt_upload_scene(ctx, &desc), "frt_upload_scene");
@@ -90,9 +104,12 @@ private:
         tile.x0 = tile.y0 = 0; tile.w = tile.nx; tile.h = tile.ny;
         tile.spp_begin = 0; tile.spp_end = (uint32_t)film->ns;
         tile.seed = seed; tile.max_depth = max_depth;
+        lap("upload");
         check(ctx, frt_render_tile(ctx, &tile), "frt_render_tile");
+        lap("launch");
         std::vector<float> sums((size_t)film->nx * film->ny * 3);
         check(ctx, frt_readback(ctx, sums.data(), sums.size(), &stats), "frt_readback");
+        lap("readback");
         give_back(ctx, n_gpus);
         // path.cpp:143 / viewer.cpp:109-132: the film divides the sum by ns and tonemaps.  As in the
         // reference every pixel is written by exactly one thread; rows are dealt to the host cores
@@ -112,6 +129,7 @@ private:
         for (int w = 1; w < n_workers; ++w) workers.emplace_back(feed, w);
         feed(0);
         for (std::thread &t : workers) t.join();
+        lap("film");
         Scene::num_rays_traversed = (unsigned int)(stats.closest_rays + stats.shadow_rays);
         Scene::num_ray_box_intersections = (unsigned int)stats.node_visits;
         Scene::num_ray_tri_intersections = (unsigned int)stats.tri_tests;

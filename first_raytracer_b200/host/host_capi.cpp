@@ -1,4 +1,7 @@
 // C ABI of the host layer (include/frt_host.h).
+#include <thread>
+#include <vector>
+#include <algorithm>
 #include "../../include/frt_host.h"
 #include <chrono>
 #include <cstring>
@@ -165,7 +168,18 @@ int frth_render(frth_scene *s, int n_gpus, int nx, int ny, uint32_t ns, uint32_t
         render.prim_ids = &s->ids.id;
         const double secs = render.Render(s->scene.get(), film);
         if (rgb_mean)
-            for (size_t i = 0; i < (size_t)nx * ny * 3; ++i) rgb_mean[i] = (float)film.fout_image[i];
+        {
+            // viewer::fout_image (double) -> caller's float32 buffer, dealt to the host cores
+            const size_t n = (size_t)nx * ny * 3;
+            const unsigned n_workers = std::max(1u, std::min(std::thread::hardware_concurrency(), (unsigned)(n >> 18) + 1u));
+            auto convert = [&](unsigned w) {
+                for (size_t i = n * w / n_workers, e = n * (w + 1) / n_workers; i < e; ++i) rgb_mean[i] = (float)film.fout_image[i];
+            };
+            std::vector<std::thread> workers;
+            for (unsigned w = 1; w < n_workers; ++w) workers.emplace_back(convert, w);
+            convert(0);
+            for (std::thread &t : workers) t.join();
+        }
         if (stats) *stats = render.stats;
         if (wall_seconds) *wall_seconds = secs;
         return FRT_OK;
