@@ -41,6 +41,9 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-roofline", action="store_true", help="skip the per-kernel timing pass (profiling runs)")
+    ap.add_argument("--scene", default="cornell", choices=["cornell", "veach", "teapot"],
+                    help="other BASELINE.json configs at N GPUs (veach: config 3, teapot: config 4, 256 spp); "
+                         "the contract bench is the default")
     ap.add_argument("--streamed-pool", action="store_true",
                     help="A/B only: the first implementation (global-memory path pool, 4 kernels per iteration)")
     return ap.parse_args()
@@ -301,7 +304,14 @@ def e2e_pass(scene, steps, n_gpus, spp):
 
 
 def main():
+    global SCENE, SPP, WORKLOAD
     args = parse()
+    if args.scene != "cornell":
+        SCENE, SPP = args.scene, 256
+        WORKLOAD = {"veach": f"veach_mi (GGX rough_conductor plates, 5 sphere lights) {NX}x{NY} {SPP} spp NEE+MIS",
+                    "teapot": f"mesh scene (teapot stand-in, 15 704 triangles) {NX}x{NY} {SPP} spp NEE+MIS"}[SCENE]
+        if args.spp == 1024:
+            args.spp = SPP
     if args.impl == "reference":
         return run_reference(args)
     from first_raytracer_b200 import api
@@ -349,7 +359,8 @@ def main():
             cpu = {"value": None, "unit": "Msamples/s", "cores": 0, "kind": "reference", "sample": f"failed: {exc}"}
     if rank == 0:
         line = {
-            "metric": "samples/s (1080p Cornell NEE+MIS)", "value": value, "unit": "Msamples/s",
+            "metric": "samples/s (1080p Cornell NEE+MIS)" if SCENE == "cornell" else f"samples/s (1080p {SCENE} NEE+MIS)",
+            "value": value, "unit": "Msamples/s",
             "mrays_per_s": (res["closest"] + res["shadow"]) / total_s / 1e6,
             "rays_per_sample": (res["closest"] + res["shadow"]) / max(1, res["samples"]),
             "n_gpus": world, "steps": steps, "warmup": args.warmup, "ms_per_step": res["total_ms"] / steps,
