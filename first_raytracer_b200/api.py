@@ -39,7 +39,11 @@ class FrtError(RuntimeError):
 
 class frt_tile(C.Structure):
     _fields_ = [(n, C.c_uint32) for n in
-                ("nx", "ny", "x0", "y0", "w", "h", "spp_begin", "spp_end", "seed", "max_depth")]
+                ("nx", "ny", "x0", "y0", "w", "h", "spp_begin", "spp_end", "seed", "max_depth", "integrator", "reserved")]
+
+
+FRT_INTEGRATOR_PATH, FRT_INTEGRATOR_AO, FRT_INTEGRATOR_NORMALS = 0, 1, 2
+INTEGRATORS = {"path": FRT_INTEGRATOR_PATH, "ao": FRT_INTEGRATOR_AO, "normals": FRT_INTEGRATOR_NORMALS}
 
 
 class frt_stats(C.Structure):
@@ -76,7 +80,7 @@ class frt_scene_desc(C.Structure):
                 ("n_tris", C.c_uint32), ("n_spheres", C.c_uint32), ("tris", C.c_void_p),
                 ("tri_normals", C.c_void_p), ("spheres", C.c_void_p), ("n_materials", C.c_uint32),
                 ("n_lights", C.c_uint32), ("materials", C.c_void_p), ("lights", C.c_void_p),
-                ("camera", frt_camera), ("env_color", C.c_float * 3), ("reserved", C.c_uint32)]
+                ("camera", frt_camera), ("env_color", C.c_float * 3), ("ao_t_max", C.c_float)]
 
 
 RAY_DTYPE = np.dtype([("o", "<f4", 3), ("d", "<f4", 3)])
@@ -221,8 +225,9 @@ class HostScene:
             raise FrtError("frth_camera_rays failed")
         return rays
 
-    def render(self, nx: int, ny: int, spp: int, seed: int = 1, n_gpus: int = 1, flags: int = 0):
-        """renderer<gpu_path_integrator>::Render → (mean image [ny,nx,3] row 0 = bottom, stats, seconds)."""
+    def render(self, nx: int, ny: int, spp: int, seed: int = 1, n_gpus: int = 1, flags: int = 0, integrator: str = "path"):
+        """renderer<gpu_{path,ao,normals}_integrator>::Render → (mean image [ny,nx,3] row 0 = bottom, stats, seconds)."""
+        flags = (flags & 0xFF) | (INTEGRATORS[integrator] << 8)
         img = np.zeros((ny, nx, 3), dtype=np.float32)
         st = frt_stats()
         secs = C.c_double()
@@ -280,9 +285,9 @@ class Context:
     def upload_desc(self, desc: frt_scene_desc):
         self._check(self._frt.frt_upload_scene(self.handle, C.addressof(desc)), "frt_upload_scene")
 
-    def render_tile(self, nx, ny, spp_begin, spp_end, seed=1, max_depth=34, rect=None):
+    def render_tile(self, nx, ny, spp_begin, spp_end, seed=1, max_depth=34, rect=None, integrator="path"):
         x0, y0, w, h = rect if rect else (0, 0, nx, ny)
-        t = frt_tile(nx, ny, x0, y0, w, h, spp_begin, spp_end, seed, max_depth)
+        t = frt_tile(nx, ny, x0, y0, w, h, spp_begin, spp_end, seed, max_depth, INTEGRATORS[integrator], 0)
         self._check(self._frt.frt_render_tile(self.handle, C.byref(t)), "frt_render_tile")
         self.nx, self.ny = nx, ny
 

@@ -177,6 +177,7 @@ int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *s)
     v.n_materials = s->n_materials; v.n_lights = s->n_lights;
     v.cam = s->camera;
     memcpy(v.env, s->env_color, sizeof v.env);
+    ctx->ao_t_max = s->ao_t_max;
     for (Device &d : ctx->dev)
     {
         CU(cudaSetDevice(d.ordinal));

@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <cmath>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -66,6 +67,7 @@ struct frt_ctx
     int wf_sort = -1;                // bit 0: bin queued rays by where they start; bit 1: shade grouped by material;
                                      // -1 = bit 0 always, bit 1 when the scene has more than one BSDF type
     bool multi_bsdf = false;
+    float ao_t_max = 0.f;
     int poll_every = 16;
     frt_stats stats{};
 };
@@ -253,9 +255,14 @@ const WfConfig wf_configs[] = {WF_CFG(256, 2), WF_CFG(128, 4), WF_CFG(128, 5), W
                                WF_CFG(384, 1), WF_CFG(448, 1), WF_CFG(192, 2)};
 const int n_wf_configs = (int)(sizeof wf_configs / sizeof wf_configs[0]);
 
-DevScene device_view(const frt_ctx *ctx, const Device &d)
+// `any_tend` = upper end of occlusion queries: path.cpp:50 passes 1 - SHADOW_EPSILON (a float literal, util.h:11)
+DevScene device_view(const frt_ctx *ctx, const Device &d, double any_tend = 1.0 - (double)1e-3f)
 {
     DevScene sc = ctx->host_view;
+    sc.any_tend = any_tend;
+    const float f = (float)any_tend; // round to nearest, then step outwards: float32 brackets of the double
+    sc.any_tend_lo = (double)f <= any_tend ? f : std::nextafter(f, -3.0e38f);
+    sc.any_tend_hi = (double)f >= any_tend ? f : std::nextafter(f, 3.0e38f);
     sc.nodes = (const float4 *)d.d_nodes;
     sc.tris = (const float4 *)d.d_tris;
     sc.tri_normals = (const float4 *)d.d_normals;

@@ -22,6 +22,10 @@ struct DevScene
     uint32_t n_nodes, n_tris, n_spheres, n_materials, n_lights;
     frt_camera cam;
     float env[3];
+    // upper end of an occlusion query (uniform per launch): 1 - SHADOW_EPSILON for path.cpp:50 and the ray-cast
+    // entry, ao_t_max for ao.cpp:22; with its float32 brackets
+    double any_tend;
+    float any_tend_lo, any_tend_hi;
 };
 
 struct Counters // one per device, device memory; mirrored to pinned host memory when polled

@@ -11,7 +11,8 @@
 #include "frt_bsdf.cuh"
 
 #define FRT_FLAG_ALIVE 1u
-#define FRT_FLAG_PREV_UNWEIGHTED 2u // previous vertex was modified_phong / metal / dielectric (path.cpp:18-22)
+#define FRT_FLAG_PREV_UNWEIGHTED 2u
+#define FRT_FLAG_FINISH 4u          // ao: the occlusion ray is in flight, splat at the next shade (no more vertices) // previous vertex was modified_phong / metal / dielectric (path.cpp:18-22)
 #define FRT_DEPTH_SHIFT 8
 
 struct PathPool
@@ -35,6 +36,7 @@ struct TileParams
     unsigned int nx, ny, x0, y0, w, h;
     unsigned int spp_begin; // first sample index of this device's share
     unsigned int seed, max_depth;
+    unsigned int integrator; // frt_integrator
 };
 
 struct KernelArgs

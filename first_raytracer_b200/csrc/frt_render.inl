@@ -97,6 +97,12 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
         return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: tile outside the film");
     if (t->spp_end < t->spp_begin) return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: empty sample range");
     if (t->max_depth > 200) return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: max_depth too large");
+    if (t->integrator > FRT_INTEGRATOR_NORMALS || t->reserved != 0)
+        return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: unknown integrator %u", t->integrator);
+    if (t->integrator == FRT_INTEGRATOR_AO && !(ctx->ao_t_max > 0.f))
+        return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: ao needs frt_scene_desc::ao_t_max > 0");
+    if (t->integrator != FRT_INTEGRATOR_PATH && (ctx->flags & FRT_FLAG_STREAMED_POOL))
+        return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: the streamed pool runs the path integrator only");
     int rc = ensure_film(ctx, t->nx, t->ny);
     if (rc != FRT_OK) return rc;
 
@@ -113,10 +119,10 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
         const uint32_t s0 = t->spp_begin + (uint32_t)(((uint64_t)spp * i) / nd);
         const uint32_t s1 = t->spp_begin + (uint32_t)(((uint64_t)spp * (i + 1)) / nd);
         KernelArgs &a = args[i];
-        a.sc = device_view(ctx, d);
+        a.sc = t->integrator == FRT_INTEGRATOR_AO ? device_view(ctx, d, (double)ctx->ao_t_max) : device_view(ctx, d);
         a.pool = d.pool;
         a.tile.nx = t->nx; a.tile.ny = t->ny; a.tile.x0 = t->x0; a.tile.y0 = t->y0; a.tile.w = t->w; a.tile.h = t->h;
-        a.tile.spp_begin = s0; a.tile.seed = t->seed; a.tile.max_depth = t->max_depth;
+        a.tile.spp_begin = s0; a.tile.seed = t->seed; a.tile.max_depth = t->max_depth; a.tile.integrator = t->integrator;
         a.ctr = d.d_ctr;
         a.film = d.d_film;
         const unsigned long long total = (unsigned long long)t->w * t->h * (s1 - s0);

@@ -117,9 +117,15 @@ __device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, co
             const unsigned int pixel = __float_as_uint(tw.w), sample = __float_as_uint(rw.w);
             float3 thr = f3(tw), rad = f3(rw);
 
-            if (prim == 0xFFFFFFFFu)
+            if (flags & FRT_FLAG_FINISH)
             {
-                // path.cpp:115 — constant environment (material.h:219-232 over constant_texture)
+                // ao: the occlusion ray of the only vertex has been resolved by the trace stage
+                end_path(a, pool, slot, rad, pixel, nonfinite);
+                terminated = true;
+            }
+            else if (prim == 0xFFFFFFFFu)
+            {
+                // path.cpp:115 / ao.cpp:27 / debug_renderer.h:17 — constant environment (material.h:219-232 over constant_texture)
                 rad = rad + thr * arr3(a.sc.env);
                 end_path(a, pool, slot, rad, pixel, nonfinite);
                 terminated = true;
@@ -164,6 +170,55 @@ __device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, co
                 const frt_material &m = a.sc.materials[mat_id];
                 const unsigned int mtype = m.type;
 
+                if (a.tile.integrator == FRT_INTEGRATOR_NORMALS)
+                {
+                    // normals_renderer::Li debug_renderer.h:11-15: hrec.normal as the colour (can be negative)
+                    end_path(a, pool, slot, h.n, pixel, nonfinite);
+                    terminated = true;
+                }
+                else if (a.tile.integrator == FRT_INTEGRATOR_AO)
+                {
+                    // ao::Li ao.cpp:4-28: one direction drawn from the BSDF's pdf (get3d for scatter, then get2d for
+                    // generate), occluded within 0.5 * world size.y -> black, else the environment colour.  A
+                    // material that does not scatter (diffuse_light) also returns the environment.
+                    const float3 env = arr3(a.sc.env);
+                    if (mtype == FRT_MAT_DIFFUSE_LIGHT || !nonzero(env))
+                    {
+                        end_path(a, pool, slot, mtype == FRT_MAT_DIFFUSE_LIGHT ? env : f3(0.f, 0.f, 0.f), pixel, nonfinite);
+                        terminated = true;
+                    }
+                    else
+                    {
+                        const float4 r1 = frt_rng_block(a.tile.seed, pixel, sample, 1);
+                        const float4 r2 = frt_rng_block(a.tile.seed, pixel, sample, 2);
+                        ScatterRec srec;
+                        mat_scatter(m, h, d, r1.x, r1.y, srec);
+                        float3 dir;
+                        if (srec.is_specular) // the specular pdfs' generate is what their scatter calls (material.h:88-89, ...)
+                        {
+                            ScatterRec again;
+                            mat_scatter(m, h, d, r2.x, r2.y, again);
+                            dir = again.dir;
+                        }
+                        else // cosine_pdf::generate pdf.h:91-94
+                        {
+                            const float r = sqrtf(r2.x);
+                            float sp, cp;
+                            sincospif(2.0f * r2.y, &sp, &cp);
+                            dir = Onb(h.n).from_local(f3(r * cp, r * sp, sqrtf(1.0f - r2.x)));
+                        }
+                        want_shadow = true; // ray(hrec.p, dir): no offset along the normal (ao.cpp:17)
+                        pool.sh_a[slot] = make_float4(h.p.x, h.p.y, h.p.z, dir.x);
+                        pool.sh_b[slot] = make_float4(dir.y, dir.z, env.x, env.y);
+                        pool.sh_c[slot] = env.z;
+                        // the slot lives one more iteration to splat what the occlusion ray leaves: its
+                        // "extension ray" starts far outside every scene box and misses at the root
+                        pool.ray_o[slot] = make_float4(3.0e30f, 3.0e30f, 3.0e30f, 0.0f);
+                        pool.ray_d[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(FRT_FLAG_ALIVE | FRT_FLAG_FINISH));
+                    }
+                }
+                else
+                {
                 // ---- emitted: diffuse_light::emitted material.h:184-190 ----
                 float3 Le = f3(0.f, 0.f, 0.f);
                 if (mtype == FRT_MAT_DIFFUSE_LIGHT && dot(h.n, d) < 0.0f) Le = arr3(m.p);
@@ -285,6 +340,7 @@ __device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, co
                     end_path(a, pool, slot, rad, pixel, nonfinite);
                     terminated = true;
                 }
+                } // integrator == path
             }
         }
         return (terminated ? FRT_SHADE_TERMINATED : 0u) | (want_shadow ? FRT_SHADE_SHADOW : 0u) |

@@ -108,7 +108,8 @@ struct Walker
     // y = bits of its entry distance, to drop it at pop time once something closer was found) and
     // hands it to round().  frt_upload_scene rejects trees deeper than the stack can serve.
 
-    __device__ __forceinline__ double tend_d() const { return ANY ? 1.0 - (double)FRT_SHADOW_EPSILON : (double)FRT_FLT_MAX; }
+    // upper end of the t interval: FLT_MAX for closest hit (path.cpp:10), DevScene::any_tend (uniform) for occlusion
+    static __device__ __forceinline__ double tend_d(const DevScene &sc) { return ANY ? sc.any_tend : (double)FRT_FLT_MAX; }
     __device__ __forceinline__ double tmin_exact() const { return frt_tmin_exact(o); }
 
     __device__ __forceinline__ void begin(const DevScene &sc, const float3 o_, const float3 d_)
@@ -120,8 +121,8 @@ struct Walker
         const float m = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
         tmin = fmaxf(9.99999974737875e-05f, __fmul_rd(9.99999974737875e-05f, m));
         tmin_hi = fmaxf(1.00000004749745e-04f, __fmul_ru(1.00000004749745e-04f, m));
-        best.prim = 0xFFFFFFFFu; best.u = best.v = 0.f; best.t = tend_d(); best.exact = true;
-        best.lo = __double2float_rd(tend_d()); best.hi = __double2float_ru(tend_d());
+        best.prim = 0xFFFFFFFFu; best.u = best.v = 0.f; best.t = tend_d(sc); best.exact = true;
+        best.lo = ANY ? sc.any_tend_lo : FRT_FLT_MAX; best.hi = ANY ? sc.any_tend_hi : FRT_FLT_MAX;
         tmax = best.hi; // culling bound
         // correctly rounded reciprocals (the library is built with -prec-div=false): the padding of the float32
         // boxes (host/flatten.h) is sized for a slab test whose only error is rounding
@@ -208,7 +209,7 @@ struct Walker
                     double t = (-b - disc) / a;
                     const double tmin_d = tmin_exact();
                     if (t < tmin_d) t = (-b + disc) / a;
-                    if (t < tmin_d || t > tend_d()) continue;
+                    if (t < tmin_d || t > tend_d(sc)) continue;
                     e.t = t; e.u = 0.f; e.v = 0.f;
                 }
                 else
@@ -257,7 +258,7 @@ struct Walker
                 // (sphere.h:41); at an exact tie the triangle the reference meets first (lower index) stays
                 if (ANY)
                 {
-                    if (is_sphere || e.t < tend_d()) { best.prim = prim; active = false; return; }
+                    if (is_sphere || e.t < tend_d(sc)) { best.prim = prim; active = false; return; }
                     continue;
                 }
                 if (!best.exact) // the closest so far was taken on its float32 interval: pin it down now

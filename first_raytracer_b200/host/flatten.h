@@ -31,6 +31,7 @@ struct frt_flat_scene
     std::vector<frt_light> lights;
     frt_camera camera{};
     float env[3] = {0, 0, 0};
+    float ao_t_max = 0.f; // ao.cpp:19-22: 0.5 * size.y of the world's bounding box
     bool any_smooth = false;
     int max_depth_wide = 0;
 
@@ -47,6 +48,7 @@ struct frt_flat_scene
         d.n_lights = (uint32_t)lights.size(); d.lights = lights.data();
         d.camera = camera;
         std::memcpy(d.env_color, env, sizeof env);
+        d.ao_t_max = ao_t_max;
         return d;
     }
 };
@@ -89,6 +91,8 @@ public:
             put3(out_.env, e);
         }
         if (out_.materials.empty()) { frt_material m{}; m.type = FRT_MAT_LAMBERTIAN; out_.materials.push_back(m); }
+        aabb world_box;
+        if (scene->world && scene->world->bounding_box(0.0, 0.0, world_box)) out_.ao_t_max = (float)(world_box.size.y() * 0.50f);
         return std::move(out_);
     }
 

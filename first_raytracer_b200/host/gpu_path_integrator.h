@@ -29,6 +29,7 @@ struct gpu_path_integrator
     uint32_t max_depth = 34;
     int max_leaf = 2; // triangles per wide-BVH leaf (measured best on B200 for the reference scenes)
     uint32_t flags = 0;
+    uint32_t integrator = FRT_INTEGRATOR_PATH; // which Li the tile runs; see gpu_ao_integrator / gpu_normals_integrator
     frt_stats stats{};
     const std::unordered_map<const hitable *, int> *prim_ids = nullptr;
 
@@ -99,7 +100,8 @@ private:
         check(ctx, frt_set_flags(ctx, flags), "frt_set_flags");
         check(ctx, frt_clear_film(ctx), "frt_clear_film");
         check(ctx, frt_upload_scene(ctx, &desc), "frt_upload_scene");
-        frt_tile tile;
+        frt_tile tile{};
+        tile.integrator = integrator;
         tile.nx = (uint32_t)film->nx; tile.ny = (uint32_t)film->ny;
         tile.x0 = tile.y0 = 0; tile.w = tile.nx; tile.h = tile.ny;
         tile.spp_begin = 0; tile.spp_end = (uint32_t)film->ns;
@@ -135,3 +137,8 @@ private:
         Scene::num_ray_tri_intersections = (unsigned int)stats.tri_tests;
     }
 };
+
+// The reference's other integrators that are one shade stage over the same trace kernels:
+// drop-ins for `ao` (ao.h:8-47, ao.cpp:4-28) and `normals_renderer` (debug_renderer.h:6-47) behind renderer<>.
+struct gpu_ao_integrator : gpu_path_integrator { gpu_ao_integrator() { integrator = FRT_INTEGRATOR_AO; } };
+struct gpu_normals_integrator : gpu_path_integrator { gpu_normals_integrator() { integrator = FRT_INTEGRATOR_NORMALS; } };

@@ -163,7 +163,8 @@ int frth_render(frth_scene *s, int n_gpus, int nx, int ny, uint32_t ns, uint32_t
         renderer<gpu_path_integrator> render;
         render.n_gpus = n_gpus;
         render.seed = seed;
-        render.flags = flags;
+        render.flags = flags & 0xFFu;
+        render.integrator = (flags >> 8) & 0xFFu; // FRTH_RENDER_* in frt_host.h
         render.max_leaf = s->max_leaf;
         render.prim_ids = &s->ids.id;
         const double secs = render.Render(s->scene.get(), film);

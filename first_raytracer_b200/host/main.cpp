@@ -35,9 +35,12 @@ int main(int argc, const char **argv)
         else if (a == "--res") { const char *r = next(); if (std::sscanf(r, "%dx%d", &nx, &ny) != 2) { std::cerr << "bad --res\n"; return 2; } }
         else { std::cerr << "unknown argument " << a << "\n"; return 2; }
     }
-    if (integrator_name != "gpu_path")
+    uint32_t li = FRT_INTEGRATOR_PATH;
+    if (integrator_name == "gpu_ao") li = FRT_INTEGRATOR_AO;
+    else if (integrator_name == "gpu_normals") li = FRT_INTEGRATOR_NORMALS;
+    else if (integrator_name != "gpu_path")
     {
-        std::cerr << "integrator '" << integrator_name << "' is not part of this build (only gpu_path)\n";
+        std::cerr << "integrator '" << integrator_name << "' is not part of this build (gpu_path, gpu_ao, gpu_normals)\n";
         return 2;
     }
     viewer film_viewer(nx, ny, ns, comp);
@@ -53,6 +56,7 @@ int main(int argc, const char **argv)
         renderer<gpu_path_integrator> render;
         render.n_gpus = gpus;
         render.seed = seed;
+        render.integrator = li;
         const double render_time = render.Render(scene.get(), film_viewer);
         const frt_stats &st = render.stats;
         std::cout << " GPU: " << st.samples << " samples, " << st.closest_rays << " closest + " << st.shadow_rays

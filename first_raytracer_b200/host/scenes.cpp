@@ -175,6 +175,15 @@ Scene *soup_scene(const double &aspect, const float *tri9, size_t n, frt_scene_i
 
 Scene *make_scene(const std::string &name, double aspect, frt_scene_ids *ids)
 {
+    // "<scene>+sky": the same scene under a constant sky-blue environment (the shipped scenes are lit by
+    // emitters under a black environment, where ao::Li is identically zero); the oracle driver does the same
+    const std::string sky = "+sky";
+    if (name.size() > sky.size() && name.compare(name.size() - sky.size(), sky.size(), sky) == 0)
+    {
+        Scene *s = make_scene(name.substr(0, name.size() - sky.size()), aspect, ids);
+        s->env_map.reset(new environment_map(std::make_unique<constant_texture>(Vector3f(0.5, 0.6, 0.8))));
+        return s;
+    }
     if (name == "cornell" || name == "cornell_box_obj") return cornell_box_obj(aspect, "Original", ids);
     if (name == "cornell_glossy") return cornell_box_obj(aspect, "Glossy", ids);
     if (name == "cornell_sphere") return cornell_box_obj(aspect, "Sphere", ids);

@@ -120,19 +120,28 @@ typedef struct frt_scene_desc {
     const frt_light *lights;
     frt_camera camera;
     float env_color[3]; /* environment_map over a constant_texture, material.h:219-232 */
-    uint32_t reserved;
+    float ao_t_max;     /* 0.5 * world bounding box size.y: the occlusion range of ao::Li (ao.cpp:19-22) */
 } frt_scene_desc;
 
 /* One unit of rendering work: the pixel rectangle and sample range path::Render's row loop
  * (path.cpp:120-147) would cover.  Sample s of pixel (x,y) is identified by (seed, y*nx+x, s)
  * whatever tile / device / rank renders it, so splitting [spp_begin,spp_end) across GPUs
  * gives the same multiset of samples as one GPU. */
+/* Which Li the tile runs (the integrators next to `path`, same trace kernels) */
+typedef enum frt_integrator {
+    FRT_INTEGRATOR_PATH = 0,   /* path::Li, path.cpp:4-116 (NEE + MIS) */
+    FRT_INTEGRATOR_AO = 1,     /* ao::Li, ao.cpp:4-28: one BSDF-sampled occlusion ray of length ao_t_max per sample */
+    FRT_INTEGRATOR_NORMALS = 2 /* normals_renderer::Li, debug_renderer.h:8-17: the hit normal as colour */
+} frt_integrator;
+
 typedef struct frt_tile {
     uint32_t nx, ny;         /* film size (viewer::nx, ny) */
     uint32_t x0, y0, w, h;   /* pixel rectangle, row 0 = bottom (viewer.cpp:109-132) */
     uint32_t spp_begin, spp_end;
     uint32_t seed;
     uint32_t max_depth;      /* deepest vertex that still scatters + 1; reference: 34 (path.cpp:36) */
+    uint32_t integrator;     /* frt_integrator; 0 = path */
+    uint32_t reserved;       /* must be 0 */
 } frt_tile;
 
 typedef struct frt_stats {

@@ -810,6 +810,61 @@ static v3 Li(octx *cx, v3 o, v3 d, int depth, const hitrec *prev, uint32_t prev_
     return Le; /* path.cpp:112 */
 }
 
+/* ---- ao::Li ao.cpp:4-28 ------------------------------------------------------------------------- */
+static v3 Li_ao(octx *cx, v3 o, v3 d, sampler *rs)
+{
+    const frt_scene_desc *sc = cx->sc;
+    hitrec h;
+    cx->st.closest_rays++;
+    if (world_hit(cx, o, d, REAL_FLT_MAX, 0, &h)) /* ao.cpp:9 */
+    {
+        fill_hit(sc, o, d, &h);
+        const frt_material *m = &sc->materials[h.mat];
+        real s0, s1, s2;
+        scatrec sr;
+        get3d(rs, &s0, &s1, &s2);
+        (void)s2;
+        if (mat_scatter(m, &h, d, s0, s1, &sr)) /* ao.cpp:13 */
+        {
+            /* srec.pdf_ptr->generate(get2d(), srec) ao.cpp:17: cosine_pdf::generate pdf.h:91-94 for lambertian;
+             * the specular pdfs' generate is what their scatter calls with (sample[0], sample[1]) */
+            real r0, r1;
+            v3 dir;
+            get2d(rs, &r0, &r1);
+            if (sr.is_specular)
+            {
+                scatrec again;
+                mat_scatter(m, &h, d, r0, r1, &again);
+                dir = again.dir;
+            }
+            else
+            {
+                const real r = rsqrt_(r0), phi = 2 * PI * r1;
+                const onb b = onb_from_w(h.n);
+                dir = from_local(&b, V(r * rcos(phi), r * rsin(phi), rsqrt_(1 - r0)));
+            }
+            /* t_max = bbox.size.y() * 0.50f ao.cpp:19-22; ray from hrec.p, not offset */
+            hitrec occ;
+            cx->st.shadow_rays++;
+            if (world_hit(cx, h.p, dir, (real)sc->ao_t_max, 1, &occ)) return V(0, 0, 0);
+        }
+    }
+    return f3(sc->env_color); /* ao.cpp:27 */
+}
+
+/* ---- normals_renderer::Li debug_renderer.h:8-17 ------------------------------------------------- */
+static v3 Li_normals(octx *cx, v3 o, v3 d)
+{
+    hitrec h;
+    cx->st.closest_rays++;
+    if (world_hit(cx, o, d, REAL_FLT_MAX, 0, &h))
+    {
+        fill_hit(cx->sc, o, d, &h);
+        return h.n;
+    }
+    return f3(cx->sc->env_color);
+}
+
 /* ---- path::Render's sample loop path.cpp:129-143 over a tile; camera::get_ray camera.h:30-35 -- */
 int frt_oracle_render(const frt_scene_desc *scene, const frt_tile *t, int use_bvh, double *rgb_sum, frt_oracle_stats *stats)
 {
@@ -854,7 +909,9 @@ int frt_oracle_render(const frt_scene_desc *scene, const frt_tile *t, int use_bv
                 const v3 ro = add(origin, offset);
                 const v3 rd = sub(sub(add(add(llc, scl(hor, u)), scl(ver, v)), origin), offset);
                 cx.st.samples++;
-                const v3 L = Li(&cx, ro, rd, 0, &none, 0xFFFFFFFFu, 0, (int)t->max_depth, &rs);
+                const v3 L = t->integrator == FRT_INTEGRATOR_AO ? Li_ao(&cx, ro, rd, &rs)
+                             : t->integrator == FRT_INTEGRATOR_NORMALS ? Li_normals(&cx, ro, rd)
+                             : Li(&cx, ro, rd, 0, &none, 0xFFFFFFFFu, 0, (int)t->max_depth, &rs);
                 if (!(isfinite(L.x) && isfinite(L.y) && isfinite(L.z))) { cx.st.nonfinite++; continue; }
                 col[0] += (double)L.x; col[1] += (double)L.y; col[2] += (double)L.z;
             }

@@ -20,6 +20,7 @@
 // Commands (all print one JSON line on stdout):
 //   frt_ref trace  <scene> <aspect> closest|shadow <rays.f32> <out.bin>
 //   frt_ref render <scene> <w> <h> <spp> <out.pfm> [--threads N] [--seed S] [--rows y0 y1] [--ystep K]
+//                  [--integrator path|ao|normals]
 //   frt_ref dump   <scene> <aspect> <out.bin>
 //   frt_ref bsdf   <in.f64> <out.f64>
 #include "Scene.h"
@@ -35,6 +36,8 @@
 #include "sampler.h"
 #include "integrator.h"
 #include "path.h"
+#include "ao.h"
+#include "debug_renderer.h"
 
 static std::string g_assets = "assets";
 
@@ -262,8 +265,11 @@ struct built_scene
     std::vector<std::shared_ptr<triangle_mesh>> meshes;
 };
 
-static built_scene &build_scene(const std::string &name, double aspect)
+static built_scene &build_scene(const std::string &full_name, double aspect)
 {
+    // "<scene>+sky": same scene under a constant sky-blue environment (gives ao::Li something to return)
+    const bool sky = full_name.size() > 4 && full_name.compare(full_name.size() - 4, 4, "+sky") == 0;
+    const std::string name = sky ? full_name.substr(0, full_name.size() - 4) : full_name;
     built_scene &b = *new built_scene;
     std::vector<hitable *> lights;
     std::vector<hitable *> list;
@@ -366,6 +372,7 @@ static built_scene &build_scene(const std::string &name, double aspect)
     else
         throw std::runtime_error("unknown scene " + name);
 
+    if (sky) env = Vector3f(0.5, 0.6, 0.8);
     b.creation_order = list;
     hitable **arr = new hitable *[list.size()];
     for (size_t i = 0; i < list.size(); ++i) arr[i] = list[i];
@@ -458,6 +465,7 @@ static int cmd_render(int argc, char **argv)
     int threads = (int)std::thread::hardware_concurrency();
     uint32_t seed = 1;
     int y0 = 0, y1 = ny, ystep = 1;
+    std::string integrator_name = "path"; // path::Li, ao::Li (ao.cpp:4-28) or normals_renderer::Li (debug_renderer.h:8-17)
     for (int i = 7; i < argc; ++i)
     {
         const std::string a = argv[i];
@@ -465,6 +473,12 @@ static int cmd_render(int argc, char **argv)
         else if (a == "--seed") seed = (uint32_t)std::atoll(argv[++i]);
         else if (a == "--rows") { y0 = std::atoi(argv[i + 1]); y1 = std::atoi(argv[i + 2]); i += 2; }
         else if (a == "--ystep") ystep = std::atoi(argv[++i]);
+        else if (a == "--integrator") integrator_name = argv[++i];
+    }
+    if (integrator_name != "path" && integrator_name != "ao" && integrator_name != "normals")
+    {
+        std::fprintf(stderr, "unknown integrator %s\n", integrator_name.c_str());
+        return 2;
     }
     const double tb = now_s();
     built_scene &b = build_scene(scene_name, double(nx) / double(ny));
@@ -475,6 +489,9 @@ static int cmd_render(int argc, char **argv)
     (void)has_lights;
     viewer film(nx, ny, ns, 3);
     path integrator;
+    ao ao_integrator;
+    normals_renderer normals_integrator;
+    const int which = integrator_name == "ao" ? 1 : (integrator_name == "normals" ? 2 : 0);
     std::atomic<uint64_t> nonfinite{0};
 
     tf::Taskflow tf(threads > 0 ? threads : 1);
@@ -498,7 +515,9 @@ static int cmd_render(int argc, char **argv)
                 double v = double(y + random_sampler.get1d()) / double(ny);
                 ray r = scene->cam.get_ray(u, v, random_sampler.get2d());
                 hit_record hrec;
-                const Vector3f sample = integrator.Li(r, scene, 0, hrec, 0.0, random_sampler);
+                const Vector3f sample = which == 1 ? ao_integrator.Li(r, scene, 0, hrec, 0.0, random_sampler)
+                                        : which == 2 ? normals_integrator.Li(r, scene, 0, hrec, 0.0, random_sampler)
+                                        : integrator.Li(r, scene, 0, hrec, 0.0, random_sampler);
                 if (!(std::isfinite(sample[0]) && std::isfinite(sample[1]) && std::isfinite(sample[2])))
                 {
                     ++nonfinite;

@@ -47,11 +47,14 @@ def trace_fixture(name, aspect, n_cam=48, n_rand=6000, n_seg=4000):
           f"{seg.shape[0]} segments, occluded {np.mean(sref['prim'] >= 0):.3f}")
 
 
-def render_fixture(name, nx, ny, spp):
-    img, info = refutil.ref_render(name, nx, ny, spp, ctr=True, seed=SEED)
-    np.savez_compressed(OUT / f"render_{name}_{nx}x{ny}x{spp}.npz", image=img.astype(np.float32), seed=SEED,
+def render_fixture(name, nx, ny, spp, integrator="path"):
+    """integrator: path::Li, ao::Li (ao.cpp:4-28) or normals_renderer::Li (debug_renderer.h:8-17); a scene name
+    ending in +sky is the scene under a constant sky-blue environment (ref_main.cpp build_scene)."""
+    img, info = refutil.ref_render(name, nx, ny, spp, ctr=True, seed=SEED, integrator=integrator)
+    tag = "render" if integrator == "path" else f"render_{integrator}"
+    np.savez_compressed(OUT / f"{tag}_{name}_{nx}x{ny}x{spp}.npz", image=img.astype(np.float32), seed=SEED,
                         closest_rays=info["closest_rays"], shadow_rays=info["shadow_rays"], nonfinite=info["nonfinite"])
-    print(f"render_{name}_{nx}x{ny}x{spp}: mean {img.mean():.6f}, rays {info['closest_rays']}+{info['shadow_rays']}")
+    print(f"{tag}_{name}_{nx}x{ny}x{spp}: mean {img.mean():.6f}, rays {info['closest_rays']}+{info['shadow_rays']}")
 
 
 def unit(v):
@@ -86,6 +89,12 @@ def bsdf_fixture(n_per=600):
     print(f"bsdf_vectors: {rec.shape[0]} records, finite {np.isfinite(out).all(axis=1).mean():.4f}")
 
 
+OTHER_INTEGRATOR_CASES = [("teapot", 48, 27, 2, "ao"), ("cornell_glossy+sky", 32, 32, 2, "ao"), ("veach+sky", 48, 32, 2, "ao"),
+                          ("cornell_sphere+sky", 32, 32, 2, "ao"), ("cornell", 32, 32, 1, "normals"),
+                          ("teapot", 48, 27, 1, "normals"), ("cornell_sphere", 32, 32, 1, "normals"),
+                          ("veach+sky", 48, 32, 2, "path"), ("teapot", 160, 90, 4, "ao")]
+
+
 def main():
     if not refutil.have_ref():
         raise SystemExit("oracle/_ref is missing: run `make -C oracle` where /root/reference exists")
@@ -97,6 +106,9 @@ def main():
                               # larger ones for the GPU parity tests (statistical bars need pixels x spp)
                               ("cornell", 128, 128, 16), ("veach", 192, 128, 16)]:
         render_fixture(name, nx, ny, spp)
+    # the integrators next to `path` and the constant-environment term of path::Li
+    for name, nx, ny, spp, integ in OTHER_INTEGRATOR_CASES:
+        render_fixture(name, nx, ny, spp, integ)
     bsdf_fixture()
 
 

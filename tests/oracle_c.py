@@ -82,9 +82,9 @@ class Oracle:
             tie[bad] = np.abs(t_other - ref_t[bad]) <= tie_rel * np.abs(ref_t[bad])
         return float(same.mean()), float((same | tie).mean())
 
-    def render(self, nx, ny, spp, seed=1, spp_begin=0, max_depth=34, rect=None, return_stats=False):
+    def render(self, nx, ny, spp, seed=1, spp_begin=0, max_depth=34, rect=None, return_stats=False, integrator="path"):
         x0, y0, w, h = rect if rect else (0, 0, nx, ny)
-        tile = api.frt_tile(nx, ny, x0, y0, w, h, spp_begin, spp_begin + spp, seed, max_depth)
+        tile = api.frt_tile(nx, ny, x0, y0, w, h, spp_begin, spp_begin + spp, seed, max_depth, api.INTEGRATORS[integrator], 0)
         img = np.zeros((ny, nx, 3), np.float64)
         st = frt_oracle_stats()
         rc = self.lib.frt_oracle_render(C.addressof(self.desc), C.byref(tile), int(self.use_bvh), img.ctypes.data, C.byref(st))

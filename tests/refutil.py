@@ -58,8 +58,8 @@ def ref_trace(scene: str, aspect: float, rays: np.ndarray, shadow: bool = False)
 
 
 def ref_render(scene: str, nx: int, ny: int, spp: int, ctr: bool = False, seed: int = 1, threads: int | None = None,
-               rows=None, ystep: int = 1):
-    """path::Li over the full frame (or a row band) → (image [ny,nx,3] row 0 = bottom, info)."""
+               rows=None, ystep: int = 1, integrator: str = "path"):
+    """path::Li / ao::Li / normals_renderer::Li over the full frame (or a row band) → (image [ny,nx,3] row 0 = bottom, info)."""
     with tempfile.TemporaryDirectory() as td:
         out = Path(td) / "img.pfm"
         cmd = [REF_CTR_BIN if ctr else REF_BIN, "render", scene, nx, ny, spp, out, "--seed", seed]
@@ -69,6 +69,8 @@ def ref_render(scene: str, nx: int, ny: int, spp: int, ctr: bool = False, seed: 
             cmd += ["--rows", rows[0], rows[1]]
         if ystep != 1:
             cmd += ["--ystep", ystep]
+        if integrator != "path":
+            cmd += ["--integrator", integrator]
         info = _run(cmd)
         img = read_pfm(out)
     return img, info

@@ -70,6 +70,34 @@ def test_same_random_numbers_as_golden(built, name, nx, ny, spp):
     assert abs(st["closest_rays"] - int(g["closest_rays"])) / int(g["closest_rays"]) < 5e-3
 
 
+@pytest.mark.parametrize("name,nx,ny,spp,integrator", [("teapot", 48, 27, 2, "ao"), ("teapot", 160, 90, 4, "ao"),
+                                                       ("cornell_glossy+sky", 32, 32, 2, "ao"), ("veach+sky", 48, 32, 2, "ao"),
+                                                       ("cornell_sphere+sky", 32, 32, 2, "ao"), ("cornell", 32, 32, 1, "normals"),
+                                                       ("teapot", 48, 27, 1, "normals"), ("cornell_sphere", 32, 32, 1, "normals"),
+                                                       ("veach+sky", 48, 32, 2, "path")])
+def test_other_integrators_match_golden(built, name, nx, ny, spp, integrator):
+    """gpu_ao_integrator / gpu_normals_integrator (same trace kernels, another shade stage) and the environment
+    term of the path integrator against fixtures rendered by the compiled reference's ao::Li /
+    normals_renderer::Li / path::Li on the same random numbers."""
+    tag = "render" if integrator == "path" else f"render_{integrator}"
+    g = np.load(refutil.GOLDEN / f"{tag}_{name}_{nx}x{ny}x{spp}.npz")
+    scene = api.HostScene(name, nx / ny, 2)
+    gpu, st, _ = scene.render(nx, ny, spp, seed=int(g["seed"]), integrator=integrator)
+    gpu = gpu.astype(np.float64)
+    ref = g["image"].astype(np.float64)
+    assert np.isfinite(gpu).all() and np.abs(ref).max() > 0
+    if integrator == "normals":
+        # one sample per pixel: a float32 jitter rounding can move a sample across an edge in a few pixels
+        close = np.abs(gpu - ref).max(axis=2) < 2e-4
+        assert close.mean() > 0.995
+    else:
+        close = (np.abs(gpu - ref).max(axis=2) / np.maximum(ref.max(axis=2), 1e-3)) < 2e-3
+        assert close.mean() > (0.999 if nx * ny > 10_000 else 0.99)
+        assert abs(gpu[close].mean() - ref[close].mean()) / ref[close].mean() < 1e-4
+    print(f"{integrator} {name} {nx}x{ny}x{spp}: pixels agreeing {close.mean():.4f}, mean gpu {gpu.mean():.6f} ref {ref.mean():.6f}, "
+          f"rays {st['closest_rays']}+{st['shadow_rays']}")
+
+
 def test_cornell_statistical_parity(built):
     """BASELINE bars on independent random numbers: 256x256, 64 spp each, 8x8 block average."""
     if not refutil.have_ref():

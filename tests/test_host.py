@@ -35,7 +35,7 @@ def test_abi_exports_every_declared_symbol(built):
 
 
 def test_struct_layouts_match_header(built):
-    assert C.sizeof(api.frt_tile) == 40
+    assert C.sizeof(api.frt_tile) == 48
     assert api.NODE_DTYPE.itemsize == 128 and api.MATERIAL_DTYPE.itemsize == 64
     assert api.LIGHT_DTYPE.itemsize == 128 and api.SPHERE_DTYPE.itemsize == 32
     assert api.RAY_DTYPE.itemsize == 24 and api.HIT_DTYPE.itemsize == 16

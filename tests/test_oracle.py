@@ -32,6 +32,26 @@ def test_oracle_render_matches_golden(built, name, nx, ny, spp):
     assert abs(img.mean() - ref.mean()) <= 1e-5 * max(ref.mean(), 1e-3)
 
 
+OTHER_INTEGRATOR_CASES = [("teapot", 48, 27, 2, "ao"), ("cornell_glossy+sky", 32, 32, 2, "ao"), ("veach+sky", 48, 32, 2, "ao"),
+                          ("cornell_sphere+sky", 32, 32, 2, "ao"), ("cornell", 32, 32, 1, "normals"),
+                          ("teapot", 48, 27, 1, "normals"), ("cornell_sphere", 32, 32, 1, "normals"),
+                          ("veach+sky", 48, 32, 2, "path")]
+
+
+@pytest.mark.parametrize("name,nx,ny,spp,integrator", OTHER_INTEGRATOR_CASES)
+def test_oracle_other_integrators_match_golden(built, name, nx, ny, spp, integrator):
+    """ao::Li (ao.cpp:4-28), normals_renderer::Li (debug_renderer.h:8-17) and path::Li's environment term against
+    fixtures rendered by the compiled reference with the same random numbers (lambertian, phong, rough
+    conductor, dielectric and sphere surfaces)."""
+    tag = "render" if integrator == "path" else f"render_{integrator}"
+    g = np.load(GOLDEN / f"{tag}_{name}_{nx}x{ny}x{spp}.npz")
+    scene = api.HostScene(name, nx / ny, 2)
+    img = oracle_c.Oracle(scene).render(nx, ny, spp, seed=int(g["seed"]), integrator=integrator)
+    ref = g["image"].astype(np.float64)
+    assert np.abs(ref).max() > 0
+    assert np.abs(img - ref).max() <= 1e-5 * max(1.0, np.abs(ref).max())
+
+
 @pytest.mark.parametrize("name,aspect", [("cornell", 1.0), ("veach", 1.5), ("teapot", 16 / 9), ("cornell_sphere", 1.0)])
 def test_oracle_trace_matches_golden(built, name, aspect):
     g = np.load(GOLDEN / f"trace_{name}.npz")
