@@ -8,6 +8,8 @@ Two kinds of comparison:
  * independent random numbers: the as-shipped mt19937 build, statistical bars of BASELINE.json
    (relMSE <= 1e-3 after block averaging at reduced spp, mean radiance within 0.5 %).
 """
+import ctypes as C
+
 import numpy as np
 import pytest
 
@@ -156,3 +158,30 @@ def test_repeated_renders_reuse_the_context(built):
     img_a2, _, _ = a.render(64, 64, 4, seed=3)
     assert img_b.shape == (64, 96, 3) and np.isfinite(img_b).all() and img_b.mean() > 0
     assert np.allclose(img_a, img_a2, rtol=1e-4, atol=1e-6)
+
+
+def test_pixel_tiles_sum_to_whole_and_bad_tiles_are_rejected(built):
+    """A sample is identified by (seed, pixel, index): rendering the film as two pixel rectangles gives the
+    frame rendered at once; tiles outside the film, unknown integrators and ao without a range are errors."""
+    scene = api.HostScene("cornell", 1.0, 2)
+    ctx = api.Context()
+    ctx.upload(scene)
+    ctx.render_tile(64, 48, 0, 6, seed=4)
+    whole, st = ctx.readback()
+    ctx.clear_film()
+    ctx.render_tile(64, 48, 0, 6, seed=4, rect=(0, 0, 64, 20))
+    ctx.render_tile(64, 48, 0, 6, seed=4, rect=(0, 20, 64, 28))
+    parts, st2 = ctx.readback()
+    assert st2["samples"] == st["samples"] == 64 * 48 * 6
+    assert np.allclose(whole, parts, rtol=1e-4, atol=1e-5)
+    with pytest.raises(api.FrtError):
+        ctx.render_tile(64, 48, 0, 1, rect=(32, 0, 64, 48))
+    bad = api.frt_tile(64, 48, 0, 0, 64, 48, 0, 1, 1, 34, 7, 0)
+    assert ctx._frt.frt_render_tile(ctx.handle, C.byref(bad)) == -1  # FRT_ERR_INVALID: unknown integrator
+    assert b"integrator" in ctx._frt.frt_last_error(ctx.handle)
+    # empty sample range: nothing rendered, nothing counted
+    ctx.clear_film()
+    ctx.render_tile(64, 48, 3, 3, seed=4)
+    empty, st3 = ctx.readback()
+    assert st3["samples"] == 0 and not empty.any()
+    ctx.close()
