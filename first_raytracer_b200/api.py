@@ -24,7 +24,7 @@ FRT_FLAG_STREAMED_POOL = 4
 FRT_SYMBOLS = [
     "frt_create", "frt_destroy", "frt_last_error", "frt_set_flags", "frt_device_count",
     "frt_upload_scene", "frt_render_tile", "frt_clear_film", "frt_readback", "frt_film_device_ptr",
-    "frt_trace_rays", "frt_trace_rays_device", "frt_stream_handle", "frt_get_counters",
+    "frt_trace_rays", "frt_trace_rays_device", "frt_stream_handle", "frt_get_counters", "frt_restore_film",
 ]
 FRTH_SYMBOLS = [
     "frth_last_error", "frth_scene_create", "frth_scene_create_soup", "frth_scene_destroy",
@@ -125,6 +125,7 @@ def load_libs():
             "frt_clear_film": (i32, [vp]),
             "frt_readback": (i32, [vp, vp, sz, C.POINTER(frt_stats)]),
             "frt_get_counters": (i32, [vp, C.POINTER(frt_stats)]),
+            "frt_restore_film": (i32, [vp, u32, u32, vp, sz]),
             "frt_film_device_ptr": (i32, [vp, i32, C.POINTER(vp), C.POINTER(sz)]),
             "frt_stream_handle": (i32, [vp, i32, C.POINTER(vp)]),
             "frt_trace_rays": (i32, [vp, vp, sz, vp, i32, C.POINTER(dbl)]),
@@ -305,6 +306,13 @@ class Context:
             self._check(self._frt.frt_readback(self.handle, None, 0, C.byref(st)), "frt_readback")
         return out, st.as_dict()
 
+    def restore_film(self, sums: np.ndarray):
+        """Film sums [ny,nx,3] float32 from an earlier readback become the film's starting state (resume)."""
+        sums = np.ascontiguousarray(sums, dtype=np.float32)
+        ny, nx = sums.shape[:2]
+        self._check(self._frt.frt_restore_film(self.handle, nx, ny, _ptr(sums), sums.size), "frt_restore_film")
+        self.nx, self.ny = nx, ny
+
     def counters(self) -> dict:
         st = frt_stats()
         self._check(self._frt.frt_get_counters(self.handle, C.byref(st)), "frt_get_counters")
@@ -335,3 +343,17 @@ class Context:
         self._check(self._frt.frt_trace_rays_device(self.handle, dev, d_rays_ptr, n, d_hits_ptr, int(any_hit),
                                                     C.byref(ms)), "frt_trace_rays_device")
         return ms.value
+
+
+def save_checkpoint(path, sums: np.ndarray, spp_done: int, seed: int, scene: str = "", integrator: str = "path"):
+    """Film checkpoint of a long render: the radiance sums and how many samples per pixel they hold.  Because a
+    sample is identified by (seed, pixel, index), rendering [spp_done, spp) on top of the restored sums gives the
+    film an uninterrupted render would have given, on any number of GPUs."""
+    np.savez_compressed(path, sums=np.asarray(sums, dtype=np.float32), spp_done=np.int64(spp_done), seed=np.int64(seed),
+                        scene=np.str_(scene), integrator=np.str_(integrator))
+
+
+def load_checkpoint(path) -> dict:
+    with np.load(path) as z:
+        return {"sums": z["sums"], "spp_done": int(z["spp_done"]), "seed": int(z["seed"]), "scene": str(z["scene"]),
+                "integrator": str(z["integrator"])}

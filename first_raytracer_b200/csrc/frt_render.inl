@@ -198,6 +198,22 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
     return FRT_OK;
 }
 
+int frt_restore_film(frt_ctx *ctx, uint32_t nx, uint32_t ny, const float *rgb_sum, size_t n_floats)
+{
+    if (!ctx || !rgb_sum || nx == 0 || ny == 0) return FRT_ERR_INVALID;
+    if (n_floats != (size_t)nx * ny * 3)
+        return fail(ctx, FRT_ERR_INVALID, "frt_restore_film: expected %zu floats, got %zu", (size_t)nx * ny * 3, n_floats);
+    int rc = ensure_film(ctx, nx, ny);
+    if (rc != FRT_OK) return rc;
+    rc = frt_clear_film(ctx);
+    if (rc != FRT_OK) return rc;
+    Device &d0 = ctx->dev[0];
+    CU(cudaSetDevice(d0.ordinal));
+    CU(cudaMemcpyAsync(d0.d_film, rgb_sum, n_floats * sizeof(float), cudaMemcpyHostToDevice, d0.stream));
+    CU(cudaStreamSynchronize(d0.stream)); // the caller's buffer may go away after the call
+    return FRT_OK;
+}
+
 int frt_get_counters(frt_ctx *ctx, frt_stats *stats)
 {
     if (!ctx || !stats) return FRT_ERR_INVALID;

@@ -30,6 +30,11 @@ struct gpu_path_integrator
     int max_leaf = 2; // triangles per wide-BVH leaf (measured best on B200 for the reference scenes)
     uint32_t flags = 0;
     uint32_t integrator = FRT_INTEGRATOR_PATH; // which Li the tile runs; see gpu_ao_integrator / gpu_normals_integrator
+    // resume: film sums of samples [0, spp_begin) from an earlier run; the render continues at
+    // spp_begin and add_sample receives the sum over all film->ns samples.  film_sums_out receives the final sums.
+    uint32_t spp_begin = 0;
+    const std::vector<float> *resume_sums = nullptr;
+    std::vector<float> *film_sums_out = nullptr;
     frt_stats stats{};
     const std::unordered_map<const hitable *, int> *prim_ids = nullptr;
 
@@ -98,13 +103,16 @@ private:
         frt_ctx *ctx = acquire(n_gpus);
         lap("context");
         check(ctx, frt_set_flags(ctx, flags), "frt_set_flags");
-        check(ctx, frt_clear_film(ctx), "frt_clear_film");
+        if (resume_sums)
+            check(ctx, frt_restore_film(ctx, (uint32_t)film->nx, (uint32_t)film->ny, resume_sums->data(), resume_sums->size()), "frt_restore_film");
+        else
+            check(ctx, frt_clear_film(ctx), "frt_clear_film");
         check(ctx, frt_upload_scene(ctx, &desc), "frt_upload_scene");
         frt_tile tile{};
         tile.integrator = integrator;
         tile.nx = (uint32_t)film->nx; tile.ny = (uint32_t)film->ny;
         tile.x0 = tile.y0 = 0; tile.w = tile.nx; tile.h = tile.ny;
-        tile.spp_begin = 0; tile.spp_end = (uint32_t)film->ns;
+        tile.spp_begin = spp_begin; tile.spp_end = (uint32_t)film->ns;
         tile.seed = seed; tile.max_depth = max_depth;
         lap("upload");
         check(ctx, frt_render_tile(ctx, &tile), "frt_render_tile");
@@ -112,6 +120,7 @@ private:
         std::vector<float> sums((size_t)film->nx * film->ny * 3);
         check(ctx, frt_readback(ctx, sums.data(), sums.size(), &stats), "frt_readback");
         lap("readback");
+        if (film_sums_out) *film_sums_out = sums;
         give_back(ctx, n_gpus);
         // path.cpp:143 / viewer.cpp:109-132: the film divides the sum by ns and tonemaps.  As in the
         // reference every pixel is written by exactly one thread; rows are dealt to the host cores

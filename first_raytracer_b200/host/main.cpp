@@ -1,12 +1,15 @@
 // frt_main — the reference's main() (main.cpp:483-525) with the GPU integrator selectable:
 //   frt_main [--ns N] [--scene cornell|veach|teapot|soup:N] [--res WxH] [--integrator gpu_path]
-//            [--gpus N] [--seed S] [--out NAME]
+//            [--gpus N] [--seed S] [--out NAME] [--checkpoint FILE] [--resume FILE]
+// --checkpoint writes the film sums after the render; --resume starts from such a file and renders only the samples
+// it does not hold yet (same seed, same resolution), so an interrupted --ns 512 job can be finished as --ns 1024.
 // Defaults follow the reference: 512x512, ns = 100 (main.cpp:485-487).  The only integrator in
 // this product is gpu_path (renderer<gpu_path_integrator>); asking for another one is an error
 // rather than a silent CPU path.
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
+#include <fstream>
 #include <iostream>
 #include <memory>
 #include <string>
@@ -14,12 +17,39 @@
 #include "integrator.h"
 #include "scenes.h"
 
+namespace
+{
+struct ckpt_header { char magic[8]; uint32_t nx, ny, spp_done, seed; };
+
+void write_checkpoint(const std::string &path, int nx, int ny, uint32_t spp_done, uint32_t seed, const std::vector<float> &sums)
+{
+    ckpt_header h{{'F', 'R', 'T', 'C', 'K', 'P', 'T', '1'}, (uint32_t)nx, (uint32_t)ny, spp_done, seed};
+    std::ofstream f(path, std::ios::binary);
+    f.write((const char *)&h, sizeof h);
+    f.write((const char *)sums.data(), (std::streamsize)(sums.size() * sizeof(float)));
+    if (!f) throw std::runtime_error("cannot write checkpoint " + path);
+}
+
+ckpt_header read_checkpoint(const std::string &path, int nx, int ny, std::vector<float> &sums)
+{
+    ckpt_header h{};
+    std::ifstream f(path, std::ios::binary);
+    f.read((char *)&h, sizeof h);
+    if (!f || std::memcmp(h.magic, "FRTCKPT1", 8) != 0) throw std::runtime_error("not a film checkpoint: " + path);
+    if ((int)h.nx != nx || (int)h.ny != ny) throw std::runtime_error("checkpoint resolution differs from --res");
+    sums.resize((size_t)nx * ny * 3);
+    f.read((char *)sums.data(), (std::streamsize)(sums.size() * sizeof(float)));
+    if (!f) throw std::runtime_error("truncated checkpoint " + path);
+    return h;
+}
+} // namespace
+
 int main(int argc, const char **argv)
 {
     int nx = 512, ny = 512;
     uint_fast64_t ns = 100;
     constexpr int comp = 3;
-    std::string scene_name = "cornell", integrator_name = "gpu_path", out = "out_test";
+    std::string scene_name = "cornell", integrator_name = "gpu_path", out = "out_test", checkpoint, resume;
     int gpus = 1;
     uint32_t seed = 1;
     for (int i = 1; i < argc; ++i)
@@ -32,6 +62,8 @@ int main(int argc, const char **argv)
         else if (a == "--gpus") gpus = std::atoi(next());
         else if (a == "--seed") seed = (uint32_t)std::atoll(next());
         else if (a == "--out") out = next();
+        else if (a == "--checkpoint") checkpoint = next();
+        else if (a == "--resume") resume = next();
         else if (a == "--res") { const char *r = next(); if (std::sscanf(r, "%dx%d", &nx, &ny) != 2) { std::cerr << "bad --res\n"; return 2; } }
         else { std::cerr << "unknown argument " << a << "\n"; return 2; }
     }
@@ -57,11 +89,23 @@ int main(int argc, const char **argv)
         render.n_gpus = gpus;
         render.seed = seed;
         render.integrator = li;
+        std::vector<float> resume_sums, final_sums;
+        if (!resume.empty())
+        {
+            const ckpt_header h = read_checkpoint(resume, nx, ny, resume_sums);
+            if (h.spp_done > ns) throw std::runtime_error("checkpoint already holds more samples than --ns");
+            render.seed = h.seed;
+            render.spp_begin = h.spp_done;
+            render.resume_sums = &resume_sums;
+            std::cout << "\nResuming at sample " << h.spp_done << " of " << ns << " (seed " << h.seed << ")";
+        }
+        render.film_sums_out = &final_sums;
         const double render_time = render.Render(scene.get(), film_viewer);
         const frt_stats &st = render.stats;
         std::cout << " GPU: " << st.samples << " samples, " << st.closest_rays << " closest + " << st.shadow_rays
                   << " shadow rays in " << st.render_ms << " ms device time = "
                   << (st.closest_rays + st.shadow_rays) / (st.render_ms * 1e3) << " Mrays/s" << std::endl;
+        if (!checkpoint.empty()) write_checkpoint(checkpoint, nx, ny, (uint32_t)ns, render.seed, final_sums);
         film_viewer.save_and_destroy(out + "_" + std::to_string(render_time) + "s");
         gpu_path_integrator::release_cached_context();
     }

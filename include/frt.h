@@ -191,6 +191,11 @@ FRT_API int frt_clear_film(frt_ctx *ctx);
  * `rgb_sum` (may be NULL to only synchronise) and fills `stats` (may be NULL). */
 FRT_API int frt_readback(frt_ctx *ctx, float *rgb_sum, size_t n_floats, frt_stats *stats);
 
+/* Resume: load radiance SUMS saved from an earlier frt_readback (nx*ny*3 float32, row 0 =
+ * bottom) as the film's starting state, so that rendering the remaining sample range continues an interrupted
+ * render; (re)allocates the film.  The sums go to device 0, the other devices' films start at zero. */
+FRT_API int frt_restore_film(frt_ctx *ctx, uint32_t nx, uint32_t ny, const float *rgb_sum, size_t n_floats);
+
 /* Counters only (rays, node visits, triangle tests since the last frt_clear_film), summed over the
  * devices; synchronises.  Works without a film, i.e. after frt_trace_rays alone: the integrator's
  * statistics block (integrator.h:33-43) for a pure ray-cast run. */

@@ -185,3 +185,53 @@ def test_pixel_tiles_sum_to_whole_and_bad_tiles_are_rejected(built):
     empty, st3 = ctx.readback()
     assert st3["samples"] == 0 and not empty.any()
     ctx.close()
+
+
+def test_checkpoint_and_resume(built, tmp_path):
+    """a render interrupted after 3 of 8 spp and resumed in a NEW context from its checkpoint
+    equals the uninterrupted render."""
+    scene = api.HostScene("cornell", 1.0, 2)
+    ctx = api.Context(); ctx.upload(scene)
+    ctx.render_tile(64, 64, 0, 8, seed=9)
+    whole, _ = ctx.readback()
+    ctx.clear_film()
+    ctx.render_tile(64, 64, 0, 3, seed=9)
+    part, _ = ctx.readback()
+    ctx.close()
+    api.save_checkpoint(tmp_path / "film.npz", part, spp_done=3, seed=9, scene="cornell")
+    ck = api.load_checkpoint(tmp_path / "film.npz")
+    assert ck["spp_done"] == 3 and ck["seed"] == 9 and ck["scene"] == "cornell"
+    ctx2 = api.Context(); ctx2.upload(scene)
+    ctx2.restore_film(ck["sums"])
+    ctx2.render_tile(64, 64, ck["spp_done"], 8, seed=ck["seed"])
+    resumed, st = ctx2.readback()
+    assert st["samples"] == 64 * 64 * 5
+    assert np.allclose(whole, resumed, rtol=1e-4, atol=1e-5)
+    with pytest.raises(api.FrtError):
+        ctx2.restore_film(np.zeros((8, 8, 2), np.float32))
+    ctx2.close()
+
+
+def test_frt_main_checkpoint_resume(built, tmp_path):
+    """frt_main --checkpoint / --resume: finishing a 3-spp job as an 8-spp job gives the 8-spp film."""
+    import subprocess
+    exe = str(api.PKG_DIR / "frt_main")
+    def run(*args):
+        r = subprocess.run([exe, "--scene", "cornell", "--res", "48x32", "--seed", "5", *args], cwd=tmp_path,
+                           capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+        return r.stdout
+    def sums(name):
+        raw = (tmp_path / name).read_bytes()
+        assert raw[:8] == b"FRTCKPT1"
+        nx, ny, done, seed = np.frombuffer(raw[8:24], np.uint32)
+        return int(done), np.frombuffer(raw[24:], np.float32).reshape(ny, nx, 3)
+    run("--ns", "8", "--checkpoint", "whole.ck")
+    run("--ns", "3", "--checkpoint", "part.ck")
+    out = run("--ns", "8", "--resume", "part.ck", "--checkpoint", "resumed.ck")
+    assert "Resuming at sample 3 of 8" in out
+    (dw, whole), (dp, _), (dr, resumed) = sums("whole.ck"), sums("part.ck"), sums("resumed.ck")
+    assert (dw, dp, dr) == (8, 3, 8)
+    assert np.allclose(whole, resumed, rtol=1e-4, atol=1e-5)
+    bad = subprocess.run([exe, "--res", "40x32", "--ns", "8", "--resume", "part.ck"], cwd=tmp_path, capture_output=True, text=True)
+    assert bad.returncode == 1 and "resolution" in bad.stderr
