@@ -122,7 +122,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -303,9 +303,22 @@ def e2e_pass(scene, steps, n_gpus, spp):
     return steps * NX * NY * spp / dt / 1e6, float(img.mean()), dt / steps
 
 
+_JSON_OUT = None
+
+
+def emit(line: dict):
+    _JSON_OUT.write(json.dumps(line) + "\n")
+    _JSON_OUT.flush()
+
+
 def main():
-    global SCENE, SPP, WORKLOAD
+    global SCENE, SPP, WORKLOAD, _JSON_OUT
     args = parse()
+    # stdout carries exactly ONE line, the JSON: everything else written to fd 1 (renderer<>::Render prints the
+    # reference's timing block with std::cout, integrator.h:33-43) goes to stderr
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.scene != "cornell":
         SCENE, SPP = args.scene, 256
         WORKLOAD = {"veach": f"veach_mi (GGX rough_conductor plates, 5 sphere lights) {NX}x{NY} {SPP} spp NEE+MIS",
@@ -373,7 +386,7 @@ def main():
             "clocks": res["clocks"], "e2e": e2e, "gpu_launches": res["launches"],
             "roofline": roof, "cpu_baseline": cpu,
         }
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0

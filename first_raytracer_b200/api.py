@@ -42,8 +42,9 @@ class frt_tile(C.Structure):
                 ("nx", "ny", "x0", "y0", "w", "h", "spp_begin", "spp_end", "seed", "max_depth", "integrator", "reserved")]
 
 
-FRT_INTEGRATOR_PATH, FRT_INTEGRATOR_AO, FRT_INTEGRATOR_NORMALS = 0, 1, 2
-INTEGRATORS = {"path": FRT_INTEGRATOR_PATH, "ao": FRT_INTEGRATOR_AO, "normals": FRT_INTEGRATOR_NORMALS}
+FRT_INTEGRATOR_PATH, FRT_INTEGRATOR_AO, FRT_INTEGRATOR_NORMALS, FRT_INTEGRATOR_DIRECT = 0, 1, 2, 3
+INTEGRATORS = {"path": FRT_INTEGRATOR_PATH, "ao": FRT_INTEGRATOR_AO, "normals": FRT_INTEGRATOR_NORMALS,
+               "direct": FRT_INTEGRATOR_DIRECT}
 
 
 class frt_stats(C.Structure):

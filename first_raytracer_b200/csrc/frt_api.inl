@@ -77,6 +77,10 @@ int frt_create(frt_ctx **out, const int *devices, int n)
             return fail(nullptr, FRT_ERR_CUDA, "frt_create: k_wavefront does not fit an SM with %u slots per CTA", c->wf_slots);
         }
         d.blocks_wavefront = per_sm * d.sms;
+        CU(cudaFuncSetAttribute(wf_other.plain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
+        CU(cudaFuncSetAttribute(wf_other.counting, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_other.plain, wf_other.threads, wf_smem));
+        d.blocks_wavefront_other = per_sm * d.sms; // 0: only the path integrator fits this FRT_WF_SLOTS
     }
     // peer access for the in-process film reduction
     for (int i = 1; i < n; ++i)

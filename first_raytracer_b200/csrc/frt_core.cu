@@ -40,7 +40,7 @@ struct Device
     float *d_film_peer = nullptr; // staging when peer access is unavailable
     size_t film_floats = 0;
     int sms = 0;
-    int blocks_extend = 0, blocks_connect = 0, blocks_trace = 0, blocks_trace_any = 0, blocks_wavefront = 0;
+    int blocks_extend = 0, blocks_connect = 0, blocks_trace = 0, blocks_trace_any = 0, blocks_wavefront = 0, blocks_wavefront_other = 0;
     unsigned int wf_ctas_launched = 0;
     bool rendered = false;
     // per-render bookkeeping
@@ -249,11 +249,14 @@ struct WfConfig
     void (*plain)(const KernelArgs, const unsigned int, const int, const int);
     void (*counting)(const KernelArgs, const unsigned int, const int, const int);
 };
-#define WF_CFG(T, B) {T, B, k_wavefront<false, T, B>, k_wavefront<true, T, B>}
+#define WF_CFG(T, B) {T, B, k_wavefront<false, T, B, false>, k_wavefront<true, T, B, false>}
 const WfConfig wf_configs[] = {WF_CFG(256, 2), WF_CFG(128, 4), WF_CFG(128, 5), WF_CFG(256, 3), WF_CFG(512, 1), WF_CFG(128, 3),
                                WF_CFG(192, 3), WF_CFG(160, 4), WF_CFG(320, 2), WF_CFG(224, 3), WF_CFG(288, 2),
                                WF_CFG(384, 1), WF_CFG(448, 1), WF_CFG(192, 2)};
 const int n_wf_configs = (int)(sizeof wf_configs / sizeof wf_configs[0]);
+// The same kernel with the shade stage of the integrators next to `path` (ao, normals_renderer, ass_1_renderer): its
+// own instantiation, so that the path kernel carries none of their code (measured: -11 % when it did), in one shape.
+const WfConfig wf_other = {512, 1, k_wavefront<false, 512, 1, true>, k_wavefront<true, 512, 1, true>};
 
 // `any_tend` = upper end of occlusion queries: path.cpp:50 passes 1 - SHADOW_EPSILON (a float literal, util.h:11)
 DevScene device_view(const frt_ctx *ctx, const Device &d, double any_tend = 1.0 - (double)1e-3f)

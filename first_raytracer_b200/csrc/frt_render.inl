@@ -97,7 +97,7 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
         return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: tile outside the film");
     if (t->spp_end < t->spp_begin) return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: empty sample range");
     if (t->max_depth > 200) return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: max_depth too large");
-    if (t->integrator > FRT_INTEGRATOR_NORMALS || t->reserved != 0)
+    if (t->integrator > FRT_INTEGRATOR_DIRECT || t->reserved != 0)
         return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: unknown integrator %u", t->integrator);
     if (t->integrator == FRT_INTEGRATOR_AO && !(ctx->ao_t_max > 0.f))
         return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: ao needs frt_scene_desc::ao_t_max > 0");
@@ -136,9 +136,12 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
             const size_t smem = (size_t)ctx->wf_slots * FRT_WF_SLOT_BYTES;
             // no more CTAs than can be kept busy: one CTA-iteration consumes up to wf_slots samples
             const unsigned long long want = (total + ctx->wf_slots - 1) / ctx->wf_slots;
-            const unsigned int grid = (unsigned int)std::min<unsigned long long>((unsigned long long)d.blocks_wavefront, want);
+            const bool other = t->integrator != FRT_INTEGRATOR_PATH;
+            const WfConfig &wc = other ? wf_other : wf_configs[ctx->wf_config];
+            const int resident = other ? d.blocks_wavefront_other : d.blocks_wavefront;
+            if (resident < 1) return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: FRT_WF_SLOTS=%u leaves no room for this integrator's kernel", ctx->wf_slots);
+            const unsigned int grid = (unsigned int)std::min<unsigned long long>((unsigned long long)resident, want);
             k_reset_tile<<<1, 1, 0, d.stream>>>(d.d_ctr, total);
-            const WfConfig &wc = wf_configs[ctx->wf_config];
             (count ? wc.counting : wc.plain)<<<grid, wc.threads, smem, d.stream>>>(a, ctx->wf_slots, ctx->wf_refill,
                                                                                      ctx->wf_sort >= 0 ? ctx->wf_sort : (ctx->multi_bsdf ? 3 : 1));
             CU(cudaGetLastError());

@@ -67,6 +67,33 @@ __device__ __forceinline__ float sphere_pdf_direct(float3 c, float radius, float
     return (1.0f / solid_angle) * fabsf(dot(to_light, rec_n)) / d2;
 }
 
+// ass_1_renderer::Li assignment_1.cpp:13-34 at a surface that scatters: every light sampled once (one get2d each, after
+// the get3d that scatter() consumes), NO visibility test, to_light left un-normalised, the light's area-measure pdf
+// used as is.  Out of line: the other integrators never call it and must not pay registers for it.
+__device__ __noinline__ float3 frt_direct_lighting(const DevScene &sc, const frt_material &m, const Surface h, unsigned int seed,
+                                                   unsigned int pixel, unsigned int sample)
+{
+    float3 Le = f3(0.f, 0.f, 0.f);
+    const float3 so = h.p + FRT_EPSILON * h.n;
+    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (unsigned int i = 0; i < sc.n_lights; ++i)
+    {
+        if ((i & 1u) == 0) r = frt_rng_block(seed, pixel, sample, 2 + (i >> 1)); // sampler layout: oracle/frt_rng.h
+        const float u0 = (i & 1u) ? r.z : r.x, u1 = (i & 1u) ? r.w : r.y;
+        const frt_light &L = sc.lights[i];
+        const LightSample ls = light_sample_direct(L, so, u0, u1);
+        const float3 bsdf = mat_eval(m, h, ls.to_light);
+        const float cos_wi = fmaxf(0.0f, dot(h.n, unit_vector(ls.to_light)));
+        float light_pdf;
+        if (L.kind == FRT_LIGHT_TRIANGLE) light_pdf = L.v0[3];
+        else light_pdf = sphere_pdf_direct(arr3(L.v0), L.v0[3], h.p, h.t, h.n, ls.to_light);
+        const frt_material &lm = sc.materials[L.material];
+        if (lm.type == FRT_MAT_DIFFUSE_LIGHT && dot(ls.n, ls.to_light) < 0.0f) // diffuse_light::emitted material.h:184-190
+            Le = Le + bsdf * arr3(lm.p) * cos_wi / light_pdf;
+    }
+    return Le;
+}
+
 __device__ __forceinline__ void end_path(const KernelArgs &a, const PathPool &pool, unsigned int slot, float3 rad,
                                          unsigned int pixel, unsigned int &nonfinite)
 {
@@ -93,6 +120,9 @@ __device__ __forceinline__ void end_path(const KernelArgs &a, const PathPool &po
 // Bits 8.. of the result = the primitive the vertex lies on (leaf-order index), a spatial key for
 // binning the rays that leave it.
 #define FRT_SHADE_PRIM_SHIFT 3
+// OTHER = false: path::Li only (the tile's integrator field is not read: the hot kernel carries none of the code
+// below it does not run); OTHER = true: ao / normals_renderer / ass_1_renderer, selected by a.tile.integrator.
+template <bool OTHER>
 __device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, const PathPool &pool, const unsigned int slot,
                                                          unsigned int &nonfinite)
 {
@@ -117,7 +147,7 @@ __device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, co
             const unsigned int pixel = __float_as_uint(tw.w), sample = __float_as_uint(rw.w);
             float3 thr = f3(tw), rad = f3(rw);
 
-            if (flags & FRT_FLAG_FINISH)
+            if (OTHER && (flags & FRT_FLAG_FINISH))
             {
                 // ao: the occlusion ray of the only vertex has been resolved by the trace stage
                 end_path(a, pool, slot, rad, pixel, nonfinite);
@@ -170,13 +200,21 @@ __device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, co
                 const frt_material &m = a.sc.materials[mat_id];
                 const unsigned int mtype = m.type;
 
-                if (a.tile.integrator == FRT_INTEGRATOR_NORMALS)
+                if (OTHER && a.tile.integrator == FRT_INTEGRATOR_NORMALS)
                 {
                     // normals_renderer::Li debug_renderer.h:11-15: hrec.normal as the colour (can be negative)
                     end_path(a, pool, slot, h.n, pixel, nonfinite);
                     terminated = true;
                 }
-                else if (a.tile.integrator == FRT_INTEGRATOR_AO)
+                else if (OTHER && a.tile.integrator == FRT_INTEGRATOR_DIRECT)
+                {
+                    // a surface that does not scatter (diffuse_light) returns black: assignment_1.cpp:15,35
+                    float3 Le = f3(0.f, 0.f, 0.f);
+                    if (mtype != FRT_MAT_DIFFUSE_LIGHT) Le = frt_direct_lighting(a.sc, m, h, a.tile.seed, pixel, sample);
+                    end_path(a, pool, slot, Le, pixel, nonfinite);
+                    terminated = true;
+                }
+                else if (OTHER && a.tile.integrator == FRT_INTEGRATOR_AO)
                 {
                     // ao::Li ao.cpp:4-28: one direction drawn from the BSDF's pdf (get3d for scatter, then get2d for
                     // generate), occluded within 0.5 * world size.y -> black, else the environment colour.  A
@@ -355,7 +393,7 @@ __global__ void __launch_bounds__(128) k_shade(const KernelArgs a, const int par
     const unsigned int n_round = (n + 31u) & ~31u;
     for (unsigned int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_round; slot += gridDim.x * blockDim.x)
     {
-        const unsigned int r = slot < n ? frt_shade_vertex(a, a.pool, slot, nonfinite) : 0u;
+        const unsigned int r = slot < n ? frt_shade_vertex<false>(a, a.pool, slot, nonfinite) : 0u;
         const bool terminated = r & FRT_SHADE_TERMINATED, want_shadow = r & FRT_SHADE_SHADOW;
         // queue compaction: warp ballot + one atomic per warp per queue
         const unsigned int qi = warp_append(want_shadow, &a.ctr->n_shadow);

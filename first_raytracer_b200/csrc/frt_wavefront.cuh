@@ -89,7 +89,7 @@ __device__ __forceinline__ void wf_trace_queue(const DevScene &sc, const PathPoo
 
 // P = slots per CTA (a multiple of 32); refill_below = a warp fetches new rays once this many lanes or
 // fewer are still traversing.
-template <bool COUNT, int THREADS, int MIN_BLOCKS>
+template <bool COUNT, int THREADS, int MIN_BLOCKS, bool OTHER>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelArgs a, const unsigned int P, const int refill_below,
                                                                    const int sort_rays)
 {
@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelA
                 if (idx >= n_shade) break;
                 const bool valid = !by_material || idx < n_ext;
                 const unsigned int slot = by_material ? (valid ? order[idx] : 0u) : idx;
-                const unsigned int r = valid ? frt_shade_vertex(a, lp, slot, nonfinite) : 0u;
+                const unsigned int r = valid ? frt_shade_vertex<OTHER>(a, lp, slot, nonfinite) : 0u;
                 const bool ended = r & FRT_SHADE_TERMINATED, goes_on = (r & FRT_SHADE_WAS_ALIVE) && !ended;
                 const unsigned int fi = warp_append(ended, &sh.n_free);
                 if (ended) free_q[fi] = slot;
@@ -280,7 +280,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelA
         {
             const unsigned int slot = s0 + tid; // P is a multiple of 32: whole warps fall off the end together
             if (slot >= P) break;
-            const unsigned int r = frt_shade_vertex(a, lp, slot, nonfinite);
+            const unsigned int r = frt_shade_vertex<OTHER>(a, lp, slot, nonfinite);
             const bool ended = r & FRT_SHADE_TERMINATED, goes_on = (r & FRT_SHADE_WAS_ALIVE) && !ended;
             const unsigned int ei = warp_append(goes_on, &sh.n_ext);
             if (goes_on) ext_q[ei] = slot;

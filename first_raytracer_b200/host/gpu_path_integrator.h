@@ -151,3 +151,5 @@ private:
 // drop-ins for `ao` (ao.h:8-47, ao.cpp:4-28) and `normals_renderer` (debug_renderer.h:6-47) behind renderer<>.
 struct gpu_ao_integrator : gpu_path_integrator { gpu_ao_integrator() { integrator = FRT_INTEGRATOR_AO; } };
 struct gpu_normals_integrator : gpu_path_integrator { gpu_normals_integrator() { integrator = FRT_INTEGRATOR_NORMALS; } };
+// `ass_1_renderer` (assignment_1.hpp:8-19, assignment_1.cpp:4-38): unshadowed direct lighting, every light sampled once.
+struct gpu_ass_1_integrator : gpu_path_integrator { gpu_ass_1_integrator() { integrator = FRT_INTEGRATOR_DIRECT; } };

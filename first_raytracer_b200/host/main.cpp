@@ -70,9 +70,10 @@ int main(int argc, const char **argv)
     uint32_t li = FRT_INTEGRATOR_PATH;
     if (integrator_name == "gpu_ao") li = FRT_INTEGRATOR_AO;
     else if (integrator_name == "gpu_normals") li = FRT_INTEGRATOR_NORMALS;
+    else if (integrator_name == "gpu_ass_1") li = FRT_INTEGRATOR_DIRECT;
     else if (integrator_name != "gpu_path")
     {
-        std::cerr << "integrator '" << integrator_name << "' is not part of this build (gpu_path, gpu_ao, gpu_normals)\n";
+        std::cerr << "integrator '" << integrator_name << "' is not part of this build (gpu_path, gpu_ao, gpu_normals, gpu_ass_1)\n";
         return 2;
     }
     viewer film_viewer(nx, ny, ns, comp);

@@ -131,7 +131,8 @@ typedef struct frt_scene_desc {
 typedef enum frt_integrator {
     FRT_INTEGRATOR_PATH = 0,   /* path::Li, path.cpp:4-116 (NEE + MIS) */
     FRT_INTEGRATOR_AO = 1,     /* ao::Li, ao.cpp:4-28: one BSDF-sampled occlusion ray of length ao_t_max per sample */
-    FRT_INTEGRATOR_NORMALS = 2 /* normals_renderer::Li, debug_renderer.h:8-17: the hit normal as colour */
+    FRT_INTEGRATOR_NORMALS = 2, /* normals_renderer::Li, debug_renderer.h:8-17: the hit normal as colour */
+    FRT_INTEGRATOR_DIRECT = 3   /* ass_1_renderer::Li, assignment_1.cpp:4-38: every light sampled once, no visibility test */
 } frt_integrator;
 
 typedef struct frt_tile {

@@ -41,6 +41,7 @@ FRT_API int frth_camera_rays(const frth_scene *s, int nx, int ny, frt_ray *out);
  * (nx*ny*3, viewer::fout_image as float, row 0 = bottom). */
 #define FRTH_RENDER_AO (FRT_INTEGRATOR_AO << 8)           /* or into `flags`: renderer<gpu_ao_integrator> */
 #define FRTH_RENDER_NORMALS (FRT_INTEGRATOR_NORMALS << 8) /* or into `flags`: renderer<gpu_normals_integrator> */
+#define FRTH_RENDER_DIRECT (FRT_INTEGRATOR_DIRECT << 8)   /* or into `flags`: renderer<gpu_ass_1_integrator> */
 FRT_API int frth_render(frth_scene *s, int n_gpus, int nx, int ny, uint32_t ns, uint32_t seed, uint32_t flags,
                         float *rgb_mean, frt_stats *stats, double *wall_seconds);
 

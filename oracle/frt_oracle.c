@@ -705,7 +705,8 @@ static void get2d(sampler *s, real *a, real *b)
     if (s->vertex < 0) { *a = sdim(s, 0, 2); *b = sdim(s, 0, 3); return; }
     int k = s->n2d++;
     if (!s->has_lights) k += 1;
-    *a = sdim(s, 2 + 2 * s->vertex, 2 * k); *b = sdim(s, 2 + 2 * s->vertex, 2 * k + 1);
+    const uint32_t block = (uint32_t)(2 + 2 * s->vertex + (k >> 1)); /* k >= 2 only in Li_direct (one draw per light) */
+    *a = sdim(s, block, 2 * (k & 1)); *b = sdim(s, block, 2 * (k & 1) + 1);
 }
 static void get3d(sampler *s, real *a, real *b, real *c)
 {
@@ -853,6 +854,42 @@ static v3 Li_ao(octx *cx, v3 o, v3 d, sampler *rs)
 }
 
 /* ---- normals_renderer::Li debug_renderer.h:8-17 ------------------------------------------------- */
+/* ---- ass_1_renderer::Li assignment_1.cpp:4-38: every light sampled once, NO visibility test, area-measure pdf -- */
+static v3 Li_direct(octx *cx, v3 o, v3 d, sampler *rs)
+{
+    const frt_scene_desc *sc = cx->sc;
+    hitrec h;
+    cx->st.closest_rays++;
+    if (!world_hit(cx, o, d, REAL_FLT_MAX, 0, &h)) return f3(sc->env_color);
+    fill_hit(sc, o, d, &h);
+    const frt_material *m = &sc->materials[h.mat];
+    v3 Le = V(0, 0, 0);
+    if (m->type == FRT_MAT_DIFFUSE_LIGHT) return Le; /* scatter() false: assignment_1.cpp:15 */
+    real s0, s1, s2;
+    get3d(rs, &s0, &s1, &s2); /* consumed by scatter(); its record is not used */
+    (void)s0; (void)s1; (void)s2;
+    const v3 offset_origin = add(h.p, scl(h.n, EPSILON));
+    for (uint32_t i = 0; i < sc->n_lights; ++i)
+    {
+        const frt_light *L = &sc->lights[i];
+        real u0, u1;
+        get2d(rs, &u0, &u1);
+        const lightsample ls = light_sample_direct(L, offset_origin, u0, u1);
+        const v3 to_light = ls.to_light; /* un-normalised throughout: assignment_1.cpp:22-31 */
+        const v3 surface_bsdf = mat_eval(m, &h, to_light);
+        real cos_wi = dot(h.n, unit(to_light));
+        if (!(cos_wi > 0)) cos_wi = 0; /* std::max(0.0, x) */
+        real light_pdf;
+        if (L->kind == FRT_LIGHT_TRIANGLE) light_pdf = (real)L->v0[3];
+        else light_pdf = sphere_pdf_direct(f3(L->v0), (real)L->v0[3], h.p, h.t, h.n, to_light);
+        const frt_material *lm = &sc->materials[L->material];
+        v3 emit = V(0, 0, 0);
+        if (lm->type == FRT_MAT_DIFFUSE_LIGHT && dot(ls.n, to_light) < 0) emit = mp3(lm, 0);
+        Le = add(Le, dvs(scl(mul(surface_bsdf, emit), cos_wi), light_pdf));
+    }
+    return Le;
+}
+
 static v3 Li_normals(octx *cx, v3 o, v3 d)
 {
     hitrec h;
@@ -911,6 +948,7 @@ int frt_oracle_render(const frt_scene_desc *scene, const frt_tile *t, int use_bv
                 cx.st.samples++;
                 const v3 L = t->integrator == FRT_INTEGRATOR_AO ? Li_ao(&cx, ro, rd, &rs)
                              : t->integrator == FRT_INTEGRATOR_NORMALS ? Li_normals(&cx, ro, rd)
+                             : t->integrator == FRT_INTEGRATOR_DIRECT ? Li_direct(&cx, ro, rd, &rs)
                              : Li(&cx, ro, rd, 0, &none, 0xFFFFFFFFu, 0, (int)t->max_depth, &rs);
                 if (!(isfinite(L.x) && isfinite(L.y) && isfinite(L.z))) { cx.st.nonfinite++; continue; }
                 col[0] += (double)L.x; col[1] += (double)L.y; col[2] += (double)L.z;

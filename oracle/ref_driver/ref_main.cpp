@@ -20,7 +20,7 @@
 // Commands (all print one JSON line on stdout):
 //   frt_ref trace  <scene> <aspect> closest|shadow <rays.f32> <out.bin>
 //   frt_ref render <scene> <w> <h> <spp> <out.pfm> [--threads N] [--seed S] [--rows y0 y1] [--ystep K]
-//                  [--integrator path|ao|normals]
+//                  [--integrator path|ao|normals|direct]
 //   frt_ref dump   <scene> <aspect> <out.bin>
 //   frt_ref bsdf   <in.f64> <out.f64>
 #include "Scene.h"
@@ -37,6 +37,7 @@
 #include "integrator.h"
 #include "path.h"
 #include "ao.h"
+#include "assignment_1.hpp"
 #include "debug_renderer.h"
 
 static std::string g_assets = "assets";
@@ -465,7 +466,7 @@ static int cmd_render(int argc, char **argv)
     int threads = (int)std::thread::hardware_concurrency();
     uint32_t seed = 1;
     int y0 = 0, y1 = ny, ystep = 1;
-    std::string integrator_name = "path"; // path::Li, ao::Li (ao.cpp:4-28) or normals_renderer::Li (debug_renderer.h:8-17)
+    std::string integrator_name = "path"; // path::Li, ao::Li (ao.cpp:4-28), normals_renderer::Li (debug_renderer.h:8-17), ass_1_renderer::Li (assignment_1.cpp:4-38)
     for (int i = 7; i < argc; ++i)
     {
         const std::string a = argv[i];
@@ -475,7 +476,7 @@ static int cmd_render(int argc, char **argv)
         else if (a == "--ystep") ystep = std::atoi(argv[++i]);
         else if (a == "--integrator") integrator_name = argv[++i];
     }
-    if (integrator_name != "path" && integrator_name != "ao" && integrator_name != "normals")
+    if (integrator_name != "path" && integrator_name != "ao" && integrator_name != "normals" && integrator_name != "direct")
     {
         std::fprintf(stderr, "unknown integrator %s\n", integrator_name.c_str());
         return 2;
@@ -491,7 +492,8 @@ static int cmd_render(int argc, char **argv)
     path integrator;
     ao ao_integrator;
     normals_renderer normals_integrator;
-    const int which = integrator_name == "ao" ? 1 : (integrator_name == "normals" ? 2 : 0);
+    ass_1_renderer direct_integrator;
+    const int which = integrator_name == "ao" ? 1 : (integrator_name == "normals" ? 2 : (integrator_name == "direct" ? 3 : 0));
     std::atomic<uint64_t> nonfinite{0};
 
     tf::Taskflow tf(threads > 0 ? threads : 1);
@@ -517,6 +519,7 @@ static int cmd_render(int argc, char **argv)
                 hit_record hrec;
                 const Vector3f sample = which == 1 ? ao_integrator.Li(r, scene, 0, hrec, 0.0, random_sampler)
                                         : which == 2 ? normals_integrator.Li(r, scene, 0, hrec, 0.0, random_sampler)
+                                        : which == 3 ? direct_integrator.Li(r, scene, 0, hrec, 0.0, random_sampler)
                                         : integrator.Li(r, scene, 0, hrec, 0.0, random_sampler);
                 if (!(std::isfinite(sample[0]) && std::isfinite(sample[1]) && std::isfinite(sample[2])))
                 {

@@ -119,13 +119,16 @@ struct sampler
     }
     // path.cpp:133 (lens) before any vertex; at a vertex: first the light sample (path.cpp:45,
     // only drawn when the scene has lights and the material is not dielectric, which never draws
-    // a second one), then the BSDF sample (path.cpp:99).
+    // a second one), then the BSDF sample (path.cpp:99).  ass_1_renderer draws one per light at its only vertex
+    // (assignment_1.cpp:17-22): the third and later ones continue into the following blocks, which belong to
+    // deeper vertices that integrator never reaches.
     inline Vector2f get2d()
     {
         if (vertex < 0) return Vector2f(dim(0, 2), dim(0, 3));
         int k = n2d++;
         if (!has_lights) k += 1;
-        return Vector2f(dim(2 + 2 * vertex, 2 * k), dim(2 + 2 * vertex, 2 * k + 1));
+        const uint32_t block = 2 + 2 * vertex + (k >> 1);
+        return Vector2f(dim(block, 2 * (k & 1)), dim(block, 2 * (k & 1) + 1));
     }
     // path.cpp:36 — exactly once per scattering vertex, before anything else at that vertex.
     inline Vector3f get3d()

@@ -76,9 +76,12 @@ def test_same_random_numbers_as_golden(built, name, nx, ny, spp):
                                                        ("cornell_glossy+sky", 32, 32, 2, "ao"), ("veach+sky", 48, 32, 2, "ao"),
                                                        ("cornell_sphere+sky", 32, 32, 2, "ao"), ("cornell", 32, 32, 1, "normals"),
                                                        ("teapot", 48, 27, 1, "normals"), ("cornell_sphere", 32, 32, 1, "normals"),
-                                                       ("veach+sky", 48, 32, 2, "path")])
+                                                       ("veach+sky", 48, 32, 2, "path"),
+                                                       ("cornell", 32, 32, 2, "direct"), ("cornell_glossy", 32, 32, 2, "direct"),
+                                                       ("teapot", 48, 27, 2, "direct"), ("teapot+sky", 48, 27, 1, "direct"),
+                                                       ("cornell", 128, 128, 4, "direct")])
 def test_other_integrators_match_golden(built, name, nx, ny, spp, integrator):
-    """gpu_ao_integrator / gpu_normals_integrator (same trace kernels, another shade stage) and the environment
+    """gpu_ao_integrator / gpu_normals_integrator / gpu_ass_1_integrator (same trace kernels, another shade stage) and the environment
     term of the path integrator against fixtures rendered by the compiled reference's ao::Li /
     normals_renderer::Li / path::Li on the same random numbers."""
     tag = "render" if integrator == "path" else f"render_{integrator}"

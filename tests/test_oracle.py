@@ -35,7 +35,10 @@ def test_oracle_render_matches_golden(built, name, nx, ny, spp):
 OTHER_INTEGRATOR_CASES = [("teapot", 48, 27, 2, "ao"), ("cornell_glossy+sky", 32, 32, 2, "ao"), ("veach+sky", 48, 32, 2, "ao"),
                           ("cornell_sphere+sky", 32, 32, 2, "ao"), ("cornell", 32, 32, 1, "normals"),
                           ("teapot", 48, 27, 1, "normals"), ("cornell_sphere", 32, 32, 1, "normals"),
-                          ("veach+sky", 48, 32, 2, "path")]
+                          ("veach+sky", 48, 32, 2, "path"),
+                          # ass_1_renderer::Li assignment_1.cpp:4-38
+                          ("cornell", 32, 32, 2, "direct"), ("cornell_glossy", 32, 32, 2, "direct"),
+                          ("teapot", 48, 27, 2, "direct"), ("teapot+sky", 48, 27, 1, "direct")]
 
 
 @pytest.mark.parametrize("name,nx,ny,spp,integrator", OTHER_INTEGRATOR_CASES)
