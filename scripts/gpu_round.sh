@@ -4,5 +4,5 @@ set -x; mkdir -p gpurun_out
 nvidia-smi -L | head -2
 python -m pytest tests -m gpu -q -s 2>&1 | grep -v "^Loading" > gpurun_out/pytest_gpu.log; tail -5 gpurun_out/pytest_gpu.log
 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | grep -v "^Loading" > gpurun_out/smoke.log; tail -3 gpurun_out/smoke.log
-timeout 900 python bench.py --steps 2 --warmup 3 > gpurun_out/bench.log 2>&1; tail -1 gpurun_out/bench.log | cut -c1-1500
+timeout 900 python bench.py --steps 2 --warmup 3 > gpurun_out/bench.log 2> gpurun_out/bench_err.log; wc -l gpurun_out/bench.log; cut -c1-1500 gpurun_out/bench.log
 SPP=${SPP:-8} bash scripts/gpu_profile.sh
