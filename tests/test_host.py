@@ -152,3 +152,13 @@ def test_soup_generator_and_builders(built):
 def test_invalid_arguments_are_reported(built):
     with pytest.raises(api.FrtError, match="unknown scene"):
         api.HostScene("no_such_scene", 1.0, 4)
+
+
+def test_checkpoint_file_round_trip(tmp_path):
+    """api.save_checkpoint / load_checkpoint keep the sums bit for bit and the bookkeeping that makes a film resumable."""
+    rng = np.random.default_rng(3)
+    sums = rng.random((6, 9, 3), dtype=np.float32) * 100
+    api.save_checkpoint(tmp_path / "f.npz", sums, spp_done=17, seed=4, scene="veach", integrator="ao")
+    ck = api.load_checkpoint(tmp_path / "f.npz")
+    assert ck["sums"].dtype == np.float32 and np.array_equal(ck["sums"], sums)
+    assert (ck["spp_done"], ck["seed"], ck["scene"], ck["integrator"]) == (17, 4, "veach", "ao")
