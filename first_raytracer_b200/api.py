@@ -81,7 +81,8 @@ class frt_scene_desc(C.Structure):
                 ("n_tris", C.c_uint32), ("n_spheres", C.c_uint32), ("tris", C.c_void_p),
                 ("tri_normals", C.c_void_p), ("spheres", C.c_void_p), ("n_materials", C.c_uint32),
                 ("n_lights", C.c_uint32), ("materials", C.c_void_p), ("lights", C.c_void_p),
-                ("camera", frt_camera), ("env_color", C.c_float * 3), ("ao_t_max", C.c_float)]
+                ("camera", frt_camera), ("env_color", C.c_float * 3), ("ao_t_max", C.c_float),
+                ("env_image", C.c_void_p), ("env_nx", C.c_uint32), ("env_ny", C.c_uint32)]
 
 
 RAY_DTYPE = np.dtype([("o", "<f4", 3), ("d", "<f4", 3)])

@@ -105,7 +105,7 @@ void frt_destroy(frt_ctx *ctx)
         cudaSetDevice(d.ordinal);
         cudaStreamSynchronize(d.stream);
         for (void *p : d.pool_allocs) cudaFree(p);
-        void *ptrs[] = {d.d_nodes, d.d_tris, d.d_normals, d.d_spheres, d.d_mats, d.d_lights, d.d_ctr, d.d_film, d.d_film_peer};
+        void *ptrs[] = {d.d_nodes, d.d_tris, d.d_normals, d.d_spheres, d.d_mats, d.d_lights, d.d_env, d.d_ctr, d.d_film, d.d_film_peer};
         for (void *p : ptrs) if (p) cudaFree(p);
         if (d.h_ctr) cudaFreeHost(d.h_ctr);
         for (cudaEvent_t e : d.timers.ev) cudaEventDestroy(e);
@@ -124,6 +124,8 @@ static int validate_scene(frt_ctx *ctx, const frt_scene_desc *s)
     if (s->n_spheres && !s->spheres) return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: spheres is NULL");
     if (s->n_materials == 0 || !s->materials) return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: no materials");
     if (s->n_lights && !s->lights) return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: lights is NULL");
+    if (s->env_image && (s->env_nx == 0 || s->env_ny == 0 || (uint64_t)s->env_nx * s->env_ny > (1ull << 28)))
+        return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: environment image of %u x %u texels", s->env_nx, s->env_ny);
     if (s->n_tris > FRT_LEAF_FIRST_MASK || s->n_spheres > FRT_LEAF_FIRST_MASK)
         return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: too many primitives");
     if ((s->n_tris || s->n_spheres) && s->n_nodes == 0) return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: primitives without nodes");
@@ -182,6 +184,7 @@ int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *s)
     v.cam = s->camera;
     memcpy(v.env, s->env_color, sizeof v.env);
     ctx->ao_t_max = s->ao_t_max;
+    v.env_nx = s->env_image ? s->env_nx : 0; v.env_ny = s->env_image ? s->env_ny : 0;
     for (Device &d : ctx->dev)
     {
         CU(cudaSetDevice(d.ordinal));
@@ -192,6 +195,7 @@ int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *s)
         if ((rc = upload_array(ctx, &d.d_spheres, s->spheres, s->n_spheres)) != FRT_OK) return rc;
         if ((rc = upload_array(ctx, &d.d_mats, s->materials, s->n_materials)) != FRT_OK) return rc;
         if ((rc = upload_array(ctx, &d.d_lights, s->lights, s->n_lights)) != FRT_OK) return rc;
+        if ((rc = upload_array(ctx, &d.d_env, s->env_image, s->env_image ? 3 * (size_t)s->env_nx * s->env_ny : 0)) != FRT_OK) return rc;
     }
     uint32_t bsdf_types = 0;
     for (uint32_t i = 0; i < s->n_materials; ++i)

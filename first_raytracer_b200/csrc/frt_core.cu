@@ -30,7 +30,7 @@ struct Device
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     // scene
     void *d_nodes = nullptr, *d_tris = nullptr, *d_normals = nullptr, *d_spheres = nullptr, *d_mats = nullptr,
-         *d_lights = nullptr;
+         *d_lights = nullptr, *d_env = nullptr;
     // pool
     PathPool pool{};
     std::vector<void *> pool_allocs;
@@ -272,6 +272,7 @@ DevScene device_view(const frt_ctx *ctx, const Device &d, double any_tend = 1.0 
     sc.spheres = (const float4 *)d.d_spheres;
     sc.materials = (const frt_material *)d.d_mats;
     sc.lights = (const frt_light *)d.d_lights;
+    sc.env_img = (const float *)d.d_env;
     return sc;
 }
 

@@ -22,6 +22,8 @@ struct DevScene
     uint32_t n_nodes, n_tris, n_spheres, n_materials, n_lights;
     frt_camera cam;
     float env[3];
+    const float *env_img; // lat-long HDR environment image (3 floats per texel, row 0 = top) or nullptr
+    uint32_t env_nx, env_ny;
     // upper end of an occlusion query (uniform per launch): 1 - SHADOW_EPSILON for path.cpp:50 and the ray-cast
     // entry, ao_t_max for ao.cpp:22; with its float32 brackets
     double any_tend;
@@ -62,3 +64,25 @@ __device__ __forceinline__ float length(float3 a) { return sqrtf(dot(a, a)); }
 __device__ __forceinline__ float3 unit_vector(float3 a) { return a * rsqrtf(dot(a, a)); }
 __device__ __forceinline__ bool nonzero(float3 a) { return a.x != 0.f || a.y != 0.f || a.z != 0.f; }
 __device__ __forceinline__ float3 arr3(const float *p) { return f3(p[0], p[1], p[2]); }
+
+// environment_map::eval material.h:219-232 — the colour a ray that leaves the scene gathers.  Over a constant_texture
+// it is sc.env; over an HDR image_texture (texture.h:60-86) the lat-long texel the direction falls in: phi =
+// atan2(x, -z) wrapped to [0, 2 pi), theta = acos(y), u = phi / 2 pi, v = theta / pi, texel (int(u nx), int(v ny)),
+// the last row / column absorbing u = 1 / v = 1, no filtering.  Out of line: one call per path at most, and the
+// path kernel's register budget stays what the traversal needs.
+__device__ __noinline__ float3 frt_env_image(const float *img, uint32_t nx, uint32_t ny, float dx, float dy, float dz)
+{
+    const float inv = rsqrtf(dx * dx + dy * dy + dz * dz);
+    dx *= inv; dy *= inv; dz *= inv;
+    float phi = atan2f(dx, -dz);
+    const float theta = acosf(fminf(1.0f, fmaxf(-1.0f, dy)));
+    if (phi < 0.0f) phi += 6.28318530717958647692f;
+    const float u = phi * 0.15915494309189533577f, v = theta * 0.31830988618379067154f;
+    const int i = min(max((int)(u * (float)nx), 0), (int)nx - 1), j = min(max((int)(v * (float)ny), 0), (int)ny - 1);
+    const float *t = img + 3 * ((size_t)j * nx + (size_t)i);
+    return f3(__ldg(t), __ldg(t + 1), __ldg(t + 2));
+}
+__device__ __forceinline__ float3 frt_env(const DevScene &sc, float3 d)
+{
+    return sc.env_img ? frt_env_image(sc.env_img, sc.env_nx, sc.env_ny, d.x, d.y, d.z) : arr3(sc.env);
+}

@@ -155,8 +155,8 @@ __device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, co
             }
             else if (prim == 0xFFFFFFFFu)
             {
-                // path.cpp:115 / ao.cpp:27 / debug_renderer.h:17 — constant environment (material.h:219-232 over constant_texture)
-                rad = rad + thr * arr3(a.sc.env);
+                // path.cpp:115 / ao.cpp:27 / debug_renderer.h:17 — environment_map::eval material.h:219-232 (constant colour or HDR image)
+                rad = rad + thr * frt_env(a.sc, d);
                 end_path(a, pool, slot, rad, pixel, nonfinite);
                 terminated = true;
             }
@@ -219,7 +219,7 @@ __device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, co
                     // ao::Li ao.cpp:4-28: one direction drawn from the BSDF's pdf (get3d for scatter, then get2d for
                     // generate), occluded within 0.5 * world size.y -> black, else the environment colour.  A
                     // material that does not scatter (diffuse_light) also returns the environment.
-                    const float3 env = arr3(a.sc.env);
+                    const float3 env = frt_env(a.sc, d); // evaluated for the camera ray (ao.cpp:27)
                     if (mtype == FRT_MAT_DIFFUSE_LIGHT || !nonzero(env))
                     {
                         end_path(a, pool, slot, mtype == FRT_MAT_DIFFUSE_LIGHT ? env : f3(0.f, 0.f, 0.f), pixel, nonfinite);

@@ -31,6 +31,8 @@ struct frt_flat_scene
     std::vector<frt_light> lights;
     frt_camera camera{};
     float env[3] = {0, 0, 0};
+    const float *env_image = nullptr; // HDR environment image, owned by the Scene's image_texture (material.h:209-213)
+    uint32_t env_nx = 0, env_ny = 0;
     float ao_t_max = 0.f; // ao.cpp:19-22: 0.5 * size.y of the world's bounding box
     bool any_smooth = false;
     int max_depth_wide = 0;
@@ -49,6 +51,7 @@ struct frt_flat_scene
         d.camera = camera;
         std::memcpy(d.env_color, env, sizeof env);
         d.ao_t_max = ao_t_max;
+        d.env_image = env_image; d.env_nx = env_image ? env_nx : 0; d.env_ny = env_image ? env_ny : 0;
         return d;
     }
 };
@@ -87,8 +90,15 @@ public:
         out_.camera.lens_radius = (float)c.lens_radius;
         if (scene->env_map && scene->env_map->env_map_tex)
         {
-            const Vector3f e = constant_colour(scene->env_map->env_map_tex.get(), "environment map");
-            put3(out_.env, e);
+            texture *et = scene->env_map->env_map_tex.get();
+            image_texture *it = dynamic_cast<image_texture *>(et);
+            if (it && it->img && it->img->type == formats::STBI_HDR && it->img->dataf && it->img->nn == 3)
+            {
+                out_.env_image = it->img->dataf; // stays owned by the scene, like every other host array
+                out_.env_nx = (uint32_t)it->img->nx; out_.env_ny = (uint32_t)it->img->ny;
+            }
+            else
+                put3(out_.env, constant_colour(et, "environment map"));
         }
         if (out_.materials.empty()) { frt_material m{}; m.type = FRT_MAT_LAMBERTIAN; out_.materials.push_back(m); }
         aabb world_box;

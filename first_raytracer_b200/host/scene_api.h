@@ -13,6 +13,8 @@
 #include <cctype>
 #include <cfloat>
 #include <cmath>
+#include <cstdio>
+#include <stdexcept>
 #include <memory>
 #include <string>
 #include <vector>
@@ -100,6 +102,134 @@ public:
     Vector3f color;
 };
 
+// ---- image.h / image.cpp / texture.h:51-112 -------------------------------------------------------
+// The reference loads HDR environment images through stb_image (image.cpp:11-22, stbi_loadf).  Here: a reader
+// for the Radiance RGBE container itself (run-length coded or flat scanlines, "-Y h +X w" orientation), decoded the
+// way stbi_loadf does: channel = mantissa * 2^(exponent - 136), exponent 0 = black; row 0 = top of the picture.
+enum class formats { STBI_JPG, STBI_PNG, STBI_BMP, STBI_HDR };
+class image
+{
+public:
+    image() {}
+    image(const std::string &filename_, const formats &format = formats::STBI_HDR) : filename(filename_), type(format)
+    {
+        if (format != formats::STBI_HDR) throw std::runtime_error("image: only Radiance .hdr files are read (" + filename + ")");
+        load_rgbe();
+        dataf = pixels.data();
+    }
+    image(const float *rgb, int nx_, int ny_) : filename("memory"), type(formats::STBI_HDR), nx(nx_), ny(ny_), nn(3)
+    {
+        pixels.assign(rgb, rgb + (size_t)nx * ny * 3);
+        dataf = pixels.data();
+    }
+    std::string filename;
+    unsigned char *data = nullptr;
+    formats type = formats::STBI_HDR;
+    float *dataf = nullptr;
+    int nx = 0, ny = 0, nn = 3;
+
+private:
+    std::vector<float> pixels;
+    void load_rgbe()
+    {
+        FILE *f = std::fopen(filename.c_str(), "rb");
+        if (!f) throw std::runtime_error("image: cannot open " + filename);
+        std::vector<unsigned char> buf;
+        unsigned char chunk[65536];
+        size_t got;
+        while ((got = std::fread(chunk, 1, sizeof chunk, f)) > 0) buf.insert(buf.end(), chunk, chunk + got);
+        std::fclose(f);
+        size_t pos = 0;
+        auto line = [&]() {
+            std::string l;
+            while (pos < buf.size() && buf[pos] != '\n') l.push_back((char)buf[pos++]);
+            ++pos;
+            return l;
+        };
+        const std::string magic = line();
+        if (magic != "#?RADIANCE" && magic != "#?RGBE") throw std::runtime_error("image: not a Radiance file: " + filename);
+        bool rgbe = false;
+        for (;;)
+        {
+            const std::string l = line();
+            if (l.empty()) break;
+            if (l == "FORMAT=32-bit_rle_rgbe") rgbe = true;
+            if (pos >= buf.size()) break;
+        }
+        if (!rgbe) throw std::runtime_error("image: unsupported Radiance format in " + filename);
+        const std::string res = line();
+        if (std::sscanf(res.c_str(), "-Y %d +X %d", &ny, &nx) != 2 || nx <= 0 || ny <= 0)
+            throw std::runtime_error("image: unsupported orientation '" + res + "' in " + filename);
+        nn = 3;
+        pixels.resize((size_t)nx * ny * 3);
+        std::vector<unsigned char> scan((size_t)nx * 4);
+        auto need = [&](size_t n) { if (pos + n > buf.size()) throw std::runtime_error("image: truncated " + filename); };
+        auto convert = [&](const unsigned char *rgbe4, float *out) {
+            if (rgbe4[3] != 0)
+            {
+                const float f1 = std::ldexp(1.0f, (int)rgbe4[3] - (128 + 8));
+                out[0] = rgbe4[0] * f1; out[1] = rgbe4[1] * f1; out[2] = rgbe4[2] * f1;
+            }
+            else out[0] = out[1] = out[2] = 0.f;
+        };
+        if (nx < 8 || nx >= 32768 || !(pos + 4 <= buf.size() && buf[pos] == 2 && buf[pos + 1] == 2 && !(buf[pos + 2] & 0x80)))
+        {
+            need((size_t)nx * ny * 4); // flat
+            for (size_t i = 0; i < (size_t)nx * ny; ++i) convert(&buf[pos + 4 * i], &pixels[3 * i]);
+            return;
+        }
+        for (int j = 0; j < ny; ++j)
+        {
+            need(4);
+            if (buf[pos] != 2 || buf[pos + 1] != 2 || ((buf[pos + 2] << 8) | buf[pos + 3]) != nx)
+                throw std::runtime_error("image: bad scanline header in " + filename);
+            pos += 4;
+            for (int k = 0; k < 4; ++k)
+            {
+                int i = 0;
+                while (i < nx)
+                {
+                    need(1);
+                    int count = buf[pos++];
+                    if (count > 128)
+                    {
+                        count -= 128;
+                        need(1);
+                        const unsigned char value = buf[pos++];
+                        if (count == 0 || i + count > nx) throw std::runtime_error("image: corrupt run in " + filename);
+                        for (int z = 0; z < count; ++z) scan[(size_t)(i++) * 4 + k] = value;
+                    }
+                    else
+                    {
+                        if (count == 0 || i + count > nx) throw std::runtime_error("image: corrupt run in " + filename);
+                        need((size_t)count);
+                        for (int z = 0; z < count; ++z) scan[(size_t)(i++) * 4 + k] = buf[pos++];
+                    }
+                }
+            }
+            for (int i = 0; i < nx; ++i) convert(&scan[(size_t)i * 4], &pixels[((size_t)j * nx + i) * 3]);
+        }
+    }
+};
+class image_texture : public texture
+{
+public:
+    image_texture() {}
+    explicit image_texture(std::unique_ptr<image> img_) : img(std::move(img_)) {}
+    Vector3f value(const hit_record &rec) const override // texture.h:60-86 (HDR branch)
+    {
+        const int nx = img->nx, ny = img->ny;
+        int i = (int)(rec.u * nx), j = (int)(rec.v * ny);
+        if (i < 0 || i > nx) i = ((i % nx) + nx) % nx;
+        if (j < 0 || j > ny) j = ((j % ny) + ny) % ny;
+        if (i == nx) i = nx - 1;
+        if (j == ny) j = ny - 1;
+        const float *t = img->dataf + ((size_t)j * nx + i) * 3;
+        return Vector3f(t[0], t[1], t[2]);
+    }
+    std::unique_ptr<image> img;
+};
+
 // ---- material.h ---------------------------------------------------------------------------------
 class material
 {
@@ -159,6 +289,10 @@ public:
 class environment_map : public material
 {
 public:
+    explicit environment_map(std::string env_map_filename_) : env_map_filename(std::move(env_map_filename_)) // material.h:209-213
+    {
+        env_map_tex = std::make_unique<image_texture>(std::make_unique<image>(env_map_filename, formats::STBI_HDR));
+    }
     explicit environment_map(std::unique_ptr<texture> e) : env_map_tex(std::move(e)) {}
     std::string env_map_filename;
     std::unique_ptr<texture> env_map_tex;

@@ -184,6 +184,15 @@ Scene *make_scene(const std::string &name, double aspect, frt_scene_ids *ids)
         s->env_map.reset(new environment_map(std::make_unique<constant_texture>(Vector3f(0.5, 0.6, 0.8))));
         return s;
     }
+    // "<scene>+hdr": the same scene under the HDR lat-long environment image main.cpp:170 loads (data/test.hdr,
+    // environment_map(filename) material.h:209-213)
+    const std::string hdr = "+hdr";
+    if (name.size() > hdr.size() && name.compare(name.size() - hdr.size(), hdr.size(), hdr) == 0)
+    {
+        Scene *s = make_scene(name.substr(0, name.size() - hdr.size()), aspect, ids);
+        s->env_map.reset(new environment_map(asset("data/test.hdr")));
+        return s;
+    }
     if (name == "cornell" || name == "cornell_box_obj") return cornell_box_obj(aspect, "Original", ids);
     if (name == "cornell_glossy") return cornell_box_obj(aspect, "Glossy", ids);
     if (name == "cornell_sphere") return cornell_box_obj(aspect, "Sphere", ids);

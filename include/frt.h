@@ -121,6 +121,11 @@ typedef struct frt_scene_desc {
     frt_camera camera;
     float env_color[3]; /* environment_map over a constant_texture, material.h:219-232 */
     float ao_t_max;     /* 0.5 * world bounding box size.y: the occlusion range of ao::Li (ao.cpp:19-22) */
+    /* environment_map over an HDR image_texture (material.h:209-232, texture.h:51-86): env_nx * env_ny * 3 floats,
+     * row 0 = top of the lat-long image (theta = 0, direction +y), nearest texel, no filtering.  NULL = the
+     * constant env_color above. */
+    const float *env_image;
+    uint32_t env_nx, env_ny;
 } frt_scene_desc;
 
 /* One unit of rendering work: the pixel rectangle and sample range path::Render's row loop

@@ -60,6 +60,28 @@ static inline real len(v3 a) { return rsqrt_(dot(a, a)); }
 static inline v3 unit(v3 a) { return dvs(a, len(a)); } /* geometry.h unit_vector */
 static inline int nonzero(v3 a) { return a.x != 0 || a.y != 0 || a.z != 0; }
 static inline v3 f3(const float *p) { return V((real)p[0], (real)p[1], (real)p[2]); }
+
+/* environment_map::eval material.h:219-232: unit direction -> phi = atan2(x, -z) (+2 pi if negative), theta = acos(y)
+ * -> u = phi / 2 pi, v = theta / pi -> env_map_tex->value.  constant_texture texture.h:17-28 returns its colour;
+ * image_texture::value texture.h:60-86 over an HDR image: i = int(u nx), j = int(v ny), wrapped with modulo when
+ * outside [0, n], i == nx -> nx - 1 (same for j), the three floats at (j nx + i) 3, no filtering. */
+static int modulo_(int a, int b) { const int r = a % b; return r < 0 ? r + b : r; } /* util.h modulo */
+static v3 env_eval(const frt_scene_desc *sc, v3 d)
+{
+    if (!sc->env_image) return f3(sc->env_color);
+    const v3 dir = unit(d);
+    real phi = ratan2(dir.x, -dir.z), theta = racos(dir.y);
+    phi = (phi < 0) ? (phi + PI * 2) : phi;
+    theta = (theta < 0) ? (theta + PI) : theta;
+    const real u = phi / (R(2.0) * PI), v = theta / PI;
+    const int nx = (int)sc->env_nx, ny = (int)sc->env_ny;
+    int i = (int)(u * nx), j = (int)(v * ny);
+    if (i < 0 || i > nx) i = modulo_(i, nx);
+    if (j < 0 || j > ny) j = modulo_(j, ny);
+    if (i == nx) i = nx - 1;
+    if (j == ny) j = ny - 1;
+    return f3(sc->env_image + ((size_t)j * nx + i) * 3);
+}
 static inline v3 q3(frt_float4 q) { return V((real)q.x, (real)q.y, (real)q.z); }
 static inline uint32_t wbits(frt_float4 q) { uint32_t u; memcpy(&u, &q.w, 4); return u; }
 static inline real comp(v3 a, int i) { return i == 0 ? a.x : (i == 1 ? a.y : a.z); }
@@ -722,7 +744,7 @@ static v3 Li(octx *cx, v3 o, v3 d, int depth, const hitrec *prev, uint32_t prev_
     hitrec h;
     cx->st.closest_rays++;
     if (!world_hit(cx, o, d, REAL_FLT_MAX, 0, &h)) /* path.cpp:10 */
-        return f3(sc->env_color);                  /* path.cpp:115, constant environment material.h:219-232 */
+        return env_eval(sc, d);                    /* path.cpp:115, environment_map::eval material.h:219-232 */
     fill_hit(sc, o, d, &h);
     const frt_material *m = &sc->materials[h.mat];
     /* diffuse_light::emitted material.h:184-190 */
@@ -850,7 +872,7 @@ static v3 Li_ao(octx *cx, v3 o, v3 d, sampler *rs)
             if (world_hit(cx, h.p, dir, (real)sc->ao_t_max, 1, &occ)) return V(0, 0, 0);
         }
     }
-    return f3(sc->env_color); /* ao.cpp:27 */
+    return env_eval(sc, d); /* ao.cpp:27: evaluated for the camera ray */
 }
 
 /* ---- normals_renderer::Li debug_renderer.h:8-17 ------------------------------------------------- */
@@ -860,7 +882,7 @@ static v3 Li_direct(octx *cx, v3 o, v3 d, sampler *rs)
     const frt_scene_desc *sc = cx->sc;
     hitrec h;
     cx->st.closest_rays++;
-    if (!world_hit(cx, o, d, REAL_FLT_MAX, 0, &h)) return f3(sc->env_color);
+    if (!world_hit(cx, o, d, REAL_FLT_MAX, 0, &h)) return env_eval(sc, d);
     fill_hit(sc, o, d, &h);
     const frt_material *m = &sc->materials[h.mat];
     v3 Le = V(0, 0, 0);
@@ -899,7 +921,7 @@ static v3 Li_normals(octx *cx, v3 o, v3 d)
         fill_hit(cx->sc, o, d, &h);
         return h.n;
     }
-    return f3(cx->sc->env_color);
+    return env_eval(cx->sc, d);
 }
 
 /* ---- path::Render's sample loop path.cpp:129-143 over a tile; camera::get_ray camera.h:30-35 -- */

@@ -270,7 +270,9 @@ static built_scene &build_scene(const std::string &full_name, double aspect)
 {
     // "<scene>+sky": same scene under a constant sky-blue environment (gives ao::Li something to return)
     const bool sky = full_name.size() > 4 && full_name.compare(full_name.size() - 4, 4, "+sky") == 0;
-    const std::string name = sky ? full_name.substr(0, full_name.size() - 4) : full_name;
+    // "<scene>+hdr": same scene under the HDR environment image of main.cpp:170 (the reference's own stb loader)
+    const bool hdr = full_name.size() > 4 && full_name.compare(full_name.size() - 4, 4, "+hdr") == 0;
+    const std::string name = (sky || hdr) ? full_name.substr(0, full_name.size() - 4) : full_name;
     built_scene &b = *new built_scene;
     std::vector<hitable *> lights;
     std::vector<hitable *> list;
@@ -378,7 +380,8 @@ static built_scene &build_scene(const std::string &full_name, double aspect)
     hitable **arr = new hitable *[list.size()];
     for (size_t i = 0; i < list.size(); ++i) arr[i] = list[i];
     b.scene.reset(new Scene(parallel_bvh_node::create_bvh(arr, (int)list.size(), 0.0, 0.0),
-                            new environment_map(std::make_unique<constant_texture>(env)), cam, lights));
+                            hdr ? new environment_map(g_assets + "/data/test.hdr")
+                                : new environment_map(std::make_unique<constant_texture>(env)), cam, lights));
     return b;
 }
 

@@ -49,7 +49,8 @@ def trace_fixture(name, aspect, n_cam=48, n_rand=6000, n_seg=4000):
 
 def render_fixture(name, nx, ny, spp, integrator="path"):
     """integrator: path::Li, ao::Li (ao.cpp:4-28) or normals_renderer::Li (debug_renderer.h:8-17); a scene name
-    ending in +sky is the scene under a constant sky-blue environment (ref_main.cpp build_scene)."""
+    ending in +sky is the scene under a constant sky-blue environment, in +hdr under the HDR lat-long image
+    assets/data/test.hdr read by the reference's own stb loader (ref_main.cpp build_scene)."""
     img, info = refutil.ref_render(name, nx, ny, spp, ctr=True, seed=SEED, integrator=integrator)
     tag = "render" if integrator == "path" else f"render_{integrator}"
     np.savez_compressed(OUT / f"{tag}_{name}_{nx}x{ny}x{spp}.npz", image=img.astype(np.float32), seed=SEED,
@@ -97,7 +98,10 @@ OTHER_INTEGRATOR_CASES = [("teapot", 48, 27, 2, "ao"), ("cornell_glossy+sky", 32
                           # with the un-normalised to_light overflows float there (the reference's film holds inf)
                           ("cornell", 32, 32, 2, "direct"), ("cornell_glossy", 32, 32, 2, "direct"),
                           ("teapot", 48, 27, 2, "direct"), ("teapot+sky", 48, 27, 1, "direct"),
-                          ("cornell", 128, 128, 4, "direct")]
+                          ("cornell", 128, 128, 4, "direct"),
+                          # environment_map over the HDR image of main.cpp:170 (material.h:209-232, texture.h:60-86)
+                          ("teapot+hdr", 48, 27, 2, "path"), ("veach+hdr", 48, 32, 2, "path"),
+                          ("teapot+hdr", 160, 90, 4, "path")]
 
 
 def main():

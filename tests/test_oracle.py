@@ -38,7 +38,10 @@ OTHER_INTEGRATOR_CASES = [("teapot", 48, 27, 2, "ao"), ("cornell_glossy+sky", 32
                           ("veach+sky", 48, 32, 2, "path"),
                           # ass_1_renderer::Li assignment_1.cpp:4-38
                           ("cornell", 32, 32, 2, "direct"), ("cornell_glossy", 32, 32, 2, "direct"),
-                          ("teapot", 48, 27, 2, "direct"), ("teapot+sky", 48, 27, 1, "direct")]
+                          ("teapot", 48, 27, 2, "direct"), ("teapot+sky", 48, 27, 1, "direct"),
+                          # environment_map over the HDR image of main.cpp:170 (material.h:209-232, texture.h:60-86)
+                          ("teapot+hdr", 48, 27, 2, "path"), ("veach+hdr", 48, 32, 2, "path"),
+                          ("teapot+hdr", 160, 90, 4, "path")]
 
 
 @pytest.mark.parametrize("name,nx,ny,spp,integrator", OTHER_INTEGRATOR_CASES)
