@@ -162,3 +162,66 @@ def test_checkpoint_file_round_trip(tmp_path):
     ck = api.load_checkpoint(tmp_path / "f.npz")
     assert ck["sums"].dtype == np.float32 and np.array_equal(ck["sums"], sums)
     assert (ck["spp_done"], ck["seed"], ck["scene"], ck["integrator"]) == (17, 4, "veach", "ao")
+
+
+def _write_hdr(path, rgbe, rle):
+    """A Radiance picture from [ny, nx, 4] uint8 RGBE texels: flat, or the run-length coded scanlines of
+    FORMAT=32-bit_rle_rgbe (per channel: count > 128 = a run of count - 128 equal bytes, else count literal bytes)."""
+    ny, nx, _ = rgbe.shape
+    out = bytearray(b"#?RADIANCE\n# test\nFORMAT=32-bit_rle_rgbe\n\n" + f"-Y {ny} +X {nx}\n".encode())
+    if not rle:
+        out += rgbe.tobytes()
+    else:
+        for j in range(ny):
+            out += bytes([2, 2, nx >> 8, nx & 255])
+            for k in range(4):
+                row, i = rgbe[j, :, k], 0
+                while i < nx:
+                    run = 1
+                    while i + run < nx and run < 127 and row[i + run] == row[i]:
+                        run += 1
+                    if run >= 3:
+                        out += bytes([128 + run, int(row[i])])
+                        i += run
+                    else:
+                        lit = min(nx - i, 5)
+                        out += bytes([lit]) + row[i:i + lit].tobytes()
+                        i += lit
+    path.write_bytes(bytes(out))
+
+
+@pytest.mark.parametrize("nx,ny,rle", [(4, 3, False), (16, 5, True), (40, 6, True)])
+def test_radiance_hdr_reader_and_environment_map(built, tmp_path, monkeypatch, nx, ny, rle):
+    """environment_map(filename) (material.h:209-213) through the host layer's own Radiance reader: the floats handed
+    to frt_scene_desc::env_image are mantissa * 2^(exponent - 136) as stbi_loadf (image.cpp:16) produces, exponent 0 =
+    black, row 0 = top — for flat and for run-length coded files (the reference's stb-loaded data/test.hdr is
+    covered by the +hdr golden renders)."""
+    rng = np.random.default_rng(nx * 100 + ny)
+    rgbe = rng.integers(0, 256, (ny, nx, 4), dtype=np.uint8)
+    rgbe[:, :, 3] = rng.integers(120, 140, (ny, nx))
+    rgbe[0, : nx // 2] = rgbe[0, 0]  # a long run
+    rgbe[1, 1, 3] = 0                # exponent 0: black whatever the mantissas
+    for sub in ("CornellBox", "cube", "veach_mi"):
+        (tmp_path / sub).symlink_to(REPO / "assets" / sub)
+    (tmp_path / "data").mkdir()
+    _write_hdr(tmp_path / "data" / "test.hdr", rgbe, rle)
+    monkeypatch.setenv("FRT_ASSETS", str(tmp_path))
+    scene = api.HostScene("cornell+hdr", 1.0, 2)
+    d = scene.desc
+    assert (d.env_nx, d.env_ny) == (nx, ny) and d.env_image
+    got = np.ctypeslib.as_array(C.cast(d.env_image, C.POINTER(C.c_float)), shape=(ny, nx, 3)).copy()
+    want = rgbe[:, :, :3].astype(np.float32) * np.ldexp(np.float32(1), rgbe[:, :, 3:].astype(np.int32) - 136).astype(np.float32)
+    want[rgbe[:, :, 3] == 0] = 0
+    assert np.array_equal(got, want)
+    scene.close()
+    # a truncated file is an error, not a partly filled image
+    full = (tmp_path / "data" / "test.hdr").read_bytes()
+    (tmp_path / "data" / "test.hdr").write_bytes(full[:-7])
+    with pytest.raises(api.FrtError):
+        api.HostScene("cornell+hdr", 1.0, 2)
+
+
+def test_constant_environment_has_no_image(built):
+    scene = api.HostScene("cornell+sky", 1.0, 2)
+    assert not scene.desc.env_image and scene.desc.env_nx == 0
+    assert np.allclose(list(scene.desc.env_color), [0.5, 0.6, 0.8])
