@@ -3,7 +3,7 @@ JSON line per config; the contract bench is bench.py).
   config 3  veach_mi (rough_conductor plates, 5 sphere lights) 768x512 and 1920x1080, 256 spp
   config 4  mesh scene (teapot stand-in, 15 704 triangles) 1920x1080, 256 spp
   config 5  synthetic triangle soup: incoherent closest-hit and shadow ray casts, unsorted / Morton-sorted
-usage: python scripts/bench_scenes.py [veach] [teapot] [soup]      env: SOUP_TRIS (1e7), SOUP_RAYS (2**26)"""
+usage: python scripts/bench_scenes.py [veach] [teapot] [hdr] [soup]      env: SOUP_TRIS (1e7), SOUP_RAYS (2**26)"""
 import json, os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
@@ -91,6 +91,8 @@ for w in which:
         render_cfg("veach", 768, 512, 256); render_cfg("veach", 1920, 1080, 256)
     elif w == "teapot":
         render_cfg("teapot", 1920, 1080, 256)
+    elif w == "hdr":  # the same scenes lit by the HDR lat-long environment image
+        render_cfg("teapot+hdr", 1920, 1080, 256); render_cfg("veach+hdr", 1920, 1080, 256)
     elif w == "cornell":
         render_cfg("cornell", 512, 512, 256)
     elif w == "soup":
