@@ -274,9 +274,12 @@ def roofline_pass(ctx, api, spp_range, peaks, base_flags, stream):
         n_launch, avg_ms, kernel = 1, e0.elapsed_time(e1), "k_wavefront"
         bytes_per_launch = (st["closest_rays"] + st["shadow_rays"]) * b_ray
     achieved = bytes_per_launch / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+    # dram__bytes_read.sum + dram__bytes_write.sum of this very launch (k_wavefront, 1080p x 1024 spp on one GPU) from the
+    # ncu pass of scripts/gpu_traffic.sh: profiles/r01_ncu_traffic_1024spp.csv.  Other launch shapes: not captured.
+    traffic = 27660544 + 294398976 if (not streamed and (s1 - s0) == 1024) else None
     return {
         "bound": "hbm", "kernel": kernel, "achieved": achieved, "peak": peak, "unit": "GB/s",
-        "frac": achieved / peak, "traffic": None,
+        "frac": achieved / peak, "traffic": traffic,
         "peak_source": "MEASURED_PEAKS.json (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s",
         "avg_launch_ms": avg_ms, "launches": n_launch, "algorithmic_bytes_per_launch": bytes_per_launch,
         "stage_ms_mean_over_ctas" if not streamed else "kernel_ms": kms,
