@@ -1,5 +1,7 @@
 # GPU box: ncu launch list + one full capture of the persistent wavefront kernel (B200_PROFILING.md:
 # each ncu pass only after the same command exited 0 without ncu)
+# Keep SPP small (8): --set full replays the launch ~40 times with instrumented passes (a 1024-spp launch takes ~19 min
+# and two copies of the report exceed gpurun_out's 64 MiB); DRAM bytes of the full-size launch: scripts/gpu_traffic.sh
 mkdir -p gpurun_out
 CMD="python bench.py --steps 1 --warmup 1 --spp ${SPP:-8} --no-e2e --no-cpu-baseline --no-roofline"
 $CMD > gpurun_out/prof_plain.log 2>&1 &&
