@@ -82,7 +82,9 @@ class frt_scene_desc(C.Structure):
                 ("tri_normals", C.c_void_p), ("spheres", C.c_void_p), ("n_materials", C.c_uint32),
                 ("n_lights", C.c_uint32), ("materials", C.c_void_p), ("lights", C.c_void_p),
                 ("camera", frt_camera), ("env_color", C.c_float * 3), ("ao_t_max", C.c_float),
-                ("env_image", C.c_void_p), ("env_nx", C.c_uint32), ("env_ny", C.c_uint32)]
+                ("env_image", C.c_void_p), ("env_nx", C.c_uint32), ("env_ny", C.c_uint32),
+                ("n_textures", C.c_uint32), ("reserved0", C.c_uint32), ("textures", C.c_void_p),
+                ("tex_texels", C.c_void_p), ("n_texels", C.c_uint64), ("tri_uv", C.c_void_p)]
 
 
 RAY_DTYPE = np.dtype([("o", "<f4", 3), ("d", "<f4", 3)])
@@ -93,6 +95,7 @@ MATERIAL_DTYPE = np.dtype([("type", "<u4"), ("p", "<f4", 15)])
 LIGHT_DTYPE = np.dtype([("kind", "<u4"), ("material", "<u4"), ("flags", "<u4"), ("pad", "<u4"),
                         ("v0", "<f4", 4), ("v1", "<f4", 4), ("v2", "<f4", 4), ("n0", "<f4", 4),
                         ("n1", "<f4", 4), ("n2", "<f4", 4), ("reserved", "<f4", 4)])
+TEXTURE_DTYPE = np.dtype([("kind", "<u4"), ("a", "<u4"), ("b", "<u4"), ("c", "<u4"), ("p", "<f4", 4)])
 SPHERE_DTYPE = np.dtype([("c", "<f4", 3), ("radius", "<f4"), ("material", "<u4"), ("prim_id", "<u4"),
                          ("pad", "<u4", 2)])
 
@@ -219,6 +222,9 @@ class HostScene:
             "spheres": self._view(d.spheres, d.n_spheres, SPHERE_DTYPE),
             "materials": self._view(d.materials, d.n_materials, MATERIAL_DTYPE),
             "lights": self._view(d.lights, d.n_lights, LIGHT_DTYPE),
+            "textures": self._view(d.textures, d.n_textures, TEXTURE_DTYPE),
+            "tex_texels": self._view(d.tex_texels, d.n_texels * 3, np.float32).reshape(-1, 3),
+            "tri_uv": self._view(d.tri_uv, d.n_tris * 6 if d.tri_uv else 0, np.float32).reshape(-1, 3, 2),
         }
 
     def camera_rays(self, nx: int, ny: int) -> np.ndarray:

@@ -105,7 +105,8 @@ void frt_destroy(frt_ctx *ctx)
         cudaSetDevice(d.ordinal);
         cudaStreamSynchronize(d.stream);
         for (void *p : d.pool_allocs) cudaFree(p);
-        void *ptrs[] = {d.d_nodes, d.d_tris, d.d_normals, d.d_spheres, d.d_mats, d.d_lights, d.d_env, d.d_ctr, d.d_film, d.d_film_peer};
+        void *ptrs[] = {d.d_nodes, d.d_tris, d.d_normals, d.d_spheres, d.d_mats, d.d_lights, d.d_env, d.d_ctr, d.d_film, d.d_film_peer,
+                        d.d_textures, d.d_texels, d.d_tri_uv};
         for (void *p : ptrs) if (p) cudaFree(p);
         if (d.h_ctr) cudaFreeHost(d.h_ctr);
         for (cudaEvent_t e : d.timers.ev) cudaEventDestroy(e);
@@ -168,6 +169,25 @@ static int validate_scene(frt_ctx *ctx, const frt_scene_desc *s)
     for (uint32_t i = 0; i < s->n_lights; ++i)
         if (s->lights[i].material >= s->n_materials || s->lights[i].kind > FRT_LIGHT_SPHERE)
             return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: light %u invalid", i);
+    // surface textures: table entries, checker children and image extents must stay inside their arrays
+    if (s->n_textures && !s->textures) return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: textures is NULL");
+    if (s->n_texels && !s->tex_texels) return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: tex_texels is NULL");
+    for (uint32_t i = 0; i < s->n_textures; ++i)
+    {
+        const frt_texture &t = s->textures[i];
+        if (t.kind > FRT_TEX_IMAGE) return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: texture %u has unknown kind", i);
+        if (t.kind == FRT_TEX_CHECKER && (t.a >= s->n_textures || t.b >= s->n_textures || t.a == i || t.b == i))
+            return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: checker texture %u refers to texture %u / %u", i, t.a, t.b);
+        if (t.kind == FRT_TEX_IMAGE && (t.b == 0 || t.c == 0 || t.b > 65536 || t.c > 65536 || (uint64_t)t.a + (uint64_t)t.b * t.c > s->n_texels))
+            return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: image texture %u (%u x %u at texel %u) outside tex_texels", i, t.b, t.c, t.a);
+    }
+    for (uint32_t i = 0; i < s->n_materials; ++i)
+        for (int slot : {FRT_MAT_TEX_A, FRT_MAT_TEX_B})
+        {
+            uint32_t ref;
+            memcpy(&ref, &s->materials[i].p[slot], 4);
+            if (ref > s->n_textures) return fail(ctx, FRT_ERR_INVALID, "frt_upload_scene: material %u refers to texture %u of %u", i, ref - 1, s->n_textures);
+        }
     return FRT_OK;
 }
 
@@ -185,6 +205,7 @@ int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *s)
     memcpy(v.env, s->env_color, sizeof v.env);
     ctx->ao_t_max = s->ao_t_max;
     v.env_nx = s->env_image ? s->env_nx : 0; v.env_ny = s->env_image ? s->env_ny : 0;
+    v.n_textures = s->n_textures;
     for (Device &d : ctx->dev)
     {
         CU(cudaSetDevice(d.ordinal));
@@ -196,6 +217,9 @@ int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *s)
         if ((rc = upload_array(ctx, &d.d_mats, s->materials, s->n_materials)) != FRT_OK) return rc;
         if ((rc = upload_array(ctx, &d.d_lights, s->lights, s->n_lights)) != FRT_OK) return rc;
         if ((rc = upload_array(ctx, &d.d_env, s->env_image, s->env_image ? 3 * (size_t)s->env_nx * s->env_ny : 0)) != FRT_OK) return rc;
+        if ((rc = upload_array(ctx, &d.d_textures, s->textures, s->n_textures)) != FRT_OK) return rc;
+        if ((rc = upload_array(ctx, &d.d_texels, s->tex_texels, 3 * (size_t)s->n_texels)) != FRT_OK) return rc;
+        if ((rc = upload_array(ctx, &d.d_tri_uv, s->tri_uv, (s->tri_uv && s->n_textures) ? 6 * (size_t)s->n_tris : 0)) != FRT_OK) return rc;
     }
     uint32_t bsdf_types = 0;
     for (uint32_t i = 0; i < s->n_materials; ++i)

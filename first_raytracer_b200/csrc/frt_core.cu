@@ -30,7 +30,7 @@ struct Device
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     // scene
     void *d_nodes = nullptr, *d_tris = nullptr, *d_normals = nullptr, *d_spheres = nullptr, *d_mats = nullptr,
-         *d_lights = nullptr, *d_env = nullptr;
+         *d_lights = nullptr, *d_env = nullptr, *d_textures = nullptr, *d_texels = nullptr, *d_tri_uv = nullptr;
     // pool
     PathPool pool{};
     std::vector<void *> pool_allocs;
@@ -273,6 +273,9 @@ DevScene device_view(const frt_ctx *ctx, const Device &d, double any_tend = 1.0 
     sc.materials = (const frt_material *)d.d_mats;
     sc.lights = (const frt_light *)d.d_lights;
     sc.env_img = (const float *)d.d_env;
+    sc.textures = (const frt_texture *)d.d_textures;
+    sc.tex_texels = (const float *)d.d_texels;
+    sc.tri_uv = (const float *)d.d_tri_uv;
     return sc;
 }
 

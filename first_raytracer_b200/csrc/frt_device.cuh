@@ -24,6 +24,11 @@ struct DevScene
     float env[3];
     const float *env_img; // lat-long HDR environment image (3 floats per texel, row 0 = top) or nullptr
     uint32_t env_nx, env_ny;
+    // surface textures (texture.h:30-112): table, texels, per-triangle mesh uv (6 floats); all null without textures
+    const frt_texture *textures;
+    const float *tex_texels;
+    const float *tri_uv;
+    uint32_t n_textures;
     // upper end of an occlusion query (uniform per launch): 1 - SHADOW_EPSILON for path.cpp:50 and the ray-cast
     // entry, ao_t_max for ao.cpp:22; with its float32 brackets
     double any_tend;
@@ -85,4 +90,48 @@ __device__ __noinline__ float3 frt_env_image(const float *img, uint32_t nx, uint
 __device__ __forceinline__ float3 frt_env(const DevScene &sc, float3 d)
 {
     return sc.env_img ? frt_env_image(sc.env_img, sc.env_nx, sc.env_ny, d.x, d.y, d.z) : arr3(sc.env);
+}
+
+// ---- surface textures -----------------------------------------------------------------------
+// (int)x as the reference's x86 build converts it (cvttsd2si): NaN and out-of-range values give INT_MIN.  The
+// 1000-radius ground sphere of random_scene feeds asin(1000) = NaN through this (sphere.h:51 passes the
+// UN-normalised p - center to get_sphere_uv).
+__device__ __forceinline__ int frt_f2i(float x) { return (x >= -2147483648.0f && x < 2147483648.0f) ? (int)x : (int)0x80000000; }
+__device__ __forceinline__ int frt_modulo(int a, int b) { const int r = a % b; return r < 0 ? r + b : r; } // util.h:125-128
+// get_sphere_uv hitable.h:15-21 on p = hit point - center (not divided by the radius, sphere.h:51)
+__device__ __forceinline__ void frt_sphere_uv(float3 p, float &u, float &v)
+{
+    const float phi = atan2f(p.z, p.x), theta = asinf(p.y);
+    u = 1.0f - (phi + FRT_PI) / (2.0f * FRT_PI);
+    v = (theta + FRT_PI / 2.0f) / FRT_PI;
+}
+// texture::value(hrec) for texture reference `ref` (1 + index): constant_texture texture.h:17-28, checker_texture
+// texture.h:30-49 (picks tex1 when the two cell parities agree, else tex0, and evaluates that one), image_texture
+// texture.h:60-86 (nearest texel, indices outside [0, n] wrapped with modulo, i == n clamped to n - 1).
+__device__ __noinline__ float3 frt_tex_eval(const DevScene &sc, uint32_t ref, float u, float v)
+{
+    uint32_t idx = ref - 1u;
+    for (int level = 0; level < 8; ++level)
+    {
+        const frt_texture t = sc.textures[idx];
+        if (t.kind == FRT_TEX_CHECKER)
+        {
+            const int x = 2 * frt_modulo(frt_f2i(u * t.p[0] * 2.0f), 2) - 1, y = 2 * frt_modulo(frt_f2i(v * t.p[1] * 2.0f), 2) - 1;
+            idx = (x * y == 1) ? t.b : t.a;
+            continue;
+        }
+        if (t.kind == FRT_TEX_IMAGE)
+        {
+            const int nx = (int)t.b, ny = (int)t.c;
+            int i = frt_f2i(u * (float)nx), j = frt_f2i(v * (float)ny);
+            if (i < 0 || i > nx) i = frt_modulo(i, nx);
+            if (j < 0 || j > ny) j = frt_modulo(j, ny);
+            if (i == nx) i = nx - 1;
+            if (j == ny) j = ny - 1;
+            const float *q = sc.tex_texels + 3 * ((size_t)t.a + (size_t)j * nx + i);
+            return f3(__ldg(q), __ldg(q + 1), __ldg(q + 2));
+        }
+        return f3(t.p[0], t.p[1], t.p[2]);
+    }
+    return f3(0.f, 0.f, 0.f);
 }

@@ -136,7 +136,8 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
             const size_t smem = (size_t)ctx->wf_slots * FRT_WF_SLOT_BYTES;
             // no more CTAs than can be kept busy: one CTA-iteration consumes up to wf_slots samples
             const unsigned long long want = (total + ctx->wf_slots - 1) / ctx->wf_slots;
-            const bool other = t->integrator != FRT_INTEGRATOR_PATH;
+            // the general kernel: the integrators next to `path`, and `path` itself over textured surfaces
+            const bool other = t->integrator != FRT_INTEGRATOR_PATH || ctx->host_view.n_textures != 0;
             const WfConfig &wc = other ? wf_other : wf_configs[ctx->wf_config];
             const int resident = other ? d.blocks_wavefront_other : d.blocks_wavefront;
             if (resident < 1) return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: FRT_WF_SLOTS=%u leaves no room for this integrator's kernel", ctx->wf_slots);

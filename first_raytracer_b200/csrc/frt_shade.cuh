@@ -197,7 +197,32 @@ __device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, co
                         h.n = unit_vector((1.0f - hw.y - hw.z) * f3(__ldg(np)) + hw.y * f3(__ldg(np + 1)) + hw.z * f3(__ldg(np + 2)));
                     }
                 }
-                const frt_material &m = a.sc.materials[mat_id];
+                const frt_material *mp = &a.sc.materials[mat_id];
+                frt_material mtex;
+                if (OTHER && a.sc.n_textures)
+                {
+                    // textured colours (texture.h:30-112) are looked up at hit_record::u, v and put where the constant
+                    // colour would be; only the general kernel carries this (the path kernel of untextured scenes does not)
+                    const unsigned int ta = __float_as_uint(mp->p[FRT_MAT_TEX_A]), tb = __float_as_uint(mp->p[FRT_MAT_TEX_B]);
+                    if (ta | tb)
+                    {
+                        float tu = 0.0f, tv = 0.0f;
+                        if (is_sphere) frt_sphere_uv(h.p - sph_c, tu, tv); // sphere.h:51
+                        else if (a.sc.tri_uv)
+                        {
+                            // triangle.h:104-106: (1 - u - v) uv[V0] + u uv[V1] + v uv[V2]
+                            const float *q = a.sc.tri_uv + 6 * (size_t)prim;
+                            const float w0 = 1.0f - hw.y - hw.z;
+                            tu = w0 * __ldg(q) + hw.y * __ldg(q + 2) + hw.z * __ldg(q + 4);
+                            tv = w0 * __ldg(q + 1) + hw.y * __ldg(q + 3) + hw.z * __ldg(q + 5);
+                        }
+                        mtex = *mp;
+                        if (ta) { const float3 c = frt_tex_eval(a.sc, ta, tu, tv); mtex.p[0] = c.x; mtex.p[1] = c.y; mtex.p[2] = c.z; }
+                        if (tb) { const float3 c = frt_tex_eval(a.sc, tb, tu, tv); mtex.p[3] = c.x; mtex.p[4] = c.y; mtex.p[5] = c.z; }
+                        mp = &mtex;
+                    }
+                }
+                const frt_material &m = *mp;
                 const unsigned int mtype = m.type;
 
                 if (OTHER && a.tile.integrator == FRT_INTEGRATOR_NORMALS)

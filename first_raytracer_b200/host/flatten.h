@@ -36,6 +36,9 @@ struct frt_flat_scene
     float ao_t_max = 0.f; // ao.cpp:19-22: 0.5 * size.y of the world's bounding box
     bool any_smooth = false;
     int max_depth_wide = 0;
+    // surface textures (texture.h:30-112): table, texels of every image_texture back to back, per-triangle mesh uv
+    std::vector<frt_texture> textures;
+    std::vector<float> tex_texels, tri_uv;
 
     frt_scene_desc desc() const
     {
@@ -52,6 +55,9 @@ struct frt_flat_scene
         std::memcpy(d.env_color, env, sizeof env);
         d.ao_t_max = ao_t_max;
         d.env_image = env_image; d.env_nx = env_image ? env_nx : 0; d.env_ny = env_image ? env_ny : 0;
+        d.n_textures = (uint32_t)textures.size(); d.textures = textures.empty() ? nullptr : textures.data();
+        d.n_texels = tex_texels.size() / 3; d.tex_texels = tex_texels.empty() ? nullptr : tex_texels.data();
+        d.tri_uv = (!textures.empty() && tri_uv.size() == tris.size() * 2) ? tri_uv.data() : nullptr;
         return d;
     }
 };
@@ -67,7 +73,7 @@ public:
     frt_flat_scene flatten(const Scene *scene)
     {
         out_ = frt_flat_scene();
-        bn_.clear(); mat_index_.clear(); next_id_ = 0;
+        bn_.clear(); mat_index_.clear(); tex_index_.clear(); next_id_ = 0;
         pad_ = 0.0;
         int root = scene->world ? import(scene->world.get()) : -1;
         if (root >= 0)
@@ -121,7 +127,8 @@ private:
     static Vector3f constant_colour(texture *t, const char *what)
     {
         if (!dynamic_cast<constant_texture *>(t))
-            throw std::runtime_error(std::string("frt_flattener: only constant_texture is supported for ") + what);
+            throw std::runtime_error(std::string("frt_flattener: only constant_texture is supported for ") + what +
+                                     " (emitters and the environment; surface colours may be checker / image textures)");
         hit_record rec;
         rec.u = 0; rec.v = 0;
         return t->value(rec);
@@ -261,6 +268,11 @@ private:
             out_.tris.push_back(pack(t->mesh->vertices[t->V[1]], material_index(t->mat_ptr)));
             out_.tris.push_back(pack(t->mesh->vertices[t->V[2]], flags));
             for (int k = 0; k < 3; ++k) out_.tri_normals.push_back(pack(t->mesh->normals[t->V[k]], 0));
+            for (int k = 0; k < 3; ++k) // triangle.h:104-106 interpolates these
+            {
+                const Vector2f uv = t->mesh->uv ? t->mesh->uv[t->V[k]] : Vector2f(0, 0);
+                out_.tri_uv.push_back((float)uv.x); out_.tri_uv.push_back((float)uv.y);
+            }
             if (!t->mesh->use_geometry_normals) out_.any_smooth = true;
         }
         return FRT_CHILD_LEAF | ((uint32_t)(prims.size() - 1) << FRT_LEAF_COUNT_SHIFT) | first;
@@ -291,6 +303,70 @@ private:
         return next_id_++;
     }
 
+    // ---- textures (texture.h:17-112) ----------------------------------------------------------------
+    // Index of `t` in the texture table; checker children and image texels are appended on first use.
+    uint32_t texture_index(texture *t, int depth)
+    {
+        auto it = tex_index_.find(t);
+        if (it != tex_index_.end()) return it->second;
+        if (!t || depth > 6) throw std::runtime_error("frt_flattener: texture missing or nested deeper than 6 checker levels");
+        const uint32_t idx = (uint32_t)out_.textures.size();
+        out_.textures.emplace_back();
+        tex_index_[t] = idx;
+        frt_texture ft;
+        std::memset(&ft, 0, sizeof ft);
+        if (dynamic_cast<constant_texture *>(t))
+        {
+            const Vector3f c = constant_colour(t, "texture");
+            ft.kind = FRT_TEX_CONSTANT;
+            ft.p[0] = (float)c[0]; ft.p[1] = (float)c[1]; ft.p[2] = (float)c[2];
+        }
+        else if (checker_texture *c = dynamic_cast<checker_texture *>(t))
+        {
+            ft.kind = FRT_TEX_CHECKER;
+            ft.a = texture_index(c->tex0, depth + 1);
+            ft.b = texture_index(c->tex1, depth + 1);
+            ft.p[0] = (float)c->u_scale; ft.p[1] = (float)c->v_scale;
+        }
+        else if (image_texture *it2 = dynamic_cast<image_texture *>(t))
+        {
+            const image *img = it2->img.get();
+            if (!img || img->nx <= 0 || img->ny <= 0 || img->nn != 3)
+                throw std::runtime_error("frt_flattener: image_texture needs a loaded 3-channel image");
+            ft.kind = FRT_TEX_IMAGE;
+            ft.a = (uint32_t)(out_.tex_texels.size() / 3); ft.b = (uint32_t)img->nx; ft.c = (uint32_t)img->ny;
+            const size_t n = (size_t)img->nx * img->ny * 3;
+            if (img->type == formats::STBI_HDR)
+            {
+                if (!img->dataf) throw std::runtime_error("frt_flattener: HDR image_texture without data");
+                out_.tex_texels.insert(out_.tex_texels.end(), img->dataf, img->dataf + n);
+            }
+            else
+            {
+                if (!img->data) throw std::runtime_error("frt_flattener: image_texture without data");
+                for (size_t i = 0; i < n; ++i) out_.tex_texels.push_back((float)FromSrgb(img->data[i] / 255.0)); // texture.h:78-80
+            }
+        }
+        else
+            throw std::runtime_error("frt_flattener: unsupported texture class (constant_texture, checker_texture, image_texture)");
+        out_.textures[idx] = ft;
+        return idx;
+    }
+
+    // A material colour: a constant_texture is stored in the material itself (p[at..at+2]); anything else goes to the
+    // texture table and the material carries 1 + its index in p[slot] (include/frt.h FRT_MAT_TEX_A / _B).
+    void set_colour(frt_material &fm, int at, int slot, texture *t, const char *what)
+    {
+        if (dynamic_cast<constant_texture *>(t))
+        {
+            const Vector3f c = constant_colour(t, what);
+            fm.p[at] = (float)c[0]; fm.p[at + 1] = (float)c[1]; fm.p[at + 2] = (float)c[2];
+            return;
+        }
+        const uint32_t ref = 1u + texture_index(t, 0);
+        std::memcpy(&fm.p[slot], &ref, 4);
+    }
+
     // ---- materials / lights -------------------------------------------------------------------
     uint32_t material_index(material *m)
     {
@@ -299,24 +375,24 @@ private:
         frt_material fm;
         std::memset(&fm, 0, sizeof fm);
         auto set3 = [&](int at, const Vector3f &v) { fm.p[at] = (float)v[0]; fm.p[at + 1] = (float)v[1]; fm.p[at + 2] = (float)v[2]; };
-        if (lambertian *l = dynamic_cast<lambertian *>(m)) { fm.type = FRT_MAT_LAMBERTIAN; set3(0, constant_colour(l->albedo, "lambertian")); }
+        if (lambertian *l = dynamic_cast<lambertian *>(m)) { fm.type = FRT_MAT_LAMBERTIAN; set_colour(fm, 0, FRT_MAT_TEX_A, l->albedo, "lambertian"); }
         else if (modified_phong *p = dynamic_cast<modified_phong *>(m))
         {
             fm.type = FRT_MAT_PHONG;
-            set3(0, constant_colour(p->diffuse_reflectance, "modified_phong"));
-            set3(3, constant_colour(p->specular_reflectance, "modified_phong"));
+            set_colour(fm, 0, FRT_MAT_TEX_A, p->diffuse_reflectance, "modified_phong");
+            set_colour(fm, 3, FRT_MAT_TEX_B, p->specular_reflectance, "modified_phong");
             fm.p[6] = (float)p->specular_exponent;
         }
         else if (dielectric *d = dynamic_cast<dielectric *>(m))
         {
             fm.type = FRT_MAT_DIELECTRIC;
-            set3(0, constant_colour(d->specular_reflectance, "dielectric"));
+            set_colour(fm, 0, FRT_MAT_TEX_A, d->specular_reflectance, "dielectric");
             fm.p[6] = (float)d->ref_idx;
         }
         else if (rough_conductor *rc = dynamic_cast<rough_conductor *>(m))
         {
             fm.type = FRT_MAT_ROUGH_CONDUCTOR;
-            set3(0, constant_colour(rc->specular_reflectance, "rough_conductor"));
+            set_colour(fm, 0, FRT_MAT_TEX_A, rc->specular_reflectance, "rough_conductor");
             set3(3, rc->eta);
             fm.p[6] = (float)rc->alphaU;
             set3(7, rc->k);
@@ -365,5 +441,6 @@ private:
     double pad_ = 0;
     std::vector<bnode> bn_;
     std::unordered_map<material *, uint32_t> mat_index_;
+    std::unordered_map<texture *, uint32_t> tex_index_;
     frt_flat_scene out_;
 };

@@ -13,6 +13,7 @@
 #include <cctype>
 #include <cfloat>
 #include <cmath>
+#include <cstdint>
 #include <cstdio>
 #include <stdexcept>
 #include <memory>
@@ -101,6 +102,17 @@ public:
     Vector3f value(const hit_record &) const override { return color; }
     Vector3f color;
 };
+// texture.h:30-49: the flattener reads tex0 / tex1 / u_scale / v_scale; the lookup itself runs on the device
+class checker_texture : public texture
+{
+public:
+    checker_texture() {}
+    checker_texture(texture *t0, texture *t1, const double u_scale_, const double v_scale_)
+        : tex0(t0), tex1(t1), u_scale(u_scale_), v_scale(v_scale_) {}
+    Vector3f value(const hit_record &) const override { throw std::runtime_error("checker_texture is evaluated on the device"); }
+    texture *tex0 = nullptr, *tex1 = nullptr;
+    double u_scale = 1, v_scale = 1;
+};
 
 // ---- image.h / image.cpp / texture.h:51-112 -------------------------------------------------------
 // The reference loads HDR environment images through stb_image (image.cpp:11-22, stbi_loadf).  Here: a reader
@@ -113,9 +125,9 @@ public:
     image() {}
     image(const std::string &filename_, const formats &format = formats::STBI_HDR) : filename(filename_), type(format)
     {
-        if (format != formats::STBI_HDR) throw std::runtime_error("image: only Radiance .hdr files are read (" + filename + ")");
-        load_rgbe();
-        dataf = pixels.data();
+        if (format == formats::STBI_HDR) { load_rgbe(); dataf = pixels.data(); }
+        else if (format == formats::STBI_BMP) { load_bmp(); data = bytes.data(); }
+        else throw std::runtime_error("image: only Radiance .hdr and 24-bit .bmp files are read (" + filename + ")");
     }
     image(const float *rgb, int nx_, int ny_) : filename("memory"), type(formats::STBI_HDR), nx(nx_), ny(ny_), nn(3)
     {
@@ -130,6 +142,38 @@ public:
 
 private:
     std::vector<float> pixels;
+    std::vector<unsigned char> bytes;
+    // image.cpp:19-21: stbi_load with stbi_set_flip_vertically_on_load(true) -> row 0 of `data` is the BOTTOM row of
+    // the picture, RGB order.  An uncompressed 24-bit BMP with positive height stores exactly that order (as BGR).
+    void load_bmp()
+    {
+        FILE *f = std::fopen(filename.c_str(), "rb");
+        if (!f) throw std::runtime_error("image: cannot open " + filename);
+        unsigned char h[54];
+        if (std::fread(h, 1, 54, f) != 54 || h[0] != 'B' || h[1] != 'M') { std::fclose(f); throw std::runtime_error("image: not a BMP file: " + filename); }
+        auto u32 = [&](int at) { return (uint32_t)h[at] | ((uint32_t)h[at + 1] << 8) | ((uint32_t)h[at + 2] << 16) | ((uint32_t)h[at + 3] << 24); };
+        const uint32_t offset = u32(10);
+        const int w = (int)u32(18), hh = (int)u32(22);
+        const int bpp = h[28] | (h[29] << 8);
+        if (u32(14) < 40 || bpp != 24 || u32(30) != 0 || w <= 0 || hh == 0)
+        { std::fclose(f); throw std::runtime_error("image: only uncompressed 24-bit BMP is read: " + filename); }
+        nx = w; ny = hh < 0 ? -hh : hh; nn = 3;
+        const size_t stride = ((size_t)nx * 3 + 3) & ~(size_t)3;
+        std::vector<unsigned char> row(stride);
+        bytes.resize((size_t)nx * ny * 3);
+        std::fseek(f, (long)offset, SEEK_SET);
+        for (int j = 0; j < ny; ++j)
+        {
+            if (std::fread(row.data(), 1, stride, f) != stride) { std::fclose(f); throw std::runtime_error("image: truncated " + filename); }
+            const int dst = hh > 0 ? j : ny - 1 - j; // top-down files (negative height) are turned bottom-up
+            for (int i = 0; i < nx; ++i)
+            {
+                unsigned char *o = &bytes[((size_t)dst * nx + i) * 3];
+                o[0] = row[3 * i + 2]; o[1] = row[3 * i + 1]; o[2] = row[3 * i];
+            }
+        }
+        std::fclose(f);
+    }
     void load_rgbe()
     {
         FILE *f = std::fopen(filename.c_str(), "rb");
@@ -216,8 +260,9 @@ class image_texture : public texture
 public:
     image_texture() {}
     explicit image_texture(std::unique_ptr<image> img_) : img(std::move(img_)) {}
-    Vector3f value(const hit_record &rec) const override // texture.h:60-86 (HDR branch)
+    Vector3f value(const hit_record &rec) const override // texture.h:60-86 (HDR branch; LDR images are looked up on the device)
     {
+        if (img->type != formats::STBI_HDR) throw std::runtime_error("image_texture: LDR lookups run on the device");
         const int nx = img->nx, ny = img->ny;
         int i = (int)(rec.u * nx), j = (int)(rec.v * ny);
         if (i < 0 || i > nx) i = ((i % nx) + nx) % nx;

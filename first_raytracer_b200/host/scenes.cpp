@@ -61,7 +61,8 @@ void add_mesh(const std::shared_ptr<triangle_mesh> &mesh, std::vector<hitable *>
 Scene *cornell_box_obj(const double &aspect, const char *variant, frt_scene_ids *ids)
 {
     std::vector<hitable *> list, lights;
-    const std::string file = std::string("CornellBox/CornellBox-") + (variant ? variant : "Original") + ".obj";
+    const bool own_file = variant && (std::string(variant) == "Glossy" || std::string(variant) == "Sphere");
+    const std::string file = std::string("CornellBox/CornellBox-") + (own_file ? variant : "Original") + ".obj";
     // Use geometry normals (main.cpp:229)
     auto meshes = mesh_loader::load_obj(asset(file), true);
     // CornellBox-Glossy.mtl as shipped has no `light` entry, so that scene renders black; give the
@@ -69,12 +70,19 @@ Scene *cornell_box_obj(const double &aspect, const char *variant, frt_scene_ids 
     for (auto &m : meshes)
         if (m->name == "light" && !dynamic_cast<diffuse_light *>(m->mat.get()))
             m->mat.reset(new diffuse_light(new constant_texture(Vector3f(17, 12, 4))));
+    // "Metal": CornellBox-Original with the tall box as a `metal` mirror (material.h:111-130; as shipped only
+    // random_scene uses that class); "Lens": CornellBox-Original through a thin lens (camera.h:10-35)
+    const std::string var = variant ? variant : "Original";
+    if (var == "Metal")
+        for (auto &m : meshes)
+            if (m->name == "tallBox") m->mat.reset(new metal(Vector3f(0.8, 0.7, 0.6)));
     for (auto &m : meshes) add_mesh(m, list, lights);
-    camera cam(Vector3f(0, 1, 3.9f), Vector3f(0, 1, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.0, 10.0);
+    camera cam = var == "Lens" ? camera(Vector3f(0, 1, 3.9f), Vector3f(0, 1, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.2, 4.0)
+                               : camera(Vector3f(0, 1, 3.9f), Vector3f(0, 1, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.0, 10.0);
     return finish(list, cam, Vector3f(0.0, 0.0, 0.0), lights, ids);
 }
 
-Scene *veach_mis(const double &aspect, frt_scene_ids *ids)
+Scene *veach_mis(const double &aspect, frt_scene_ids *ids, const char *distribution)
 {
     std::vector<hitable *> list, lights;
     // veach_mi/veach_mi.obj numbers each object's faces from 1 again; OBJ indices are global, so as
@@ -92,7 +100,7 @@ Scene *veach_mis(const double &aspect, frt_scene_ids *ids)
                 m->mat.reset(new lambertian(new constant_texture(FromSrgb(Vector3f(0.4, 0.4, 0.4)))));
             else
                 m->mat.reset(new rough_conductor(alpha[p], 1.0, Vector3f(1.65746, 0.880369, 0.521229),
-                                                 Vector3f(9.22387, 6.26952, 4.837), new constant_texture(Vector3f(1, 1, 1)), "ggx"));
+                                                 Vector3f(9.22387, 6.26952, 4.837), new constant_texture(Vector3f(1, 1, 1)), distribution));
             m->name = p < 0 ? "floor" : "plate" + std::to_string(p + 1);
             meshes.push_back(m);
         }
@@ -122,6 +130,52 @@ Scene *teapot_scene(const double &aspect, frt_scene_ids *ids)
     for (auto &m : meshes) add_mesh(m, list, lights);
     camera cam(Vector3f(0, 125, 175.0), Vector3f(0, 50, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.0, 300.0);
     return finish(list, cam, Vector3f(0.05, 0.06, 0.08), lights, ids);
+}
+
+// A reduced random_scene (main.cpp:55-113): the 1000-radius ground sphere under a checker_texture, the sphere light,
+// small spheres of the three materials random_scene draws (lambertian / metal / dielectric) on a fixed grid, plus
+// checker_texture (texture.h:30-49) and image_texture (texture.h:51-112) on spheres (get_sphere_uv hitable.h:15-21)
+// and on triangles (uv interpolation triangle.h:104-113).  The oracle driver builds the same scene from the
+// reference's own classes (oracle/ref_driver/ref_main.cpp "textured").
+Scene *textured_scene(const double &aspect, frt_scene_ids *ids)
+{
+    std::vector<hitable *> list, lights;
+    texture *checker = new checker_texture(new constant_texture(Vector3f(0.2f, 0.3f, 0.1f)),
+                                           new constant_texture(Vector3f(0.99f, 0.99f, 0.99f)), 1, 1);
+    auto tiles = [&]() { return new image_texture(std::make_unique<image>(asset("data/tiles.bmp"), formats::STBI_BMP)); };
+    list.push_back(new sphere(Vector3f(0, -1000, 0), 1000, new lambertian(checker)));
+    list.push_back(new sphere(Vector3f(0, 1.5, 0), 1.5, new diffuse_light(new constant_texture(Vector3f(10, 10, 10)))));
+    lights.push_back(new sphere(Vector3f(0, 1.5, 0), 1.5, new diffuse_light(new constant_texture(Vector3f(10, 10, 10)))));
+    int k = 0;
+    for (int a = -2; a <= 2; ++a)
+        for (int c = -2; c <= 2; ++c, ++k)
+        {
+            if (a == 0 && c == 0) continue;
+            // float32-representable centres: the C ABI carries spheres as float32 (frt_sphere)
+                const Vector3f center((float)(1.6 * a + 0.3 * ((k * 7) % 5) / 5.0), 0.4f, (float)(1.6 * c + 0.3 * ((k * 3) % 5) / 5.0));
+            material *m;
+            switch (k % 6)
+            {
+            case 0: m = new lambertian(new constant_texture(Vector3f(0.1 + 0.15 * (k % 5), 0.6 - 0.1 * (k % 4), 0.3))); break;
+            case 1: m = new metal(Vector3f(0.5 * (1 + 0.2 * (k % 5)), 0.5 * (1 + 0.25 * (k % 3)), 0.5 * (1 + 0.1 * (k % 7)))); break;
+            case 2: m = new dielectric(1.5, new constant_texture(Vector3f(1.0, 1.0, 1.0)), new constant_texture(Vector3f(1.0, 1.0, 1.0))); break;
+            case 3: m = new lambertian(new checker_texture(new constant_texture(Vector3f(0.8, 0.1, 0.1)),
+                                                           new constant_texture(Vector3f(0.1, 0.1, 0.8)), 4, 16)); break;
+            case 4: m = new lambertian(tiles()); break;
+            default: m = new modified_phong(new checker_texture(tiles(), new constant_texture(Vector3f(0.05, 0.05, 0.05)), 2, 8),
+                                            new constant_texture(Vector3f(0.3, 0.3, 0.3)), 40.0); break;
+            }
+            list.push_back(new sphere(center, 0.4f, m));
+        }
+    std::vector<std::shared_ptr<triangle_mesh>> meshes;
+    meshes.push_back(quad(Vector3f(5, 0, -4), Vector3f(5, 0, 4), Vector3f(5, 4, 4), Vector3f(5, 4, -4),
+                          std::make_unique<lambertian>(tiles()), "picture"));
+    meshes.push_back(quad(Vector3f(-4, 0, -5), Vector3f(5, 0, -5), Vector3f(5, 4, -5), Vector3f(-4, 4, -5),
+                          std::make_unique<lambertian>(new checker_texture(new constant_texture(Vector3f(0.9, 0.8, 0.2)), tiles(), 3, 2)),
+                          "checkerwall"));
+    for (auto &m : meshes) add_mesh(m, list, lights);
+    camera cam(Vector3f(-9, 3, 5), Vector3f(0.5, 0.6, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.1f, 10.0);
+    return finish(list, cam, Vector3f(0.15, 0.18, 0.24), lights, ids);
 }
 
 // splitmix64 stream, centre ~ U[0,1)^3, two edges ~ U[-l,l]^3
@@ -196,7 +250,11 @@ Scene *make_scene(const std::string &name, double aspect, frt_scene_ids *ids)
     if (name == "cornell" || name == "cornell_box_obj") return cornell_box_obj(aspect, "Original", ids);
     if (name == "cornell_glossy") return cornell_box_obj(aspect, "Glossy", ids);
     if (name == "cornell_sphere") return cornell_box_obj(aspect, "Sphere", ids);
-    if (name == "veach" || name == "veach_mis") return veach_mis(aspect, ids);
+    if (name == "cornell_metal") return cornell_box_obj(aspect, "Metal", ids);
+    if (name == "cornell_lens") return cornell_box_obj(aspect, "Lens", ids);
+    if (name == "veach" || name == "veach_mis") return veach_mis(aspect, ids, "ggx");
+    if (name == "veach_beckmann") return veach_mis(aspect, ids, "beckmann");
+    if (name == "textured") return textured_scene(aspect, ids);
     if (name == "teapot") return teapot_scene(aspect, ids);
     if (name.rfind("soup:", 0) == 0)
     {

@@ -10,7 +10,8 @@
 struct frt_scene_ids { std::unordered_map<const hitable *, int> id; };
 
 Scene *cornell_box_obj(const double &aspect, const char *variant = "Original", frt_scene_ids *ids = nullptr);
-Scene *veach_mis(const double &aspect, frt_scene_ids *ids = nullptr);
+Scene *veach_mis(const double &aspect, frt_scene_ids *ids = nullptr, const char *distribution = "ggx");
+Scene *textured_scene(const double &aspect, frt_scene_ids *ids = nullptr);
 Scene *teapot_scene(const double &aspect, frt_scene_ids *ids = nullptr);
 Scene *soup_scene(const double &aspect, const float *tri9, size_t n, frt_scene_ids *ids = nullptr);
 void soup_triangles(size_t n, uint64_t seed, float edge, std::vector<float> &out);

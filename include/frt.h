@@ -89,6 +89,25 @@ typedef struct frt_material {
     float p[15];
 } frt_material;
 
+/* texture.h:17-112 — a material colour that is not a constant_texture.  The material keeps the constant colour in
+ * p[0..2] / p[3..5]; a slot that is textured instead carries 1 + the texture's index (as uint32 bits) in
+ * p[FRT_MAT_TEX_A] (colour p[0..2]: lambertian albedo, phong Kd, dielectric Ks, conductor reflectance) or
+ * p[FRT_MAT_TEX_B] (colour p[3..5]: phong Ks); 0 = constant.  Evaluated at the hit's texture coordinates
+ * hit_record::u,v: interpolated mesh uv for triangles (triangle.h:104-113), get_sphere_uv of the UN-normalised
+ * p - center for spheres (hitable.h:15-21, sphere.h:51 — as written in the reference). */
+typedef enum frt_texture_kind {
+    FRT_TEX_CONSTANT = 0, /* p[0..2] colour                                           texture.h:17-28  */
+    FRT_TEX_CHECKER = 1,  /* a, b = texture indices tex0, tex1; p[0], p[1] = u, v scale  texture.h:30-49  */
+    FRT_TEX_IMAGE = 2     /* a = first texel in tex_texels, b = nx, c = ny; nearest texel, wrap, no filtering
+                             (texture.h:60-86); texels are linear RGB floats (LDR files: FromSrgb(byte / 255)) */
+} frt_texture_kind;
+typedef struct frt_texture {
+    uint32_t kind, a, b, c;
+    float p[4];
+} frt_texture;
+#define FRT_MAT_TEX_A 11
+#define FRT_MAT_TEX_B 12
+
 /* Scene::lights (Scene.h:13): self-contained copies, because the reference's light list may
  * hold objects that are not the ones in `world` (veach_mis, main.cpp:292-302). */
 typedef enum frt_light_kind { FRT_LIGHT_TRIANGLE = 0, FRT_LIGHT_SPHERE = 1 } frt_light_kind;
@@ -126,6 +145,13 @@ typedef struct frt_scene_desc {
      * constant env_color above. */
     const float *env_image;
     uint32_t env_nx, env_ny;
+    /* surface textures: all may be 0 / NULL for a scene of constant colours */
+    uint32_t n_textures;
+    uint32_t reserved0;
+    const frt_texture *textures;
+    const float *tex_texels; /* 3 floats per texel, every image back to back; row 0 = image::data row 0 */
+    uint64_t n_texels;
+    const float *tri_uv;     /* 6 floats per triangle (mesh->uv of V[0], V[1], V[2]), leaf order; NULL = all zero */
 } frt_scene_desc;
 
 /* One unit of rendering work: the pixel rectangle and sample range path::Render's row loop

@@ -19,6 +19,7 @@ typedef float real;
 #define rcos(x) cosf(x)
 #define rtan(x) tanf(x)
 #define racos(x) acosf(x)
+#define rasin(x) asinf(x)
 #define ratan2(a, b) atan2f(a, b)
 #define rcopysign(a, b) copysignf(a, b)
 #else
@@ -33,6 +34,7 @@ typedef double real;
 #define rcos(x) cos(x)
 #define rtan(x) tan(x)
 #define racos(x) acos(x)
+#define rasin(x) asin(x)
 #define ratan2(a, b) atan2(a, b)
 #define rcopysign(a, b) copysign(a, b)
 #endif
@@ -93,6 +95,7 @@ typedef struct {
     uint32_t prim; /* triangle index (leaf order) or sphere index | FRT_CHILD_SPHERE */
     v3 p, wi, n;
     uint32_t mat;
+    real u, v; /* hit_record::u, v — texture coordinates */
 } hitrec;
 
 typedef struct {
@@ -241,6 +244,13 @@ static void fill_hit(const frt_scene_desc *sc, v3 o, v3 d, hitrec *h)
         const v3 oc = sub(o, c);
         if (dot(oc, oc) < r * r) h->n = neg(h->n);
         h->mat = s->material;
+        /* get_sphere_uv hitable.h:15-21, called with the UN-normalised p - center (sphere.h:51) */
+        {
+            const v3 q = sub(h->p, c);
+            const real phi = ratan2(q.z, q.x), theta = rasin(q.y);
+            h->u = 1 - (phi + PI) / (2 * PI);
+            h->v = (theta + PI / 2) / PI;
+        }
         return;
     }
     const size_t i = h->prim;
@@ -253,6 +263,59 @@ static void fill_hit(const frt_scene_desc *sc, v3 o, v3 d, hitrec *h)
         const v3 n0 = q3(sc->tri_normals[3 * i]), n1 = q3(sc->tri_normals[3 * i + 1]), n2 = q3(sc->tri_normals[3 * i + 2]);
         h->n = unit(add(add(scl(n0, 1 - h->b1 - h->b2), scl(n1, h->b1)), scl(n2, h->b2)));
     }
+    /* triangle.h:104-106: uvhit = (1 - u - v) uv[V0] + u uv[V1] + v uv[V2] */
+    h->u = h->v = 0;
+    if (sc->tri_uv)
+    {
+        const float *q = sc->tri_uv + 6 * i;
+        const real w0 = 1 - h->b1 - h->b2;
+        h->u = w0 * (real)q[0] + h->b1 * (real)q[2] + h->b2 * (real)q[4];
+        h->v = w0 * (real)q[1] + h->b1 * (real)q[3] + h->b2 * (real)q[5];
+    }
+}
+
+/* (int)x as the reference's x86-64 build converts a double (cvttsd2si): NaN and out-of-range give INT_MIN */
+static int f2i(real x) { return (x >= (real)-2147483648.0 && x < (real)2147483648.0) ? (int)x : (int)0x80000000; }
+
+/* texture::value(hrec): constant_texture texture.h:17-28, checker_texture texture.h:30-49, image_texture texture.h:60-86 */
+static v3 tex_eval(const frt_scene_desc *sc, uint32_t ref, real u, real v)
+{
+    uint32_t idx = ref - 1u;
+    for (int level = 0; level < 8; ++level)
+    {
+        const frt_texture *t = &sc->textures[idx];
+        if (t->kind == FRT_TEX_CHECKER)
+        {
+            const int x = 2 * modulo_(f2i(u * (real)t->p[0] * 2), 2) - 1, y = 2 * modulo_(f2i(v * (real)t->p[1] * 2), 2) - 1;
+            idx = (x * y == 1) ? t->b : t->a;
+            continue;
+        }
+        if (t->kind == FRT_TEX_IMAGE)
+        {
+            const int nx = (int)t->b, ny = (int)t->c;
+            int i = f2i(u * nx), j = f2i(v * ny);
+            if (i < 0 || i > nx) i = modulo_(i, nx);
+            if (j < 0 || j > ny) j = modulo_(j, ny);
+            if (i == nx) i = nx - 1;
+            if (j == ny) j = ny - 1;
+            return f3(sc->tex_texels + 3 * ((size_t)t->a + (size_t)j * nx + i));
+        }
+        return f3(t->p);
+    }
+    return V(0, 0, 0);
+}
+
+/* the material of a hit with its textured colours (albedo->value(hrec) etc., material.h:64,98,158,297) put where the
+ * constant colours are */
+static frt_material material_at(const frt_scene_desc *sc, const hitrec *h)
+{
+    frt_material m = sc->materials[h->mat];
+    uint32_t ta, tb;
+    memcpy(&ta, &m.p[FRT_MAT_TEX_A], 4);
+    memcpy(&tb, &m.p[FRT_MAT_TEX_B], 4);
+    if (sc->n_textures && ta) { const v3 c = tex_eval(sc, ta, h->u, h->v); m.p[0] = (float)c.x; m.p[1] = (float)c.y; m.p[2] = (float)c.z; }
+    if (sc->n_textures && tb) { const v3 c = tex_eval(sc, tb, h->u, h->v); m.p[3] = (float)c.x; m.p[4] = (float)c.y; m.p[5] = (float)c.z; }
+    return m;
 }
 
 int frt_oracle_trace(const frt_scene_desc *scene, const frt_ray *rays, size_t n, int any_hit, int use_bvh,
@@ -746,7 +809,8 @@ static v3 Li(octx *cx, v3 o, v3 d, int depth, const hitrec *prev, uint32_t prev_
     if (!world_hit(cx, o, d, REAL_FLT_MAX, 0, &h)) /* path.cpp:10 */
         return env_eval(sc, d);                    /* path.cpp:115, environment_map::eval material.h:219-232 */
     fill_hit(sc, o, d, &h);
-    const frt_material *m = &sc->materials[h.mat];
+    const frt_material mm = material_at(sc, &h);
+    const frt_material *m = &mm;
     /* diffuse_light::emitted material.h:184-190 */
     v3 Le = V(0, 0, 0);
     if (m->type == FRT_MAT_DIFFUSE_LIGHT && dot(h.n, d) < 0) Le = mp3(m, 0);
@@ -842,7 +906,8 @@ static v3 Li_ao(octx *cx, v3 o, v3 d, sampler *rs)
     if (world_hit(cx, o, d, REAL_FLT_MAX, 0, &h)) /* ao.cpp:9 */
     {
         fill_hit(sc, o, d, &h);
-        const frt_material *m = &sc->materials[h.mat];
+        const frt_material mm = material_at(sc, &h);
+        const frt_material *m = &mm;
         real s0, s1, s2;
         scatrec sr;
         get3d(rs, &s0, &s1, &s2);
@@ -884,7 +949,8 @@ static v3 Li_direct(octx *cx, v3 o, v3 d, sampler *rs)
     cx->st.closest_rays++;
     if (!world_hit(cx, o, d, REAL_FLT_MAX, 0, &h)) return env_eval(sc, d);
     fill_hit(sc, o, d, &h);
-    const frt_material *m = &sc->materials[h.mat];
+    const frt_material mm = material_at(sc, &h);
+    const frt_material *m = &mm;
     v3 Le = V(0, 0, 0);
     if (m->type == FRT_MAT_DIFFUSE_LIGHT) return Le; /* scatter() false: assignment_1.cpp:15 */
     real s0, s1, s2;

@@ -274,28 +274,42 @@ static built_scene &build_scene(const std::string &full_name, double aspect)
     const bool hdr = full_name.size() > 4 && full_name.compare(full_name.size() - 4, 4, "+hdr") == 0;
     const std::string name = (sky || hdr) ? full_name.substr(0, full_name.size() - 4) : full_name;
     built_scene &b = *new built_scene;
+    // The HDR environment is loaded FIRST: image.cpp:19-21 switches stb_image's process-global vertical flip on when
+    // any LDR image is loaded, and a later stbi_loadf would then flip the environment too (as shipped, main.cpp:170
+    // loads the environment of a scene without LDR textures, i.e. unflipped).
+    environment_map *hdr_env = hdr ? new environment_map(g_assets + "/data/test.hdr") : nullptr;
     std::vector<hitable *> lights;
     std::vector<hitable *> list;
     camera cam;
     Vector3f env(0, 0, 0);
 
-    if (name == "cornell" || name == "cornell_glossy" || name == "cornell_sphere")
+    if (name == "cornell" || name == "cornell_glossy" || name == "cornell_sphere" || name == "cornell_metal" || name == "cornell_lens")
     {
         // main.cpp:222-252 (cornell_box_obj)
-        const char *file = name == "cornell" ? "/CornellBox/CornellBox-Original.obj"
-                         : name == "cornell_glossy" ? "/CornellBox/CornellBox-Glossy.obj"
-                                                    : "/CornellBox/CornellBox-Sphere.obj";
+        // cornell_metal: the tall box becomes a `metal` mirror (material.h:111-130, only random_scene uses it as shipped)
+        // cornell_lens : thin-lens camera, aperture 0.2 focused on the boxes (camera.h:10-35, util.h:21-41)
+        const char *file = name == "cornell_glossy" ? "/CornellBox/CornellBox-Glossy.obj"
+                         : name == "cornell_sphere" ? "/CornellBox/CornellBox-Sphere.obj"
+                                                    : "/CornellBox/CornellBox-Original.obj";
         b.meshes = read_obj(g_assets + file, true);
         // CornellBox-Glossy.mtl has no `light` entry (the shipped scene is black): same emitter as Original
         for (auto &m : b.meshes)
             if (m->name == "light" && !dynamic_cast<diffuse_light *>(m->mat.get()))
                 m->mat.reset(new diffuse_light(new constant_texture(Vector3f(17, 12, 4))));
+        if (name == "cornell_metal")
+            for (auto &m : b.meshes)
+                if (m->name == "tallBox") m->mat.reset(new metal(Vector3f(0.8, 0.7, 0.6)));
         push_triangles(b.meshes, b.keep, lights);
         for (auto &t : b.keep) list.push_back(t.get());
-        cam = camera(Vector3f(0, 1, 3.9f), Vector3f(0, 1, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.0, 10.0);
+        if (name == "cornell_lens")
+            cam = camera(Vector3f(0, 1, 3.9f), Vector3f(0, 1, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.2, 4.0);
+        else
+            cam = camera(Vector3f(0, 1, 3.9f), Vector3f(0, 1, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.0, 10.0);
     }
-    else if (name == "veach")
+    else if (name == "veach" || name == "veach_beckmann")
     {
+        // veach_beckmann: the same plates with the Beckmann distribution (pdf.h:280-403, microfacet.h:47-128)
+        const char *distribution = name == "veach" ? "ggx" : "beckmann";
         // main.cpp:281-314 (veach_mis) + SURVEY §8c(iii)
         // veach_mi.obj restarts its face indices per object, which (OBJ indices being global) puts
         // every plate on top of the floor triangles; the per-object files hold the intended geometry.
@@ -310,7 +324,7 @@ static built_scene &build_scene(const std::string &full_name, double aspect)
                 else
                     m->mat.reset(new rough_conductor(alpha[p], 1.0, Vector3f(1.65746, 0.880369, 0.521229),
                                                      Vector3f(9.22387, 6.26952, 4.837),
-                                                     new constant_texture(Vector3f(1, 1, 1)), "ggx"));
+                                                     new constant_texture(Vector3f(1, 1, 1)), distribution));
                 b.meshes.push_back(m);
             }
         }
@@ -342,6 +356,51 @@ static built_scene &build_scene(const std::string &full_name, double aspect)
         for (auto &t : b.keep) list.push_back(t.get());
         cam = camera(Vector3f(0, 125, 175.0), Vector3f(0, 50, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.0, 300.0);
         env = Vector3f(0.05, 0.06, 0.08);
+    }
+    else if (name == "textured")
+    {
+        // A reduced random_scene (main.cpp:55-113): the 1000-radius ground sphere under a checker_texture, the sphere
+        // light, small spheres of every material random_scene draws (lambertian / metal / dielectric) on a fixed
+        // grid, plus what exercises the texture classes on every primitive type: checker_texture (texture.h:30-49)
+        // and image_texture (texture.h:51-112, LDR file through the reference's own stb loader) on spheres
+        // (get_sphere_uv hitable.h:15-21) and on triangles (uv interpolation triangle.h:104-113).
+        texture *checker = new checker_texture(new constant_texture(Vector3f(0.2f, 0.3f, 0.1f)),
+                                               new constant_texture(Vector3f(0.99f, 0.99f, 0.99f)), 1, 1);
+        auto tiles = [&]() { return new image_texture(std::make_unique<image>(g_assets + "/data/tiles.bmp", formats::STBI_BMP)); };
+        list.push_back(new sphere(Vector3f(0, -1000, 0), 1000, new lambertian(checker)));
+        list.push_back(new sphere(Vector3f(0, 1.5, 0), 1.5, new diffuse_light(new constant_texture(Vector3f(10, 10, 10)))));
+        lights.push_back(new sphere(Vector3f(0, 1.5, 0), 1.5, new diffuse_light(new constant_texture(Vector3f(10, 10, 10)))));
+        int k = 0;
+        for (int a = -2; a <= 2; ++a)
+            for (int c = -2; c <= 2; ++c, ++k)
+            {
+                if (a == 0 && c == 0) continue;
+                // float32-representable centres: the C ABI carries spheres as float32 (frt_sphere)
+                const Vector3f center((float)(1.6 * a + 0.3 * ((k * 7) % 5) / 5.0), 0.4f, (float)(1.6 * c + 0.3 * ((k * 3) % 5) / 5.0));
+                material *m;
+                switch (k % 6)
+                {
+                case 0: m = new lambertian(new constant_texture(Vector3f(0.1 + 0.15 * (k % 5), 0.6 - 0.1 * (k % 4), 0.3))); break;
+                case 1: m = new metal(Vector3f(0.5 * (1 + 0.2 * (k % 5)), 0.5 * (1 + 0.25 * (k % 3)), 0.5 * (1 + 0.1 * (k % 7)))); break;
+                case 2: m = new dielectric(1.5, new constant_texture(Vector3f(1.0, 1.0, 1.0)), new constant_texture(Vector3f(1.0, 1.0, 1.0))); break;
+                case 3: m = new lambertian(new checker_texture(new constant_texture(Vector3f(0.8, 0.1, 0.1)),
+                                                               new constant_texture(Vector3f(0.1, 0.1, 0.8)), 4, 16)); break;
+                case 4: m = new lambertian(tiles()); break;
+                default: m = new modified_phong(new checker_texture(tiles(), new constant_texture(Vector3f(0.05, 0.05, 0.05)), 2, 8),
+                                                new constant_texture(Vector3f(0.3, 0.3, 0.3)), 40.0); break;
+                }
+                list.push_back(new sphere(center, 0.4f, m));
+            }
+        // textured triangles: a picture wall (image_texture) and a checker wall standing behind the spheres
+        b.meshes.push_back(quad_mesh(Vector3f(5, 0, -4), Vector3f(5, 0, 4), Vector3f(5, 4, 4), Vector3f(5, 4, -4),
+                                     std::make_unique<lambertian>(tiles()), "picture"));
+        b.meshes.push_back(quad_mesh(Vector3f(-4, 0, -5), Vector3f(5, 0, -5), Vector3f(5, 4, -5), Vector3f(-4, 4, -5),
+                                     std::make_unique<lambertian>(new checker_texture(new constant_texture(Vector3f(0.9, 0.8, 0.2)),
+                                                                                     tiles(), 3, 2)), "checkerwall"));
+        push_triangles(b.meshes, b.keep, lights);
+        for (auto &t : b.keep) list.push_back(t.get());
+        cam = camera(Vector3f(-9, 3, 5), Vector3f(0.5, 0.6, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.1f, 10.0);
+        env = Vector3f(0.15, 0.18, 0.24);
     }
     else if (name.rfind("soupfile:", 0) == 0)
     {
@@ -380,8 +439,7 @@ static built_scene &build_scene(const std::string &full_name, double aspect)
     hitable **arr = new hitable *[list.size()];
     for (size_t i = 0; i < list.size(); ++i) arr[i] = list[i];
     b.scene.reset(new Scene(parallel_bvh_node::create_bvh(arr, (int)list.size(), 0.0, 0.0),
-                            hdr ? new environment_map(g_assets + "/data/test.hdr")
-                                : new environment_map(std::make_unique<constant_texture>(env)), cam, lights));
+                            hdr ? hdr_env : new environment_map(std::make_unique<constant_texture>(env)), cam, lights));
     return b;
 }
 

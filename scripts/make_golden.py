@@ -104,10 +104,32 @@ OTHER_INTEGRATOR_CASES = [("teapot", 48, 27, 2, "ao"), ("cornell_glossy+sky", 32
                           ("teapot+hdr", 160, 90, 4, "path")]
 
 
+# Round 2: the branches no shipped scene reaches — Beckmann rough_conductor (pdf.h:280-403), `metal`
+# (material.h:111-130), the thin-lens camera (camera.h:10-35, util.h:21-41) — and surface textures (texture.h:30-112)
+# on the reduced random_scene of ref_main.cpp "textured" (ao is left out there: constant_pdf::generate throws, pdf.h:197).
+ROUND2_TRACE = [("textured", 1.5)]
+ROUND2_RENDER = [("veach_beckmann", 48, 32, 4, "path"), ("veach_beckmann", 192, 128, 16, "path"),
+                 ("cornell_metal", 32, 32, 2, "path"), ("cornell_metal", 96, 96, 8, "path"),
+                 ("cornell_lens", 32, 32, 2, "path"), ("cornell_lens", 96, 96, 8, "path"),
+                 ("textured", 48, 32, 2, "path"), ("textured", 192, 128, 8, "path"), ("textured+hdr", 48, 32, 2, "path"),
+                 ("textured", 96, 64, 2, "direct"), ("textured", 96, 64, 1, "normals"),
+                 ("veach_beckmann+sky", 48, 32, 2, "ao")]
+
+
 def main():
+    import argparse
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--round2-only", action="store_true", help="only the fixtures added in round 2")
+    args = ap.parse_args()
     if not refutil.have_ref():
         raise SystemExit("oracle/_ref is missing: run `make -C oracle` where /root/reference exists")
     OUT.mkdir(parents=True, exist_ok=True)
+    for name, aspect in ROUND2_TRACE:
+        trace_fixture(name, aspect)
+    for name, nx, ny, spp, integ in ROUND2_RENDER:
+        render_fixture(name, nx, ny, spp, integ)
+    if args.round2_only:
+        return
     for name, aspect in [("cornell", 1.0), ("veach", 1.5), ("teapot", 16 / 9), ("cornell_sphere", 1.0)]:
         trace_fixture(name, aspect)
     for name, nx, ny, spp in [("cornell", 48, 48, 4), ("veach", 48, 32, 4), ("cornell_sphere", 32, 32, 2),

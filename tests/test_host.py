@@ -225,3 +225,62 @@ def test_constant_environment_has_no_image(built):
     scene = api.HostScene("cornell+sky", 1.0, 2)
     assert not scene.desc.env_image and scene.desc.env_nx == 0
     assert np.allclose(list(scene.desc.env_color), [0.5, 0.6, 0.8])
+
+
+def test_textured_scene_description(built):
+    """Surface textures (texture.h:30-112) reach the C ABI as a table: checker children and image extents stay inside
+    their arrays, the LDR texels are FromSrgb(byte / 255) of assets/data/tiles.bmp in the reference's row order
+    (stb_image with vertical flip, image.cpp:19-21 = the BMP file's own bottom-up order), triangles carry mesh uv."""
+    scene = api.HostScene("textured", 1.5, 2)
+    a = scene.arrays()
+    tex, texels = a["textures"], a["tex_texels"]
+    assert scene.desc.struct_size == C.sizeof(api.frt_scene_desc)
+    kinds = set(tex["kind"].tolist())
+    assert kinds == {0, 1, 2}
+    for t in tex:
+        if t["kind"] == 1:
+            assert t["a"] < len(tex) and t["b"] < len(tex)
+        if t["kind"] == 2:
+            assert (t["b"], t["c"]) == (64, 32) and t["a"] + 64 * 32 <= len(texels)
+    raw = (REPO / "assets" / "data" / "tiles.bmp").read_bytes()
+    bgr = np.frombuffer(raw[54:], np.uint8).reshape(32, 64, 3).astype(np.float64) / 255.0
+    rgb = bgr[:, :, ::-1]
+    lin = np.where(rgb <= 0.04045, rgb / 12.92, ((rgb + 0.055) / 1.055) ** 2.4)
+    first = int(tex[tex["kind"] == 2][0]["a"])
+    assert np.allclose(texels[first:first + 64 * 32].reshape(32, 64, 3), lin, rtol=1e-6, atol=1e-7)
+    # textured materials carry 1 + texture index in p[11] / p[12]; constants keep 0 there
+    refs = a["materials"]["p"][:, 11:13].copy().view(np.uint32)
+    assert refs.max() <= len(tex) and (refs > 0).sum() >= 5
+    uv = a["tri_uv"]
+    assert uv.shape == (scene.desc.n_tris, 3, 2) and uv.min() == 0.0 and uv.max() == 1.0
+    # a scene of constant colours uploads no texture arrays at all
+    plain = api.HostScene("cornell", 1.0, 2)
+    assert plain.desc.n_textures == 0 and not plain.desc.tri_uv and not plain.desc.tex_texels
+
+
+def test_round2_scene_variants_equal_reference_driver(built):
+    """cornell_metal / cornell_lens / veach_beckmann / textured: the host layer's scenes hold what the reference driver
+    (oracle/ref_driver/ref_main.cpp, the reference's own classes) builds under the same names."""
+    if not refutil.have_ref():
+        pytest.skip("oracle/_ref not built")
+    for name, aspect in [("cornell_metal", 1.0), ("cornell_lens", 1.0), ("veach_beckmann", 1.5), ("textured", 1.5)]:
+        scene = api.HostScene(name, aspect, 2)
+        ref, info = refutil.ref_dump(name, aspect)
+        a = scene.arrays()
+        d = scene.desc
+        cam = np.concatenate([np.asarray(getattr(d.camera, f)[:], np.float64) for f in
+                              ("origin", "lower_left_corner", "horizontal", "vertical", "u", "v", "w")] + [[d.camera.lens_radius]])
+        assert np.allclose(cam, ref["camera"], rtol=1e-6, atol=1e-6), name
+        assert d.n_tris + d.n_spheres == len(ref["kind"]) and d.n_lights == ref["n_lights"]
+        # material classes per primitive (creation order): the reference's dynamic type vs the flattened tag
+        ids = a["tris"][:, 0, 3].view(np.uint32)
+        mats = a["tris"][:, 1, 3].view(np.uint32)
+        for i, m in zip(ids, mats):
+            assert int(ref["mat_kind"][i]) == int(a["materials"]["type"][m]), (name, i)
+        for s in a["spheres"]:
+            assert int(ref["mat_kind"][s["prim_id"]]) == int(a["materials"]["type"][s["material"]]), name
+        if name == "veach_beckmann":
+            rc = a["materials"][a["materials"]["type"] == 3]
+            assert len(rc) == 4 and (rc["p"][:, 10] == 1.0).all()
+        if name == "cornell_lens":
+            assert abs(d.camera.lens_radius - 0.1) < 1e-7

@@ -14,7 +14,11 @@ from first_raytracer_b200 import api
 
 GOLDEN = refutil.GOLDEN
 RENDER_CASES = [("cornell", 48, 48, 4), ("veach", 48, 32, 4), ("cornell_sphere", 32, 32, 2),
-                ("cornell_glossy", 32, 32, 2), ("teapot", 48, 27, 2)]
+                ("cornell_glossy", 32, 32, 2), ("teapot", 48, 27, 2),
+                # round 2: Beckmann rough_conductor (pdf.h:280-403), metal (material.h:111-130), thin lens (camera.h:30-35,
+                # util.h:21-41), checker_texture / image_texture on spheres and triangles (texture.h:30-112)
+                ("veach_beckmann", 48, 32, 4), ("cornell_metal", 32, 32, 2), ("cornell_lens", 32, 32, 2),
+                ("textured", 48, 32, 2), ("textured+hdr", 48, 32, 2)]
 
 
 @pytest.mark.parametrize("name,nx,ny,spp", RENDER_CASES)
@@ -41,7 +45,9 @@ OTHER_INTEGRATOR_CASES = [("teapot", 48, 27, 2, "ao"), ("cornell_glossy+sky", 32
                           ("teapot", 48, 27, 2, "direct"), ("teapot+sky", 48, 27, 1, "direct"),
                           # environment_map over the HDR image of main.cpp:170 (material.h:209-232, texture.h:60-86)
                           ("teapot+hdr", 48, 27, 2, "path"), ("veach+hdr", 48, 32, 2, "path"),
-                          ("teapot+hdr", 160, 90, 4, "path")]
+                          ("teapot+hdr", 160, 90, 4, "path"),
+                          ("textured", 96, 64, 2, "direct"), ("textured", 96, 64, 1, "normals"),
+                          ("veach_beckmann+sky", 48, 32, 2, "ao")]
 
 
 @pytest.mark.parametrize("name,nx,ny,spp,integrator", OTHER_INTEGRATOR_CASES)
@@ -58,7 +64,8 @@ def test_oracle_other_integrators_match_golden(built, name, nx, ny, spp, integra
     assert np.abs(img - ref).max() <= 1e-5 * max(1.0, np.abs(ref).max())
 
 
-@pytest.mark.parametrize("name,aspect", [("cornell", 1.0), ("veach", 1.5), ("teapot", 16 / 9), ("cornell_sphere", 1.0)])
+@pytest.mark.parametrize("name,aspect", [("cornell", 1.0), ("veach", 1.5), ("teapot", 16 / 9), ("cornell_sphere", 1.0),
+                                         ("textured", 1.5)])
 def test_oracle_trace_matches_golden(built, name, aspect):
     g = np.load(GOLDEN / f"trace_{name}.npz")
     scene = api.HostScene(name, aspect, 4)
