@@ -16,20 +16,22 @@ PKG_DIR = Path(__file__).resolve().parent
 REPO_DIR = PKG_DIR.parent
 
 FRT_OK = 0
+FRTH_CANCELLED = 1
 FRT_FLAG_COUNTERS = 1
-FRT_FLAG_KERNEL_TIMERS = 2
-FRT_FLAG_STREAMED_POOL = 4
+FRT_TRACE_ANY_HIT = 1
+FRT_TRACE_SORT = 2
 
 # every exported symbol of include/frt.h and include/frt_host.h (tests check the libraries export them)
 FRT_SYMBOLS = [
     "frt_create", "frt_destroy", "frt_last_error", "frt_set_flags", "frt_device_count",
     "frt_upload_scene", "frt_render_tile", "frt_clear_film", "frt_readback", "frt_film_device_ptr",
     "frt_trace_rays", "frt_trace_rays_device", "frt_stream_handle", "frt_get_counters", "frt_restore_film",
+    "frt_readback_film", "frt_cancel", "frt_poll", "frt_host_alloc", "frt_host_free", "frt_build_wide8",
 ]
 FRTH_SYMBOLS = [
     "frth_last_error", "frth_scene_create", "frth_scene_create_soup", "frth_scene_destroy",
     "frth_scene_desc", "frth_scene_info", "frth_soup_triangles", "frth_camera_rays", "frth_render",
-    "frth_bvh4_build",
+    "frth_bvh4_build", "frth_cancel", "frth_last_ldr",
 ]
 
 
@@ -135,6 +137,12 @@ def load_libs():
             "frt_stream_handle": (i32, [vp, i32, C.POINTER(vp)]),
             "frt_trace_rays": (i32, [vp, vp, sz, vp, i32, C.POINTER(dbl)]),
             "frt_trace_rays_device": (i32, [vp, i32, vp, sz, vp, i32, C.POINTER(dbl)]),
+            "frt_readback_film": (i32, [vp, u64, vp, vp, vp, C.POINTER(frt_stats)]),
+            "frt_cancel": (i32, [vp]),
+            "frt_poll": (i32, [vp, C.POINTER(i32)]),
+            "frt_host_alloc": (vp, [sz]),
+            "frt_host_free": (None, [vp]),
+            "frt_build_wide8": (i32, [vp, vp, sz, C.POINTER(u32), C.POINTER(i32)]),
         },
         frth: {
             "frth_last_error": (C.c_char_p, []),
@@ -147,6 +155,8 @@ def load_libs():
             "frth_camera_rays": (i32, [vp, i32, i32, vp]),
             "frth_render": (i32, [vp, i32, i32, i32, u32, u32, u32, vp, C.POINTER(frt_stats), C.POINTER(dbl)]),
             "frth_bvh4_build": (i32, [vp, sz, i32, dbl, C.POINTER(vp)]),
+            "frth_cancel": (i32, []),
+            "frth_last_ldr": (i32, [vp, sz]),
         },
     }
     for lib, table in sig.items():
@@ -241,9 +251,18 @@ class HostScene:
         st = frt_stats()
         secs = C.c_double()
         rc = self._frth.frth_render(self.handle, n_gpus, nx, ny, spp, seed, flags, _ptr(img), C.byref(st), C.byref(secs))
-        if rc != FRT_OK:
+        if rc not in (FRT_OK, FRTH_CANCELLED):
             raise FrtError(f"frth_render: {self._frth.frth_last_error().decode()}")
-        return img, st.as_dict(), secs.value
+        d = st.as_dict()
+        d["cancelled"] = rc == FRTH_CANCELLED
+        return img, d, secs.value
+
+    def last_ldr(self, nx: int, ny: int) -> np.ndarray:
+        """viewer::out_image of the last render: the 8-bit tone-mapped film [ny, nx, 3], row 0 = bottom."""
+        out = np.zeros((ny, nx, 3), np.uint8)
+        if self._frth.frth_last_ldr(_ptr(out), out.size) != FRT_OK:
+            raise FrtError("frth_last_ldr: no film of that size")
+        return out
 
 
 def soup_triangles(n: int, seed: int = 0x5EED0001, edge: float = 0.004) -> np.ndarray:
@@ -336,21 +355,72 @@ class Context:
         self._check(self._frt.frt_stream_handle(self.handle, dev, C.byref(p)), "frt_stream_handle")
         return p.value
 
-    def trace(self, rays: np.ndarray, any_hit: bool = False):
+    def trace(self, rays: np.ndarray, any_hit: bool = False, sort: bool = False, hits: np.ndarray | None = None):
         """Host buffers in, host buffers out (H2D / D2H inside the call) → (hits, device_ms)."""
         rays = np.ascontiguousarray(rays)
         assert rays.dtype == RAY_DTYPE
-        hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
+        if hits is None:
+            hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
         ms = C.c_double()
-        self._check(self._frt.frt_trace_rays(self.handle, _ptr(rays), rays.shape[0], _ptr(hits), int(any_hit),
-                                             C.byref(ms)), "frt_trace_rays")
+        mode = (FRT_TRACE_ANY_HIT if any_hit else 0) | (FRT_TRACE_SORT if sort else 0)
+        self._check(self._frt.frt_trace_rays(self.handle, _ptr(rays), rays.shape[0], _ptr(hits), mode, C.byref(ms)), "frt_trace_rays")
         return hits, ms.value
 
-    def trace_device(self, d_rays_ptr: int, n: int, d_hits_ptr: int, any_hit: bool = False, dev: int = 0) -> float:
+    def trace_device(self, d_rays_ptr: int, n: int, d_hits_ptr: int, any_hit: bool = False, dev: int = 0, sort: bool = False) -> float:
         ms = C.c_double()
-        self._check(self._frt.frt_trace_rays_device(self.handle, dev, d_rays_ptr, n, d_hits_ptr, int(any_hit),
-                                                    C.byref(ms)), "frt_trace_rays_device")
+        mode = (FRT_TRACE_ANY_HIT if any_hit else 0) | (FRT_TRACE_SORT if sort else 0)
+        self._check(self._frt.frt_trace_rays_device(self.handle, dev, d_rays_ptr, n, d_hits_ptr, mode, C.byref(ms)), "frt_trace_rays_device")
         return ms.value
+
+    def readback_film(self, ns: int):
+        """frt_readback_film → (mean [ny,nx,3] float64 = viewer::fout_image, 8-bit tone-mapped image = viewer::out_image, stats)."""
+        st = frt_stats()
+        fout = np.zeros((self.ny, self.nx, 3), dtype=np.float64)
+        ldr = np.zeros((self.ny, self.nx, 3), dtype=np.uint8)
+        self._check(self._frt.frt_readback_film(self.handle, ns, _ptr(fout), _ptr(ldr), None, C.byref(st)), "frt_readback_film")
+        return fout, ldr, st.as_dict()
+
+    def cancel(self):
+        self._check(self._frt.frt_cancel(self.handle), "frt_cancel")
+
+    def poll(self) -> bool:
+        done = C.c_int()
+        self._check(self._frt.frt_poll(self.handle, C.byref(done)), "frt_poll")
+        return bool(done.value)
+
+
+class Pinned:
+    """A numpy array over frt_host_alloc'ed (pinned) host memory: `.array`; `.close()` frees it (drop every view first)."""
+
+    def __init__(self, n: int, dtype):
+        frt, _ = load_libs()
+        self._frt = frt
+        dt = np.dtype(dtype)
+        self.nbytes = max(1, n * dt.itemsize)
+        self.ptr = frt.frt_host_alloc(self.nbytes)
+        if not self.ptr:
+            raise FrtError("frt_host_alloc failed")
+        self.array = np.frombuffer((C.c_char * self.nbytes).from_address(self.ptr), dtype=dt, count=n)
+
+    def close(self):
+        if self.ptr:
+            self.array = None
+            self._frt.frt_host_free(self.ptr)
+            self.ptr = None
+
+
+def build_wide8(scene: "HostScene"):
+    """frt_build_wide8 → (words [n8, 24] uint32, depth)."""
+    frt, _ = load_libs()
+    n8, depth = C.c_uint32(), C.c_int()
+    rc = frt.frt_build_wide8(C.addressof(scene.desc), None, 0, C.byref(n8), C.byref(depth))
+    if rc != FRT_OK:
+        raise FrtError("frt_build_wide8 failed")
+    words = np.zeros((n8.value, 24), np.uint32)
+    rc = frt.frt_build_wide8(C.addressof(scene.desc), _ptr(words), words.size, C.byref(n8), C.byref(depth))
+    if rc != FRT_OK:
+        raise FrtError("frt_build_wide8 failed")
+    return words, depth.value
 
 
 def save_checkpoint(path, sums: np.ndarray, spp_done: int, seed: int, scene: str = "", integrator: str = "path"):

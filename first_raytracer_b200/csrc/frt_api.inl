@@ -9,6 +9,7 @@ int frt_device_count(const frt_ctx *ctx) { return ctx ? (int)ctx->dev.size() : 0
 int frt_set_flags(frt_ctx *ctx, uint32_t flags)
 {
     if (!ctx) return FRT_ERR_INVALID;
+    if (flags & ~FRT_FLAG_COUNTERS) return fail(ctx, FRT_ERR_INVALID, "frt_set_flags: unknown flag bits 0x%x", flags & ~FRT_FLAG_COUNTERS);
     ctx->flags = flags;
     return FRT_OK;
 }
@@ -28,14 +29,18 @@ int frt_create(frt_ctx **out, const int *devices, int n)
         const int o = devices ? devices[i] : i;
         if (o < 0 || o >= have) return fail(nullptr, FRT_ERR_INVALID, "frt_create: device %d not present (%d visible)", o, have);
     }
-    frt_ctx *c = new frt_ctx;
+    // owned until the end: every error path below gives the streams, events and buffers back
+    std::unique_ptr<frt_ctx, void (*)(frt_ctx *)> guard(new frt_ctx, frt_destroy);
+    frt_ctx *c = guard.get();
     c->dev.resize(n);
-    if (const char *s = getenv("FRT_POOL_SLOTS")) c->n_slots = (unsigned int)std::max(1024ll, atoll(s));
-    if (const char *s = getenv("FRT_POLL_EVERY")) c->poll_every = std::max(1, atoi(s));
     if (const char *s = getenv("FRT_WF_SLOTS")) c->wf_slots = (unsigned int)std::min(1568, std::max(32, atoi(s) / 32 * 32));
     if (const char *s = getenv("FRT_WF_CONFIG")) c->wf_config = std::min(n_wf_configs - 1, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_WF_SORT")) c->wf_sort = atoi(s) & 3;
     if (const char *s = getenv("FRT_WF_REFILL")) c->wf_refill = std::min(31, std::max(0, atoi(s)));
+    if (const char *s = getenv("FRT_WIDE8")) c->wide8 = atoi(s) ? 1 : 0;
+    if (const char *s = getenv("FRT_WIDE8_MIN_TRIS")) c->wide8_min_tris = (uint32_t)std::max(0ll, atoll(s));
+    CU(cudaHostAlloc((void **)&c->h_cancel, sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable));
+    *c->h_cancel = 0;
     for (int i = 0; i < n; ++i)
     {
         Device &d = c->dev[i];
@@ -44,56 +49,53 @@ int frt_create(frt_ctx **out, const int *devices, int n)
         cudaDeviceProp prop;
         CU(cudaGetDeviceProperties(&prop, d.ordinal));
         if (prop.major < 10)
-        {
-            delete c;
             return fail(nullptr, FRT_ERR_CUDA, "frt_create: device %d is sm_%d%d; this library is built for sm_100a only",
                         d.ordinal, prop.major, prop.minor);
-        }
         d.sms = prop.multiProcessorCount;
         CU(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
-        CU(cudaEventCreate(&d.ev_begin));
-        CU(cudaEventCreate(&d.ev_end));
+        for (cudaEvent_t *ev : {&d.ev_begin, &d.ev_end, &d.ev_sum, &d.ev_t0, &d.ev_t1}) CU(cudaEventCreate(ev));
         CU(cudaMalloc((void **)&d.d_ctr, sizeof(Counters)));
         CU(cudaMemset(d.d_ctr, 0, sizeof(Counters)));
         CU(cudaMallocHost((void **)&d.h_ctr, sizeof(Counters)));
         memset(d.h_ctr, 0, sizeof(Counters));
         int per_sm = 0;
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend<false>, 128, 0));
-        d.blocks_extend = std::max(1, per_sm) * d.sms;
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_connect<false>, 128, 0));
-        d.blocks_connect = std::max(1, per_sm) * d.sms;
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<false, false>, 128, 0));
         d.blocks_trace = std::max(1, per_sm) * d.sms;
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<true, false>, 128, 0));
         d.blocks_trace_any = std::max(1, per_sm) * d.sms;
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace8<false, false>, 128, 0));
+        d.blocks_trace8 = std::max(1, per_sm) * d.sms;
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace8<true, false>, 128, 0));
+        d.blocks_trace8_any = std::max(1, per_sm) * d.sms;
         const size_t wf_smem = (size_t)c->wf_slots * FRT_WF_SLOT_BYTES;
         const WfConfig &wc = wf_configs[c->wf_config];
         CU(cudaFuncSetAttribute(wc.plain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
         CU(cudaFuncSetAttribute(wc.counting, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wc.plain, wc.threads, wf_smem));
         if (per_sm < 1)
-        {
-            delete c;
             return fail(nullptr, FRT_ERR_CUDA, "frt_create: k_wavefront does not fit an SM with %u slots per CTA", c->wf_slots);
-        }
         d.blocks_wavefront = per_sm * d.sms;
         CU(cudaFuncSetAttribute(wf_other.plain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
         CU(cudaFuncSetAttribute(wf_other.counting, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_other.plain, wf_other.threads, wf_smem));
         d.blocks_wavefront_other = per_sm * d.sms; // 0: only the path integrator fits this FRT_WF_SLOTS
     }
-    // peer access for the in-process film reduction
-    for (int i = 1; i < n; ++i)
-    {
-        int can = 0;
-        cudaDeviceCanAccessPeer(&can, c->dev[0].ordinal, c->dev[i].ordinal);
-        if (!can) { c->peer_ok = false; continue; }
-        cudaSetDevice(c->dev[0].ordinal);
-        cudaError_t pe = cudaDeviceEnablePeerAccess(c->dev[i].ordinal, 0);
-        if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) c->peer_ok = false;
-        cudaGetLastError();
-    }
-    *out = c;
+    // peer access between every pair of the context's devices: the film reduce-scatter of frt_readback reads
+    // every device's film from every device (the same ordinal listed twice needs none)
+    for (int i = 0; i < n; ++i)
+        for (int j = 0; j < n; ++j)
+        {
+            if (c->dev[i].ordinal == c->dev[j].ordinal) continue;
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, c->dev[i].ordinal, c->dev[j].ordinal);
+            if (!can) { c->peer_ok = false; continue; }
+            cudaSetDevice(c->dev[i].ordinal);
+            cudaError_t pe = cudaDeviceEnablePeerAccess(c->dev[j].ordinal, 0);
+            if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) c->peer_ok = false;
+            cudaGetLastError();
+        }
+    if (getenv("FRT_NO_PEER")) c->peer_ok = false; // exercise the staged fallback
+    *out = guard.release();
     return FRT_OK;
 }
 
@@ -103,18 +105,53 @@ void frt_destroy(frt_ctx *ctx)
     for (Device &d : ctx->dev)
     {
         cudaSetDevice(d.ordinal);
-        cudaStreamSynchronize(d.stream);
-        for (void *p : d.pool_allocs) cudaFree(p);
-        void *ptrs[] = {d.d_nodes, d.d_tris, d.d_normals, d.d_spheres, d.d_mats, d.d_lights, d.d_env, d.d_ctr, d.d_film, d.d_film_peer,
-                        d.d_textures, d.d_texels, d.d_tri_uv};
+        if (d.stream) cudaStreamSynchronize(d.stream);
+        void *ptrs[] = {d.d_nodes, d.d_tris, d.d_normals, d.d_spheres, d.d_mats, d.d_lights, d.d_env, d.d_ctr, d.d_film, d.d_film_stage,
+                        d.d_textures, d.d_texels, d.d_tri_uv, d.d_nodes8, d.d_rays, d.d_hits, d.d_sort};
         for (void *p : ptrs) if (p) cudaFree(p);
         if (d.h_ctr) cudaFreeHost(d.h_ctr);
-        for (cudaEvent_t e : d.timers.ev) cudaEventDestroy(e);
-        if (d.ev_begin) cudaEventDestroy(d.ev_begin);
-        if (d.ev_end) cudaEventDestroy(d.ev_end);
+        for (cudaEvent_t ev : {d.ev_begin, d.ev_end, d.ev_sum, d.ev_t0, d.ev_t1}) if (ev) cudaEventDestroy(ev);
         if (d.stream) cudaStreamDestroy(d.stream);
     }
+    if (!ctx->dev.empty()) cudaSetDevice(ctx->dev[0].ordinal);
+    if (ctx->d_ldr) cudaFree(ctx->d_ldr);
+    if (ctx->h_film) cudaFreeHost(ctx->h_film);
+    if (ctx->h_ldr) cudaFreeHost(ctx->h_ldr);
+    if (ctx->h_cancel) cudaFreeHost(ctx->h_cancel);
     delete ctx;
+}
+
+// Pinned host memory for callers that want their ray / hit / film buffers to move at link speed and asynchronously
+// (frt_trace_rays recognises such pointers and skips its staging).
+void *frt_host_alloc(size_t bytes)
+{
+    void *p = nullptr;
+    if (bytes == 0 || cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void frt_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+// The 8-wide compressed nodes frt_upload_scene derives for large scenes, as a host utility (no device needed): lets
+// the CPU tests check the conversion.  Writes up to `cap_words` uint32 words (24 per node) and the node count.
+int frt_build_wide8(const frt_scene_desc *s, uint32_t *words, size_t cap_words, uint32_t *n_nodes8, int *depth)
+{
+    if (!s || !n_nodes8 || (s->n_nodes && !s->nodes)) return FRT_ERR_INVALID;
+    std::vector<uint32_t> w;
+    float m = 0.f;
+    for (uint32_t i = 0; i < s->n_nodes; ++i)
+        for (int k = 0; k < 4; ++k)
+            if (s->nodes[i].child[k] != FRT_CHILD_EMPTY)
+                for (const float v : {s->nodes[i].lo_x[k], s->nodes[i].hi_x[k], s->nodes[i].lo_y[k], s->nodes[i].hi_y[k], s->nodes[i].lo_z[k], s->nodes[i].hi_z[k]})
+                    if (std::isfinite(v)) m = std::fmax(m, std::fabs(v));
+    for (int a = 0; a < 3; ++a) m = std::fmax(m, std::fabs(s->camera.origin[a]));
+    frt_wide8::build(s->nodes, s->n_nodes, 8e-7f * m, w, depth);
+    *n_nodes8 = (uint32_t)(w.size() / 24);
+    if (words)
+    {
+        if (cap_words < w.size()) return FRT_ERR_INVALID;
+        memcpy(words, w.data(), w.size() * sizeof(uint32_t));
+    }
+    return FRT_OK;
 }
 
 static int validate_scene(frt_ctx *ctx, const frt_scene_desc *s)
@@ -221,6 +258,49 @@ int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *s)
         if ((rc = upload_array(ctx, &d.d_texels, s->tex_texels, 3 * (size_t)s->n_texels)) != FRT_OK) return rc;
         if ((rc = upload_array(ctx, &d.d_tri_uv, s->tri_uv, (s->tri_uv && s->n_textures) ? 6 * (size_t)s->n_tris : 0)) != FRT_OK) return rc;
     }
+    // scene box (children of the root): the Morton keys of frt_trace_rays' sort are taken inside it
+    for (int a = 0; a < 3; ++a) { ctx->bounds_lo[a] = 0.f; ctx->bounds_hi[a] = 0.f; }
+    if (s->n_nodes)
+    {
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        const frt_bvh4_node &r = s->nodes[0];
+        for (int k = 0; k < 4; ++k)
+        {
+            if (r.child[k] == FRT_CHILD_EMPTY) continue;
+            lo[0] = std::fmin(lo[0], r.lo_x[k]); lo[1] = std::fmin(lo[1], r.lo_y[k]); lo[2] = std::fmin(lo[2], r.lo_z[k]);
+            hi[0] = std::fmax(hi[0], r.hi_x[k]); hi[1] = std::fmax(hi[1], r.hi_y[k]); hi[2] = std::fmax(hi[2], r.hi_z[k]);
+        }
+        for (int a = 0; a < 3; ++a) if (std::isfinite(lo[a]) && std::isfinite(hi[a])) { ctx->bounds_lo[a] = lo[a]; ctx->bounds_hi[a] = hi[a]; }
+    }
+    // large scenes: ray casting walks 8-wide compressed nodes derived from the 4-wide ones (frt_wide8.cuh)
+    ctx->have_wide8 = false;
+    ctx->n_nodes8 = 0;
+    const bool want8 = ctx->wide8 >= 0 ? ctx->wide8 != 0 : s->n_tris >= ctx->wide8_min_tris;
+    if (want8 && s->n_nodes)
+    {
+        std::vector<uint32_t> words;
+        uint32_t n8 = 0;
+        int depth8 = 0;
+        float m = 0.f;
+        for (int a = 0; a < 3; ++a) m = std::fmax(m, std::fmax(std::fabs(ctx->bounds_lo[a]), std::fabs(ctx->bounds_hi[a])));
+        for (int a = 0; a < 3; ++a) m = std::fmax(m, std::fabs(s->camera.origin[a]));
+        frt_wide8::build(s->nodes, s->n_nodes, 8e-7f * m, words, &depth8);
+        n8 = (uint32_t)(words.size() / 24);
+        if (7 * depth8 + 1 <= FRT_STACK8_SIZE)
+        {
+            for (Device &d : ctx->dev)
+            {
+                CU(cudaSetDevice(d.ordinal));
+                if ((rc = upload_array(ctx, &d.d_nodes8, words.data(), words.size())) != FRT_OK) return rc;
+            }
+            ctx->have_wide8 = true;
+            ctx->n_nodes8 = n8;
+        }
+    }
+    if (!ctx->have_wide8)
+        for (Device &d : ctx->dev)
+            if (d.d_nodes8) { cudaSetDevice(d.ordinal); cudaFree(d.d_nodes8); d.d_nodes8 = nullptr; }
+    v.prefetch = getenv("FRT_PREFETCH") ? (uint32_t)atoi(getenv("FRT_PREFETCH")) : 1u;
     uint32_t bsdf_types = 0;
     for (uint32_t i = 0; i < s->n_materials; ++i)
         if (s->materials[i].type != FRT_MAT_DIFFUSE_LIGHT) bsdf_types |= 1u << s->materials[i].type;

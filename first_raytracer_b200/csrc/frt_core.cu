@@ -1,5 +1,5 @@
-// libfrt.so — context, scene upload, wavefront driver loop, film readback and the ray-cast
-// entry points behind include/frt.h.  sm_100a only; no CPU path exists in this library.
+// libfrt.so — context, scene upload, tile launch, film readback and the ray-cast entry points
+// behind include/frt.h.  sm_100a only; no CPU path exists in this library.
 #include <cuda_runtime.h>
 #include <algorithm>
 #include <cstdarg>
@@ -7,46 +7,41 @@
 #include <cstdlib>
 #include <cmath>
 #include <cstring>
+#include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 #include "frt_shade.cuh"
 #include "frt_wavefront.cuh"
+#include "frt_wide8.cuh"
+#include "frt_sort.cuh"
 
 namespace {
 
 thread_local std::string g_create_error;
 
-struct KernelTimer
-{
-    std::vector<cudaEvent_t> ev; // pairs
-    std::vector<int> kind;
-    double ms[4] = {0, 0, 0, 0};
-};
-
 struct Device
 {
     int ordinal = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_sum = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
     // scene
     void *d_nodes = nullptr, *d_tris = nullptr, *d_normals = nullptr, *d_spheres = nullptr, *d_mats = nullptr,
-         *d_lights = nullptr, *d_env = nullptr, *d_textures = nullptr, *d_texels = nullptr, *d_tri_uv = nullptr;
-    // pool
-    PathPool pool{};
-    std::vector<void *> pool_allocs;
+         *d_lights = nullptr, *d_env = nullptr, *d_textures = nullptr, *d_texels = nullptr, *d_tri_uv = nullptr,
+         *d_nodes8 = nullptr;
     Counters *d_ctr = nullptr;
     Counters *h_ctr = nullptr; // pinned
     float *d_film = nullptr;
-    float *d_film_peer = nullptr; // staging when peer access is unavailable
+    float *d_film_stage = nullptr; // device 0 only: staging for a peer's film when peer access is unavailable
     size_t film_floats = 0;
+    // ray casting: device buffers kept between calls (grow-only), sort scratch
+    void *d_rays = nullptr, *d_hits = nullptr, *d_sort = nullptr;
+    size_t trace_cap = 0, sort_cap = 0;
     int sms = 0;
-    int blocks_extend = 0, blocks_connect = 0, blocks_trace = 0, blocks_trace_any = 0, blocks_wavefront = 0, blocks_wavefront_other = 0;
+    int blocks_trace = 0, blocks_trace_any = 0, blocks_trace8 = 0, blocks_trace8_any = 0, blocks_wavefront = 0, blocks_wavefront_other = 0;
     unsigned int wf_ctas_launched = 0;
     bool rendered = false;
-    // per-render bookkeeping
-    bool done = true;
-    unsigned long long iterations = 0, launches = 0, tile_iter = 0;
-    KernelTimer timers;
+    unsigned long long launches = 0;
 };
 
 } // namespace
@@ -60,15 +55,24 @@ struct frt_ctx
     bool peer_ok = true;
     DevScene host_view{}; // counts + camera; pointers filled per device
     uint32_t nx = 0, ny = 0;
-    unsigned int n_slots = 1u << 20; // streamed (global-memory) pool
-    unsigned int wf_slots = 1024;    // CTA-resident pool: slots per CTA (multiple of 32)
-    int wf_config = 4;               // index into wf_configs[]: 512 threads, one CTA per SM (measured best)
-    int wf_refill = 24;              // dynamic fetch threshold (lanes still traversing)
-    int wf_sort = -1;                // bit 0: bin queued rays by where they start; bit 1: shade grouped by material;
-                                     // -1 = bit 0 always, bit 1 when the scene has more than one BSDF type
+    unsigned int wf_slots = 1024; // slots per CTA (multiple of 32)
+    int wf_config = 4;            // index into wf_configs[]: 512 threads, one CTA per SM (measured best)
+    int wf_refill = 24;           // dynamic fetch threshold (lanes still traversing)
+    int wf_sort = -1;             // bit 0: bin queued rays by where they start; bit 1: shade grouped by material;
+                                  // -1 = bit 0 always, bit 1 when the scene has more than one BSDF type
+    int wide8 = -1;               // ray casting over the 8-wide compressed nodes: -1 = scenes of >= wide8_min_tris triangles
+    uint32_t wide8_min_tris = 1u << 16;
+    bool have_wide8 = false;
+    uint32_t n_nodes8 = 0;
     bool multi_bsdf = false;
     float ao_t_max = 0.f;
-    int poll_every = 16;
+    float bounds_lo[3] = {0, 0, 0}, bounds_hi[3] = {0, 0, 0}; // scene box (root node): Morton keys of frt_trace_rays' sort
+    int *h_cancel = nullptr; // mapped pinned flag, read by the render kernels (frt_cancel)
+    // host staging of the film (pinned, ctx-owned): float sums and the 8-bit tonemapped image
+    float *h_film = nullptr;
+    unsigned char *h_ldr = nullptr;
+    size_t h_film_floats = 0;
+    unsigned char *d_ldr = nullptr; // device 0
     frt_stats stats{};
 };
 
@@ -102,50 +106,18 @@ int upload_array(frt_ctx *ctx, void **dst, const T *src, size_t n)
     return FRT_OK;
 }
 
-int alloc_pool(frt_ctx *ctx, Device &d, unsigned int n)
+// Work split over host threads for the film copies (a 1080p film is 25 MB of sums in, 50 MB of doubles out).
+template <class F>
+void parallel_chunks(size_t n, size_t min_chunk, F fn)
 {
-    for (void *p : d.pool_allocs) cudaFree(p);
-    d.pool_allocs.clear();
-    auto grab = [&](size_t bytes, void **out) -> cudaError_t {
-        cudaError_t e = cudaMalloc(out, bytes);
-        if (e == cudaSuccess) d.pool_allocs.push_back(*out);
-        return e;
-    };
-    PathPool &p = d.pool;
-    p.n_slots = n;
-    CU(grab(sizeof(float4) * n, (void **)&p.ray_o));
-    CU(grab(sizeof(float4) * n, (void **)&p.ray_d));
-    CU(grab(sizeof(float4) * n, (void **)&p.hit));
-    CU(grab(sizeof(float4) * n, (void **)&p.thr));
-    CU(grab(sizeof(float4) * n, (void **)&p.rad));
-    CU(grab(sizeof(float4) * n, (void **)&p.prev_p));
-    CU(grab(sizeof(float4) * n, (void **)&p.sh_a));
-    CU(grab(sizeof(float4) * n, (void **)&p.sh_b));
-    CU(grab(sizeof(float) * n, (void **)&p.sh_c));
-    CU(grab(sizeof(unsigned int) * n, (void **)&p.free_q[0]));
-    CU(grab(sizeof(unsigned int) * n, (void **)&p.free_q[1]));
-    CU(grab(sizeof(unsigned int) * n, (void **)&p.shadow_q));
-    return FRT_OK;
-}
-
-__global__ void k_reset_pool(PathPool pool, Counters *ctr, unsigned long long total)
-{
-    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < pool.n_slots)
-    {
-        pool.free_q[0][i] = i;
-        pool.ray_d[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    if (i == 0)
-    {
-        ctr->next_sample = 0;
-        ctr->total_samples = total;
-        ctr->n_alive = 0;
-        ctr->n_free[0] = pool.n_slots;
-        ctr->n_free[1] = 0;
-        ctr->n_shadow = 0;
-        ctr->extend_next = ctr->connect_next = 0;
-    }
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const size_t want = std::max<size_t>(1, n / std::max<size_t>(1, min_chunk));
+    const unsigned nt = (unsigned)std::min<size_t>(std::min<unsigned>(hw, 16u), want);
+    if (nt <= 1) { fn((size_t)0, n); return; }
+    std::vector<std::thread> workers;
+    for (unsigned w = 1; w < nt; ++w) workers.emplace_back(fn, n * w / nt, n * (w + 1) / nt);
+    fn((size_t)0, n / nt);
+    for (std::thread &t : workers) t.join();
 }
 
 __global__ void k_reset_tile(Counters *ctr, unsigned long long total)
@@ -154,34 +126,60 @@ __global__ void k_reset_tile(Counters *ctr, unsigned long long total)
     ctr->total_samples = total;
 }
 
-// Sum the other devices' films into device 0's over NVLink peer loads (one pass, no staging).
+// In-process multi-GPU film sum as a reduce-scatter over peer memory (NVLink loads / stores): the device that runs
+// this sums float4 range [begin, end) of EVERY device's film and stores the result into device 0's film.  Range g is
+// read and written by device g only, so the sum is in place; device 0 then holds the whole film.
 struct PeerFilms { const float *p[16]; int n; };
-__global__ void k_sum_films(float *dst, PeerFilms peers, size_t n)
+__global__ void k_sum_slice(float *dst, PeerFilms films, size_t begin4, size_t end4, size_t tail_begin, size_t tail_end)
 {
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    const size_t stride = (size_t)gridDim.x * blockDim.x, t0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    for (size_t i = begin4 + t0; i < end4; i += stride)
     {
-        float s = dst[i];
-        for (int k = 0; k < peers.n; ++k) s += peers.p[k][i];
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int k = 0; k < films.n; ++k)
+        {
+            const float4 v = reinterpret_cast<const float4 *>(films.p[k])[i];
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+        reinterpret_cast<float4 *>(dst)[i] = s;
+    }
+    for (size_t i = tail_begin + t0; i < tail_end; i += stride) // the < 4 floats a film size leaves over
+    {
+        float s = 0.f;
+        for (int k = 0; k < films.n; ++k) s += films.p[k][i];
         dst[i] = s;
     }
 }
 
-// Ray source / hit sink of the ray-cast entry points: frt_ray array in, frt_hit array out (global memory).
+// viewer::add_sample's tone map for the whole film (viewer.cpp:111-126): c = sum * (1 / ns) in double
+// (geometry.h:533-538), 8-bit = (GLubyte) int(pow(1 - exp(-c), 1 / 2.2) * 255 + .5).
+__global__ void k_tonemap(const float *sum, unsigned char *ldr, size_t n, double inv_ns)
+{
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    {
+        const double c = (double)sum[i] * inv_ns;
+        const double v = pow(1.0 - exp(-c), 1.0 / 2.2) * 255.0 + 0.5;
+        // int(NaN) (a negative mean, e.g. the normals integrator) is INT_MIN on the reference's x86 build -> byte 0
+        ldr[i] = (v >= -2147483648.0 && v < 2147483648.0) ? (unsigned char)(int)v : (unsigned char)0;
+    }
+}
+
+// Ray source / hit sink of the ray-cast entry points: frt_ray array in, frt_hit array out (global memory).  With
+// `order` (frt_trace_rays' Morton sort) work item k is ray order[k]; hits go back to the ray's own index.
 struct TraceIo
 {
     const float2 *rays;
     frt_hit *hits;
+    const unsigned int *order;
     unsigned int i;
     __device__ __forceinline__ void load(const unsigned int item, float3 &o, float3 &d)
     {
-        i = item;
+        i = order ? __ldg(order + item) : item;
         const float2 r0 = __ldg(rays + 3 * (size_t)i), r1 = __ldg(rays + 3 * (size_t)i + 1), r2 = __ldg(rays + 3 * (size_t)i + 2);
         o = f3(r0.x, r0.y, r1.x); d = f3(r1.y, r2.x, r2.y);
     }
-    template <class W>
-    __device__ __forceinline__ void store(const DevScene &sc, W &w)
+    __device__ __forceinline__ void put(const DevScene &sc, const RayHit h)
     {
-        const RayHit h = w.finish(sc);
         int prim_id = -1;
         if (h.prim != 0xFFFFFFFFu)
         {
@@ -192,20 +190,46 @@ struct TraceIo
         }
         reinterpret_cast<float4 *>(hits)[i] = make_float4(h.t, h.u, h.v, __int_as_float(prim_id));
     }
+    template <class W>
+    __device__ __forceinline__ void store(const DevScene &sc, W &w) { put(sc, w.finish(sc)); }
 };
 
-// frt_trace_rays: persistent warps over a global cursor with dynamic fetch (frt_persistent_trace).
-// frt_trace_rays.  Closest hit: persistent warps over a global cursor with dynamic fetch
-// (frt_persistent_trace): on the 10M-triangle soup 308 -> 467 Mrays/s.  Occlusion queries end early and
-// carry little state; for them plain batches of 32 rays measured faster (357 vs 333 Mrays/s), kept.
-// Register budget: closest hit 4 CTAs / SM (no spills); occlusion queries 8 (64 registers; measured on the soup:
-// 351 -> 386 Mrays/s; for closest hit 5 / 6 / 8 CTAs measured within 3 % of 4).
+// Ray counts of a ray-cast launch: into the device counters frt_get_counters reads (closest_rays for closest-hit
+// casts, shadow_rays for occlusion casts), one set of atomics per warp.
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ void frt_trace_count(Counters *ctr, unsigned int n_rays, unsigned int n_nodes, unsigned int n_tris)
+{
+    unsigned long long r = n_rays, nn = n_nodes, nt = n_tris;
+    for (int off = 16; off > 0; off >>= 1)
+    {
+        r += __shfl_down_sync(0xFFFFFFFFu, r, off);
+        if (COUNT)
+        {
+            nn += __shfl_down_sync(0xFFFFFFFFu, nn, off);
+            nt += __shfl_down_sync(0xFFFFFFFFu, nt, off);
+        }
+    }
+    if (lane_id() == 0)
+    {
+        if (r) atomicAdd(ANY ? &ctr->shadow_rays : &ctr->closest_rays, r);
+        if (COUNT)
+        {
+            atomicAdd(&ctr->node_visits, nn);
+            atomicAdd(&ctr->tri_tests, nt);
+        }
+    }
+}
+
+// frt_trace_rays over the 4-wide nodes (scenes below ctx->wide8_min_tris).  Closest hit: persistent warps over a
+// global cursor with dynamic fetch (frt_persistent_trace).  Occlusion queries end early and carry little state; for
+// them plain batches of 32 rays measured faster, kept.  Register budget: closest hit 4 CTAs / SM (no spills);
+// occlusion queries 8 (64 registers).
 template <bool ANY, bool COUNT>
 __global__ void __launch_bounds__(128, ANY ? 8 : 4) k_trace(DevScene sc, Counters *ctr, const float2 *rays, frt_hit *hits,
-                                                                    unsigned int n, int refill_below)
+                                                                    const unsigned int *order, unsigned int n, int refill_below)
 {
     unsigned int n_rays = 0, n_nodes = 0, n_tris = 0;
-    TraceIo io{rays, hits, 0u};
+    TraceIo io{rays, hits, order, 0u};
     if (ANY)
     {
         while (true)
@@ -222,23 +246,23 @@ __global__ void __launch_bounds__(128, ANY ? 8 : 4) k_trace(DevScene sc, Counter
             w.begin(sc, o, d);
             while (w.active) w.round(sc, stk, n_nodes, n_tris);
             io.store(sc, w);
+            ++n_rays;
         }
     }
     else
         frt_persistent_trace<ANY, COUNT>(sc, io, n, &ctr->trace_next, refill_below, n_rays, n_nodes, n_tris);
-    if (COUNT)
-    {
-        for (int off = 16; off > 0; off >>= 1)
-        {
-            n_nodes += __shfl_down_sync(0xFFFFFFFFu, n_nodes, off);
-            n_tris += __shfl_down_sync(0xFFFFFFFFu, n_tris, off);
-        }
-        if (lane_id() == 0)
-        {
-            atomicAdd(&ctr->node_visits, (unsigned long long)n_nodes);
-            atomicAdd(&ctr->tri_tests, (unsigned long long)n_tris);
-        }
-    }
+    frt_trace_count<ANY, COUNT>(ctr, n_rays, n_nodes, n_tris);
+}
+
+// The same entry over the 8-wide compressed nodes (frt_wide8.cuh): scenes large enough to leave the caches.
+template <bool ANY, bool COUNT>
+__global__ void __launch_bounds__(128, ANY ? 6 : 4) k_trace8(DevScene sc, Counters *ctr, const float2 *rays, frt_hit *hits,
+                                                                     const unsigned int *order, unsigned int n, int refill_below)
+{
+    unsigned int n_rays = 0, n_nodes = 0, n_tris = 0;
+    TraceIo io{rays, hits, order, 0u};
+    frt_persistent_trace8<ANY, COUNT>(sc, io, n, &ctr->trace_next, refill_below, n_rays, n_nodes, n_tris);
+    frt_trace_count<ANY, COUNT>(ctr, n_rays, n_nodes, n_tris);
 }
 
 // Launch shapes of k_wavefront compiled into the library (threads per CTA, CTAs per SM the register
@@ -254,8 +278,9 @@ const WfConfig wf_configs[] = {WF_CFG(256, 2), WF_CFG(128, 4), WF_CFG(128, 5), W
                                WF_CFG(192, 3), WF_CFG(160, 4), WF_CFG(320, 2), WF_CFG(224, 3), WF_CFG(288, 2),
                                WF_CFG(384, 1), WF_CFG(448, 1), WF_CFG(192, 2)};
 const int n_wf_configs = (int)(sizeof wf_configs / sizeof wf_configs[0]);
-// The same kernel with the shade stage of the integrators next to `path` (ao, normals_renderer, ass_1_renderer): its
-// own instantiation, so that the path kernel carries none of their code (measured: -11 % when it did), in one shape.
+// The general kernel: the integrators next to `path` (ao, normals_renderer, ass_1_renderer) and `path` over textured
+// surfaces.  Its own instantiation, so that the path kernel of the untextured scenes carries none of that code
+// (measured: -11 % when it did), in one shape.
 const WfConfig wf_other = {512, 1, k_wavefront<false, 512, 1, true>, k_wavefront<true, 512, 1, true>};
 
 // `any_tend` = upper end of occlusion queries: path.cpp:50 passes 1 - SHADOW_EPSILON (a float literal, util.h:11)
@@ -276,6 +301,7 @@ DevScene device_view(const frt_ctx *ctx, const Device &d, double any_tend = 1.0 
     sc.textures = (const frt_texture *)d.d_textures;
     sc.tex_texels = (const float *)d.d_texels;
     sc.tri_uv = (const float *)d.d_tri_uv;
+    sc.nodes8 = (const uint4 *)d.d_nodes8;
     return sc;
 }
 

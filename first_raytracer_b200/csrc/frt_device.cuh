@@ -14,6 +14,8 @@
 struct DevScene
 {
     const float4 *nodes;       // 8 float4 per frt_bvh4_node
+    const uint4 *nodes8;       // 6 uint4 per 8-wide compressed node (frt_wide8.cuh) or nullptr
+    uint32_t prefetch;         // 8-wide walk: L2-prefetch postponed children when they are pushed
     const float4 *tris;        // 3 float4 per triangle
     const float4 *tri_normals; // 3 float4 per triangle or nullptr
     const float4 *spheres;     // 2 float4 per frt_sphere
@@ -35,17 +37,14 @@ struct DevScene
     float any_tend_lo, any_tend_hi;
 };
 
-struct Counters // one per device, device memory; mirrored to pinned host memory when polled
+struct Counters // one per device, device memory; mirrored to pinned host memory by readback
 {
     unsigned long long next_sample;   // next unissued sample index of the current tile
     unsigned long long total_samples; // samples in the current tile (this device's share)
     unsigned long long closest_rays, shadow_rays, node_visits, tri_tests, samples_started, nonfinite;
-    int n_alive;                      // paths in flight
-    unsigned int n_free[2];           // ping-pong free-slot queue lengths
-    unsigned int n_shadow;            // shadow queue length of this iteration
-    unsigned int extend_next, connect_next, trace_next; // persistent-warp work cursors
-    unsigned int wf_iterations;       // CTA-resident wavefront: most iterations any CTA ran
-    unsigned long long stage_ns[4];   // CTA-resident wavefront: generate, extend, shade, connect time summed over CTAs
+    unsigned int trace_next;          // k_trace: persistent-warp work cursor
+    unsigned int wf_iterations;       // wavefront: most iterations any CTA ran
+    unsigned long long stage_ns[4];   // wavefront: generate, extend, shade, connect time summed over CTAs
 };
 
 __device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }

@@ -1,9 +1,7 @@
-// Wavefront path-tracing kernels: generate → extend → shade → connect, one launch each per
-// iteration.  Together they restate path::Render's sample loop and the recursion of path::Li
-// (path.cpp:4-148) as `rad += thr * Le; thr *= f` over a pool of path slots kept in HBM/L2 as
-// SoA float4 arrays.  A slot whose path ended is pushed on a free queue (warp ballot + one
-// atomic per warp) and refilled with the next camera sample by `generate`, so the pool stays
-// full until the tile's samples run out.
+// Building blocks of the wavefront path tracer (frt_wavefront.cuh) and of the ray-cast entry (k_trace): the path
+// pool layout, the persistent-warp trace loop with dynamic fetch, and camera-sample generation.  Together with
+// frt_shade.cuh they restate path::Render's sample loop and the recursion of path::Li (path.cpp:4-148) as
+// `rad += thr * Le; thr *= f` over a pool of path slots kept as SoA float4 arrays in SHARED memory.
 #pragma once
 #include "frt_device.cuh"
 #include "frt_rng.cuh"
@@ -26,8 +24,6 @@ struct PathPool
     float4 *sh_a;   // shadow ray: origin.xyz, w = to_light.x
     float4 *sh_b;   // to_light.y, to_light.z, contribution.r, contribution.g
     float *sh_c;    // contribution.b
-    unsigned int *free_q[2];
-    unsigned int *shadow_q;
     unsigned int n_slots;
 };
 
@@ -42,10 +38,10 @@ struct TileParams
 struct KernelArgs
 {
     DevScene sc;
-    PathPool pool;
     TileParams tile;
     Counters *ctr;
-    float *film; // nx*ny*3 radiance sums, row 0 = bottom
+    float *film;                // nx*ny*3 radiance sums, row 0 = bottom
+    const volatile int *cancel; // mapped host flag set by frt_cancel (viewer::to_exit, viewer.cpp:101-104 / path.cpp:127)
 };
 
 __device__ __forceinline__ unsigned int lane_id() { return threadIdx.x & 31u; }
@@ -71,15 +67,15 @@ __device__ __forceinline__ unsigned int warp_append(bool pred, unsigned int *cou
 // atomic per warp), so a warp is not held by its slowest ray.  (Letting lanes run several rounds between two
 // looks at the warp was measured: no gain.)  Io::load(item, o, d) fetches a ray,
 // Io::store(sc, walker) consumes the finished traversal; both run for the lanes of one refill together.
-template <bool ANY, bool COUNT, class Io>
+template <bool ANY, bool COUNT, class Io, int WIDE = 4>
 __device__ __forceinline__ void frt_persistent_trace(const DevScene &sc, Io &io, const unsigned int n_items, unsigned int *cursor,
                                                      const int refill_below, unsigned int &n_rays, unsigned int &n_nodes,
                                                      unsigned int &n_tris)
 {
     if (n_items == 0) return;
     const unsigned int lane = lane_id();
-    Walker<ANY, COUNT> w;
-    uint2 stk[FRT_STACK_SIZE];
+    Walker<ANY, COUNT, WIDE> w;
+    uint2 stk[WIDE == 8 ? FRT_STACK8_SIZE : FRT_STACK_SIZE];
     w.active = false;
     bool pending = false, more = true;
     while (true)
@@ -115,6 +111,14 @@ __device__ __forceinline__ void frt_persistent_trace(const DevScene &sc, Io &io,
         }
         if (!more && act == 0) break;
     }
+}
+
+template <bool ANY, bool COUNT, class Io>
+__device__ __forceinline__ void frt_persistent_trace8(const DevScene &sc, Io &io, const unsigned int n_items, unsigned int *cursor,
+                                                      const int refill_below, unsigned int &n_rays, unsigned int &n_nodes,
+                                                      unsigned int &n_tris)
+{
+    frt_persistent_trace<ANY, COUNT, Io, 8>(sc, io, n_items, cursor, refill_below, n_rays, n_nodes, n_tris);
 }
 
 // Camera path number `idx` of the tile (sample idx / npix of pixel idx % npix) into slot `slot`.
@@ -153,132 +157,4 @@ __device__ __forceinline__ void frt_generate_path(const KernelArgs &a, const Pat
     pool.thr[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(pixel));
     pool.rad[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(s));
     pool.prev_p[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-}
-
-__global__ void __launch_bounds__(256) k_generate(const KernelArgs a, const int parity)
-{
-    Counters *ctr = a.ctr;
-    const unsigned int n_free = ctr->n_free[parity];
-    const unsigned int tid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tid == 0)
-    {
-        ctr->n_free[parity ^ 1] = 0; // filled by this iteration's shade
-        ctr->n_shadow = 0;
-        ctr->extend_next = 0;
-        ctr->connect_next = 0;
-    }
-    const unsigned long long total = ctr->total_samples;
-    for (unsigned int i = tid; i < ((n_free + 31u) & ~31u); i += gridDim.x * blockDim.x)
-    {
-        const bool want = i < n_free;
-        // one atomic per warp hands out consecutive sample indices
-        const unsigned int mask = __ballot_sync(0xFFFFFFFFu, want);
-        unsigned long long base = 0;
-        if (lane_id() == 0 && mask) base = atomicAdd(&ctr->next_sample, (unsigned long long)__popc(mask));
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        const unsigned long long idx = base + __popc(mask & ((1u << lane_id()) - 1u));
-        const bool start = want && idx < total;
-        const unsigned int started = __popc(__ballot_sync(0xFFFFFFFFu, start));
-        if (lane_id() == 0 && started)
-        {
-            atomicAdd(&ctr->n_alive, (int)started);
-            atomicAdd(&ctr->samples_started, (unsigned long long)started);
-        }
-        if (!start) continue;
-        frt_generate_path(a, a.pool, a.pool.free_q[parity][i], idx);
-    }
-}
-
-// ---------------------------------------------------------------------------------------------
-// extend: world->hit(r, EPSILON, FLT_MAX, hrec)  path.cpp:10.  Persistent warps pull batches of
-// 32 slots from a global cursor so that long traversals do not hold a block's other warps.
-// ---------------------------------------------------------------------------------------------
-template <bool COUNT>
-__global__ void __launch_bounds__(128) k_extend(const KernelArgs a)
-{
-    unsigned int n_rays = 0, n_nodes = 0, n_tris = 0;
-    const unsigned int n = a.pool.n_slots;
-    while (true)
-    {
-        unsigned int base = 0;
-        if (lane_id() == 0) base = atomicAdd(&a.ctr->extend_next, 32u);
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (base >= n) break;
-        const unsigned int slot = base + lane_id();
-        if (slot >= n) continue;
-        const float4 dw = a.pool.ray_d[slot];
-        if (!(__float_as_uint(dw.w) & FRT_FLAG_ALIVE)) continue;
-        const float4 ow = a.pool.ray_o[slot];
-        const RayHit h = frt_traverse<false, COUNT>(a.sc, f3(ow), f3(dw), FRT_FLT_MAX, n_nodes, n_tris);
-        a.pool.hit[slot] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
-        ++n_rays;
-    }
-    // one set of atomics per warp
-    for (int off = 16; off > 0; off >>= 1)
-    {
-        n_rays += __shfl_down_sync(0xFFFFFFFFu, n_rays, off);
-        if (COUNT)
-        {
-            n_nodes += __shfl_down_sync(0xFFFFFFFFu, n_nodes, off);
-            n_tris += __shfl_down_sync(0xFFFFFFFFu, n_tris, off);
-        }
-    }
-    if (lane_id() == 0)
-    {
-        if (n_rays) atomicAdd(&a.ctr->closest_rays, (unsigned long long)n_rays);
-        if (COUNT)
-        {
-            atomicAdd(&a.ctr->node_visits, (unsigned long long)n_nodes);
-            atomicAdd(&a.ctr->tri_tests, (unsigned long long)n_tris);
-        }
-    }
-}
-
-// ---------------------------------------------------------------------------------------------
-// connect: !world->hit(shadow_ray, EPSILON, 1 - SHADOW_EPSILON, lrec)  path.cpp:50, any-hit
-// with early exit; the contribution computed by shade is committed when unoccluded (path.cpp:73)
-// ---------------------------------------------------------------------------------------------
-template <bool COUNT>
-__global__ void __launch_bounds__(128) k_connect(const KernelArgs a)
-{
-    unsigned int n_rays = 0, n_nodes = 0, n_tris = 0;
-    const unsigned int n = a.ctr->n_shadow;
-    while (true)
-    {
-        unsigned int base = 0;
-        if (lane_id() == 0) base = atomicAdd(&a.ctr->connect_next, 32u);
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (base >= n) break;
-        const unsigned int i = base + lane_id();
-        if (i >= n) continue;
-        const unsigned int slot = a.pool.shadow_q[i];
-        const float4 sa = a.pool.sh_a[slot], sb = a.pool.sh_b[slot];
-        const RayHit h = frt_traverse<true, COUNT>(a.sc, f3(sa), f3(sa.w, sb.x, sb.y), 1.0f - FRT_SHADOW_EPSILON,
-                                                   n_nodes, n_tris);
-        ++n_rays;
-        if (h.prim == 0xFFFFFFFFu)
-        {
-            float4 r = a.pool.rad[slot];
-            r.x += sb.z; r.y += sb.w; r.z += a.pool.sh_c[slot];
-            a.pool.rad[slot] = r;
-        }
-    }
-    for (int off = 16; off > 0; off >>= 1)
-    {
-        n_rays += __shfl_down_sync(0xFFFFFFFFu, n_rays, off);
-        if (COUNT)
-        {
-            n_nodes += __shfl_down_sync(0xFFFFFFFFu, n_nodes, off);
-            n_tris += __shfl_down_sync(0xFFFFFFFFu, n_tris, off);
-        }
-    }
-    if (lane_id() == 0)
-    {
-        if (n_rays) atomicAdd(&a.ctr->shadow_rays, (unsigned long long)n_rays);
-        if (COUNT)
-        {
-            atomicAdd(&a.ctr->node_visits, (unsigned long long)n_nodes);
-            atomicAdd(&a.ctr->tri_tests, (unsigned long long)n_tris);
-        }
-    }
 }

@@ -1,29 +1,6 @@
-// Part of frt_core.cu: wavefront driver loop, film readback, ray-cast entry points.
+// Part of frt_core.cu: tile launch, film sum / readback / tone map, cancellation, ray-cast entry points.
 
 namespace {
-
-void timer_mark(Device &d, int kind, bool begin)
-{
-    cudaEvent_t e;
-    cudaEventCreate(&e);
-    cudaEventRecord(e, d.stream);
-    d.timers.ev.push_back(e);
-    if (begin) d.timers.kind.push_back(kind);
-}
-
-void timer_collect(Device &d)
-{
-    for (size_t i = 0; i + 1 < d.timers.ev.size(); i += 2)
-    {
-        float ms = 0.f;
-        cudaEventElapsedTime(&ms, d.timers.ev[i], d.timers.ev[i + 1]);
-        d.timers.ms[d.timers.kind[i / 2]] += ms;
-        cudaEventDestroy(d.timers.ev[i]);
-        cudaEventDestroy(d.timers.ev[i + 1]);
-    }
-    d.timers.ev.clear();
-    d.timers.kind.clear();
-}
 
 int ensure_film(frt_ctx *ctx, uint32_t nx, uint32_t ny)
 {
@@ -34,7 +11,7 @@ int ensure_film(frt_ctx *ctx, uint32_t nx, uint32_t ny)
         if (d.film_floats != n)
         {
             if (d.d_film) cudaFree(d.d_film);
-            if (d.d_film_peer) { cudaFree(d.d_film_peer); d.d_film_peer = nullptr; }
+            if (d.d_film_stage) { cudaFree(d.d_film_stage); d.d_film_stage = nullptr; }
             d.d_film = nullptr;
             CU(cudaMalloc((void **)&d.d_film, n * sizeof(float)));
             d.film_floats = n;
@@ -45,27 +22,120 @@ int ensure_film(frt_ctx *ctx, uint32_t nx, uint32_t ny)
     return FRT_OK;
 }
 
-// One wavefront iteration on one device: generate → extend → shade → connect.
-template <bool COUNT>
-void launch_iteration(frt_ctx *ctx, Device &d, const KernelArgs &a)
+// ctx-owned pinned host staging of the film: sums (float) and the 8-bit image
+int ensure_host_film(frt_ctx *ctx, size_t n)
 {
-    const int parity = (int)(d.tile_iter & 1ull);
-    const unsigned int n = d.pool.n_slots;
-    const bool timed = ctx->flags & FRT_FLAG_KERNEL_TIMERS;
-    const int gs_blocks = std::min<unsigned int>((n + 255u) / 256u, (unsigned int)d.sms * 8u);
-    const int sh_blocks = std::min<unsigned int>((n + 127u) / 128u, (unsigned int)d.sms * 16u);
-    if (timed) timer_mark(d, 0, true);
-    k_generate<<<gs_blocks, 256, 0, d.stream>>>(a, parity);
-    if (timed) { timer_mark(d, 0, false); timer_mark(d, 1, true); }
-    k_extend<COUNT><<<d.blocks_extend, 128, 0, d.stream>>>(a);
-    if (timed) { timer_mark(d, 1, false); timer_mark(d, 2, true); }
-    k_shade<<<sh_blocks, 128, 0, d.stream>>>(a, parity ^ 1);
-    if (timed) { timer_mark(d, 2, false); timer_mark(d, 3, true); }
-    k_connect<COUNT><<<d.blocks_connect, 128, 0, d.stream>>>(a);
-    if (timed) timer_mark(d, 3, false);
-    d.iterations += 1;
-    d.tile_iter += 1;
-    d.launches += 4;
+    if (ctx->h_film_floats == n) return FRT_OK;
+    if (ctx->h_film) { cudaFreeHost(ctx->h_film); ctx->h_film = nullptr; }
+    if (ctx->h_ldr) { cudaFreeHost(ctx->h_ldr); ctx->h_ldr = nullptr; }
+    ctx->h_film_floats = 0;
+    CU(cudaSetDevice(ctx->dev[0].ordinal));
+    if (ctx->d_ldr) { cudaFree(ctx->d_ldr); ctx->d_ldr = nullptr; }
+    CU(cudaHostAlloc((void **)&ctx->h_film, n * sizeof(float), cudaHostAllocPortable));
+    CU(cudaHostAlloc((void **)&ctx->h_ldr, n, cudaHostAllocPortable));
+    CU(cudaMalloc((void **)&ctx->d_ldr, n));
+    ctx->h_film_floats = n;
+    return FRT_OK;
+}
+
+// Waits for every device's tiles, gathers the counters and leaves the SUM of the per-device films in device 0's film
+// (stream-ordered on device 0's stream: the caller enqueues its copies behind it).
+int finish_render(frt_ctx *ctx, frt_stats *out)
+{
+    frt_stats st;
+    memset(&st, 0, sizeof st);
+    Device &d0 = ctx->dev[0];
+    const int nd = (int)ctx->dev.size();
+    // the film sum first, so that it overlaps the counter copies: every device sums its range of all the films over
+    // peer loads as soon as ALL renders are done, and stores it into device 0's film
+    int n_rendered = 0;
+    for (Device &d : ctx->dev) n_rendered += d.rendered ? 1 : 0;
+    const bool need_sum = nd > 1 && d0.d_film && (n_rendered > 1 || (n_rendered == 1 && !d0.rendered));
+    if (need_sum && ctx->peer_ok)
+    {
+        PeerFilms films;
+        films.n = 0;
+        for (Device &d : ctx->dev) films.p[films.n++] = d.d_film; // a device that rendered nothing holds zeros
+        const size_t n4 = d0.film_floats / 4;
+        for (int g = 0; g < nd; ++g)
+        {
+            Device &d = ctx->dev[g];
+            CU(cudaSetDevice(d.ordinal));
+            for (int k = 0; k < nd; ++k)
+                if (k != g && ctx->dev[k].rendered) CU(cudaStreamWaitEvent(d.stream, ctx->dev[k].ev_end, 0));
+            const size_t b4 = n4 * g / nd, e4 = n4 * (g + 1) / nd;
+            const size_t tb = g == nd - 1 ? 4 * n4 : 0, te = g == nd - 1 ? d0.film_floats : 0;
+            k_sum_slice<<<d.sms * 2, 256, 0, d.stream>>>(d0.d_film, films, b4, e4, tb, te);
+            CU(cudaGetLastError());
+            CU(cudaEventRecord(d.ev_sum, d.stream));
+            d.launches += 1;
+        }
+        CU(cudaSetDevice(d0.ordinal));
+        for (int g = 1; g < nd; ++g) CU(cudaStreamWaitEvent(d0.stream, ctx->dev[g].ev_sum, 0));
+    }
+    else if (need_sum)
+    {
+        // no peer access: the films are copied to device 0 one after the other and added there
+        CU(cudaSetDevice(d0.ordinal));
+        if (!d0.d_film_stage) CU(cudaMalloc((void **)&d0.d_film_stage, d0.film_floats * sizeof(float)));
+        for (int g = 1; g < nd; ++g)
+        {
+            Device &d = ctx->dev[g];
+            if (!d.rendered) continue;
+            CU(cudaStreamWaitEvent(d0.stream, d.ev_end, 0));
+            CU(cudaMemcpyPeerAsync(d0.d_film_stage, d0.ordinal, d.d_film, d.ordinal, d0.film_floats * sizeof(float), d0.stream));
+            PeerFilms two;
+            two.n = 2; two.p[0] = d0.d_film; two.p[1] = d0.d_film_stage;
+            k_sum_slice<<<d0.sms * 2, 256, 0, d0.stream>>>(d0.d_film, two, 0, d0.film_floats / 4, d0.film_floats / 4 * 4, d0.film_floats);
+            CU(cudaGetLastError());
+            d0.launches += 1;
+        }
+    }
+    for (Device &d : ctx->dev)
+    {
+        CU(cudaSetDevice(d.ordinal));
+        CU(cudaMemcpyAsync(d.h_ctr, d.d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
+    }
+    for (Device &d : ctx->dev)
+    {
+        CU(cudaSetDevice(d.ordinal));
+        CU(cudaStreamSynchronize(d.stream));
+        st.samples += d.h_ctr->samples_started;
+        st.closest_rays += d.h_ctr->closest_rays;
+        st.shadow_rays += d.h_ctr->shadow_rays;
+        st.node_visits += d.h_ctr->node_visits;
+        st.tri_tests += d.h_ctr->tri_tests;
+        st.iterations = std::max<uint64_t>(st.iterations, d.h_ctr->wf_iterations);
+        st.kernel_launches += d.launches;
+        if (d.rendered)
+        {
+            float ms = 0.f;
+            CU(cudaEventElapsedTime(&ms, d.ev_begin, d.ev_end));
+            st.render_ms = std::max<double>(st.render_ms, ms);
+        }
+        const double per_cta = d.wf_ctas_launched ? 1e-6 / d.wf_ctas_launched : 0.0; // ns summed over CTAs -> mean ms
+        st.generate_ms = std::max(st.generate_ms, d.h_ctr->stage_ns[0] * per_cta);
+        st.extend_ms = std::max(st.extend_ms, d.h_ctr->stage_ns[1] * per_cta);
+        st.shade_ms = std::max(st.shade_ms, d.h_ctr->stage_ns[2] * per_cta);
+        st.connect_ms = std::max(st.connect_ms, d.h_ctr->stage_ns[3] * per_cta);
+    }
+    if (need_sum)
+    {
+        // the partial sums are folded into device 0: clear the others so that a second readback (or further tiles)
+        // does not count them twice
+        for (int g = 1; g < nd; ++g)
+        {
+            Device &d = ctx->dev[g];
+            CU(cudaSetDevice(d.ordinal));
+            CU(cudaMemsetAsync(d.d_film, 0, d.film_floats * sizeof(float), d.stream));
+            d.rendered = false;
+        }
+        d0.rendered = true;
+        CU(cudaSetDevice(d0.ordinal));
+    }
+    ctx->stats = st;
+    if (out) *out = st;
+    return FRT_OK;
 }
 
 } // namespace
@@ -80,10 +150,9 @@ int frt_clear_film(frt_ctx *ctx)
         CU(cudaSetDevice(d.ordinal));
         if (d.d_film) CU(cudaMemsetAsync(d.d_film, 0, d.film_floats * sizeof(float), d.stream));
         CU(cudaMemsetAsync(d.d_ctr, 0, sizeof(Counters), d.stream));
-        d.iterations = d.launches = 0;
+        d.launches = 0;
         d.wf_ctas_launched = 0;
         d.rendered = false;
-        for (double &m : d.timers.ms) m = 0;
     }
     memset(&ctx->stats, 0, sizeof ctx->stats);
     return FRT_OK;
@@ -93,24 +162,24 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
 {
     if (!ctx || !t) return FRT_ERR_INVALID;
     if (!ctx->have_scene) return fail(ctx, FRT_ERR_STATE, "frt_render_tile: no scene uploaded");
-    if (t->nx == 0 || t->ny == 0 || t->w == 0 || t->h == 0 || t->x0 + t->w > t->nx || t->y0 + t->h > t->ny)
+    // bounds without 32-bit wrap-around: x0 = 0xFFFFFFF0, w = 0x20 must not pass
+    if (t->nx == 0 || t->ny == 0 || t->w == 0 || t->h == 0 || t->w > t->nx || t->x0 > t->nx - t->w || t->h > t->ny || t->y0 > t->ny - t->h)
         return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: tile outside the film");
+    if ((uint64_t)t->nx * t->ny >= (1ull << 32) / 3)
+        return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: film of %u x %u pixels is too large (pixel indices are 32-bit)", t->nx, t->ny);
     if (t->spp_end < t->spp_begin) return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: empty sample range");
     if (t->max_depth > 200) return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: max_depth too large");
     if (t->integrator > FRT_INTEGRATOR_DIRECT || t->reserved != 0)
         return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: unknown integrator %u", t->integrator);
     if (t->integrator == FRT_INTEGRATOR_AO && !(ctx->ao_t_max > 0.f))
         return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: ao needs frt_scene_desc::ao_t_max > 0");
-    if (t->integrator != FRT_INTEGRATOR_PATH && (ctx->flags & FRT_FLAG_STREAMED_POOL))
-        return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: the streamed pool runs the path integrator only");
     int rc = ensure_film(ctx, t->nx, t->ny);
     if (rc != FRT_OK) return rc;
+    *ctx->h_cancel = 0; // a cancel request applies to the tiles launched before it
 
     const int nd = (int)ctx->dev.size();
     const uint32_t spp = t->spp_end - t->spp_begin;
-    const bool streamed = ctx->flags & FRT_FLAG_STREAMED_POOL;
     const bool count = ctx->flags & FRT_FLAG_COUNTERS;
-    std::vector<KernelArgs> args(nd);
     for (int i = 0; i < nd; ++i)
     {
         Device &d = ctx->dev[i];
@@ -118,86 +187,60 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
         // spp range split evenly over the devices
         const uint32_t s0 = t->spp_begin + (uint32_t)(((uint64_t)spp * i) / nd);
         const uint32_t s1 = t->spp_begin + (uint32_t)(((uint64_t)spp * (i + 1)) / nd);
-        KernelArgs &a = args[i];
+        KernelArgs a;
         a.sc = t->integrator == FRT_INTEGRATOR_AO ? device_view(ctx, d, (double)ctx->ao_t_max) : device_view(ctx, d);
-        a.pool = d.pool;
         a.tile.nx = t->nx; a.tile.ny = t->ny; a.tile.x0 = t->x0; a.tile.y0 = t->y0; a.tile.w = t->w; a.tile.h = t->h;
         a.tile.spp_begin = s0; a.tile.seed = t->seed; a.tile.max_depth = t->max_depth; a.tile.integrator = t->integrator;
         a.ctr = d.d_ctr;
         a.film = d.d_film;
+        int *dc = nullptr;
+        CU(cudaHostGetDevicePointer((void **)&dc, ctx->h_cancel, 0));
+        a.cancel = dc;
         const unsigned long long total = (unsigned long long)t->w * t->h * (s1 - s0);
-        d.done = total == 0;
-        if (d.done) continue;
+        if (total == 0) continue;
         if (!d.rendered) CU(cudaEventRecord(d.ev_begin, d.stream));
         d.rendered = true;
-        if (!streamed)
-        {
-            // CTA-resident pool: the whole tile is one persistent launch; nothing to poll
-            const size_t smem = (size_t)ctx->wf_slots * FRT_WF_SLOT_BYTES;
-            // no more CTAs than can be kept busy: one CTA-iteration consumes up to wf_slots samples
-            const unsigned long long want = (total + ctx->wf_slots - 1) / ctx->wf_slots;
-            // the general kernel: the integrators next to `path`, and `path` itself over textured surfaces
-            const bool other = t->integrator != FRT_INTEGRATOR_PATH || ctx->host_view.n_textures != 0;
-            const WfConfig &wc = other ? wf_other : wf_configs[ctx->wf_config];
-            const int resident = other ? d.blocks_wavefront_other : d.blocks_wavefront;
-            if (resident < 1) return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: FRT_WF_SLOTS=%u leaves no room for this integrator's kernel", ctx->wf_slots);
-            const unsigned int grid = (unsigned int)std::min<unsigned long long>((unsigned long long)resident, want);
-            k_reset_tile<<<1, 1, 0, d.stream>>>(d.d_ctr, total);
-            (count ? wc.counting : wc.plain)<<<grid, wc.threads, smem, d.stream>>>(a, ctx->wf_slots, ctx->wf_refill,
-                                                                                     ctx->wf_sort >= 0 ? ctx->wf_sort : (ctx->multi_bsdf ? 3 : 1));
-            CU(cudaGetLastError());
-            CU(cudaEventRecord(d.ev_end, d.stream));
-            d.launches += 2;
-            d.wf_ctas_launched += grid;
-            d.done = true;
-            continue;
-        }
-        if (d.pool.n_slots != ctx->n_slots)
-        {
-            int prc = alloc_pool(ctx, d, ctx->n_slots);
-            if (prc != FRT_OK) return prc;
-            a.pool = d.pool;
-        }
-        d.tile_iter = 0; // queue parity restarts with the pool reset
-        k_reset_pool<<<(d.pool.n_slots + 255) / 256, 256, 0, d.stream>>>(d.pool, d.d_ctr, total);
-        d.launches += 1;
+        // the whole tile is one persistent launch: path state lives in the CTAs' shared memory
+        const size_t smem = (size_t)ctx->wf_slots * FRT_WF_SLOT_BYTES;
+        // no more CTAs than can be kept busy: one CTA-iteration consumes up to wf_slots samples
+        const unsigned long long want = (total + ctx->wf_slots - 1) / ctx->wf_slots;
+        // the general kernel: the integrators next to `path`, and `path` itself over textured surfaces
+        const bool other = t->integrator != FRT_INTEGRATOR_PATH || ctx->host_view.n_textures != 0;
+        const WfConfig &wc = other ? wf_other : wf_configs[ctx->wf_config];
+        const int resident = other ? d.blocks_wavefront_other : d.blocks_wavefront;
+        if (resident < 1) return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: FRT_WF_SLOTS=%u leaves no room for this integrator's kernel", ctx->wf_slots);
+        const unsigned int grid = (unsigned int)std::min<unsigned long long>((unsigned long long)resident, want);
+        k_reset_tile<<<1, 1, 0, d.stream>>>(d.d_ctr, total);
+        (count ? wc.counting : wc.plain)<<<grid, wc.threads, smem, d.stream>>>(a, ctx->wf_slots, ctx->wf_refill,
+                                                                                 ctx->wf_sort >= 0 ? ctx->wf_sort : (ctx->multi_bsdf ? 3 : 1));
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(d.ev_end, d.stream));
+        d.launches += 2;
+        d.wf_ctas_launched += grid;
     }
-    // streamed pool: lock-step issue across devices; a device is polled every poll_every iterations
-    bool all_done = true;
-    for (int i = 0; i < nd; ++i) all_done = all_done && ctx->dev[i].done;
-    while (!all_done)
+    return FRT_OK;
+}
+
+// viewer::to_exit (viewer.cpp:101-104) / path.cpp:127: the tiles launched so far stop taking samples and drop their
+// paths in flight; frt_readback then returns whatever the film holds.  Callable from any thread.
+int frt_cancel(frt_ctx *ctx)
+{
+    if (!ctx || !ctx->h_cancel) return FRT_ERR_INVALID;
+    *(volatile int *)ctx->h_cancel = 1;
+    return FRT_OK;
+}
+
+// Non-blocking: *done = 1 when every tile launched so far has finished on every device.
+int frt_poll(frt_ctx *ctx, int *done)
+{
+    if (!ctx || !done) return FRT_ERR_INVALID;
+    *done = 1;
+    for (Device &d : ctx->dev)
     {
-        for (int it = 0; it < ctx->poll_every; ++it)
-            for (int i = 0; i < nd; ++i)
-            {
-                Device &d = ctx->dev[i];
-                if (d.done) continue;
-                cudaSetDevice(d.ordinal);
-                if (count) launch_iteration<true>(ctx, d, args[i]); else launch_iteration<false>(ctx, d, args[i]);
-            }
-        for (int i = 0; i < nd; ++i)
-        {
-            Device &d = ctx->dev[i];
-            if (d.done) continue;
-            CU(cudaSetDevice(d.ordinal));
-            CU(cudaMemcpyAsync(d.h_ctr, d.d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
-        }
-        all_done = true;
-        for (int i = 0; i < nd; ++i)
-        {
-            Device &d = ctx->dev[i];
-            if (d.done) continue;
-            CU(cudaSetDevice(d.ordinal));
-            CU(cudaStreamSynchronize(d.stream));
-            if (ctx->flags & FRT_FLAG_KERNEL_TIMERS) timer_collect(d);
-            if (d.h_ctr->next_sample >= d.h_ctr->total_samples && d.h_ctr->n_alive == 0)
-            {
-                d.done = true;
-                CU(cudaEventRecord(d.ev_end, d.stream));
-            }
-            else
-                all_done = false;
-        }
+        if (!d.rendered) continue;
+        const cudaError_t e = cudaEventQuery(d.ev_end);
+        if (e == cudaErrorNotReady) { *done = 0; cudaGetLastError(); }
+        else if (e != cudaSuccess) return fail(ctx, FRT_ERR_CUDA, "frt_poll: %s", cudaGetErrorString(e));
     }
     return FRT_OK;
 }
@@ -263,139 +306,184 @@ int frt_readback(frt_ctx *ctx, float *rgb_sum, size_t n_floats, frt_stats *stats
     if (!d0.d_film) return fail(ctx, FRT_ERR_STATE, "frt_readback: nothing rendered");
     if (rgb_sum && n_floats != d0.film_floats)
         return fail(ctx, FRT_ERR_INVALID, "frt_readback: expected %zu floats, got %zu", d0.film_floats, n_floats);
-    frt_stats st;
-    memset(&st, 0, sizeof st);
-    for (Device &d : ctx->dev)
-    {
-        CU(cudaSetDevice(d.ordinal));
-        CU(cudaMemcpyAsync(d.h_ctr, d.d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
-        CU(cudaStreamSynchronize(d.stream));
-        st.samples += d.h_ctr->samples_started;
-        st.closest_rays += d.h_ctr->closest_rays;
-        st.shadow_rays += d.h_ctr->shadow_rays;
-        st.node_visits += d.h_ctr->node_visits;
-        st.tri_tests += d.h_ctr->tri_tests;
-        st.iterations = std::max<uint64_t>(st.iterations, d.iterations + d.h_ctr->wf_iterations);
-        st.kernel_launches += d.launches;
-        if (d.rendered)
-        {
-            float ms = 0.f;
-            CU(cudaEventElapsedTime(&ms, d.ev_begin, d.ev_end));
-            st.render_ms = std::max<double>(st.render_ms, ms);
-        }
-        const double per_cta = d.wf_ctas_launched ? 1e-6 / d.wf_ctas_launched : 0.0; // ns summed over CTAs -> mean ms
-        st.generate_ms = std::max(st.generate_ms, d.timers.ms[0] + d.h_ctr->stage_ns[0] * per_cta);
-        st.extend_ms = std::max(st.extend_ms, d.timers.ms[1] + d.h_ctr->stage_ns[1] * per_cta);
-        st.shade_ms = std::max(st.shade_ms, d.timers.ms[2] + d.h_ctr->stage_ns[2] * per_cta);
-        st.connect_ms = std::max(st.connect_ms, d.timers.ms[3] + d.h_ctr->stage_ns[3] * per_cta);
-    }
-    // in-process multi-GPU: device 0 sums its peers' films (P2P loads over NVLink when enabled)
-    if (ctx->dev.size() > 1)
-    {
-        CU(cudaSetDevice(d0.ordinal));
-        PeerFilms peers;
-        peers.n = 0;
-        for (size_t i = 1; i < ctx->dev.size(); ++i)
-        {
-            Device &d = ctx->dev[i];
-            if (!d.rendered) continue;
-            if (ctx->peer_ok)
-                peers.p[peers.n++] = d.d_film;
-            else
-            {
-                if (!d0.d_film_peer) CU(cudaMalloc((void **)&d0.d_film_peer, d0.film_floats * sizeof(float)));
-                CU(cudaMemcpyPeerAsync(d0.d_film_peer, d0.ordinal, d.d_film, d.ordinal, d0.film_floats * sizeof(float), d0.stream));
-                PeerFilms one;
-                one.n = 1; one.p[0] = d0.d_film_peer;
-                k_sum_films<<<d0.sms * 4, 256, 0, d0.stream>>>(d0.d_film, one, d0.film_floats);
-            }
-        }
-        if (peers.n) k_sum_films<<<d0.sms * 4, 256, 0, d0.stream>>>(d0.d_film, peers, d0.film_floats);
-        CU(cudaStreamSynchronize(d0.stream));
-        // the peers' partial sums are now folded into device 0: clear them so a second readback
-        // (or further tiles) does not count them twice
-        for (size_t i = 1; i < ctx->dev.size(); ++i)
-        {
-            Device &d = ctx->dev[i];
-            CU(cudaSetDevice(d.ordinal));
-            CU(cudaMemsetAsync(d.d_film, 0, d.film_floats * sizeof(float), d.stream));
-        }
-        CU(cudaSetDevice(d0.ordinal));
-    }
-    if (rgb_sum) CU(cudaMemcpy(rgb_sum, d0.d_film, n_floats * sizeof(float), cudaMemcpyDeviceToHost));
-    ctx->stats = st;
-    if (stats) *stats = st;
+    int rc = finish_render(ctx, stats);
+    if (rc != FRT_OK) return rc;
+    if (!rgb_sum) { CU(cudaStreamSynchronize(d0.stream)); return FRT_OK; }
+    // device -> pinned staging at link speed, then out to the caller's (pageable) buffer on several host threads
+    if ((rc = ensure_host_film(ctx, d0.film_floats)) != FRT_OK) return rc;
+    CU(cudaSetDevice(d0.ordinal));
+    CU(cudaMemcpyAsync(ctx->h_film, d0.d_film, n_floats * sizeof(float), cudaMemcpyDeviceToHost, d0.stream));
+    CU(cudaStreamSynchronize(d0.stream));
+    const float *src = ctx->h_film;
+    parallel_chunks(n_floats, 1u << 19, [=](size_t b, size_t e) { memcpy(rgb_sum + b, src + b, (e - b) * sizeof(float)); });
     return FRT_OK;
 }
 
-int frt_trace_rays_device(frt_ctx *ctx, int dev, const void *d_rays, size_t n, void *d_hits, int any_hit, double *device_ms)
+// Replaces the per-pixel viewer::add_sample calls of path.cpp:143 for the whole film (viewer.cpp:109-132): the mean
+// c = sum * (1 / ns) goes to fout_image (double) and / or mean_rgb (float32), the tone-mapped
+// int(pow(1 - exp(-c), 1 / 2.2) * 255 + .5) — evaluated in double on device 0 — to out_image.  Each of the three
+// outputs may be NULL.  Layout nx * ny * 3, row 0 = bottom, like the viewer's buffers.
+int frt_readback_film(frt_ctx *ctx, uint64_t ns, double *fout_image, unsigned char *out_image, float *mean_rgb, frt_stats *stats)
+{
+    if (!ctx || ns == 0) return FRT_ERR_INVALID;
+    Device &d0 = ctx->dev[0];
+    if (!d0.d_film) return fail(ctx, FRT_ERR_STATE, "frt_readback_film: nothing rendered");
+    int rc = finish_render(ctx, stats);
+    if (rc != FRT_OK) return rc;
+    const size_t n = d0.film_floats;
+    if ((rc = ensure_host_film(ctx, n)) != FRT_OK) return rc;
+    CU(cudaSetDevice(d0.ordinal));
+    const double inv_ns = 1.0 / (double)ns; // geometry.h:533-538: operator/= multiplies by the reciprocal
+    if (out_image)
+    {
+        k_tonemap<<<d0.sms * 4, 256, 0, d0.stream>>>(d0.d_film, ctx->d_ldr, n, inv_ns);
+        CU(cudaGetLastError());
+        d0.launches += 1;
+        ctx->stats.kernel_launches += 1;
+        if (stats) stats->kernel_launches += 1;
+        CU(cudaMemcpyAsync(ctx->h_ldr, ctx->d_ldr, n, cudaMemcpyDeviceToHost, d0.stream));
+    }
+    if (fout_image || mean_rgb) CU(cudaMemcpyAsync(ctx->h_film, d0.d_film, n * sizeof(float), cudaMemcpyDeviceToHost, d0.stream));
+    CU(cudaStreamSynchronize(d0.stream));
+    const float *sums = ctx->h_film;
+    const unsigned char *ldr = ctx->h_ldr;
+    parallel_chunks(n, 1u << 18, [=](size_t b, size_t e) {
+        if (fout_image) for (size_t i = b; i < e; ++i) fout_image[i] = (double)sums[i] * inv_ns;
+        if (mean_rgb) for (size_t i = b; i < e; ++i) mean_rgb[i] = (float)((double)sums[i] * inv_ns);
+        if (out_image) memcpy(out_image + b, ldr + b, e - b);
+    });
+    return FRT_OK;
+}
+
+int frt_trace_rays_device(frt_ctx *ctx, int dev, const void *d_rays, size_t n, void *d_hits, int mode, double *device_ms)
 {
     if (!ctx || dev < 0 || dev >= (int)ctx->dev.size()) return FRT_ERR_INVALID;
     if (!ctx->have_scene) return fail(ctx, FRT_ERR_STATE, "frt_trace_rays: no scene uploaded");
     if (n > 0xFFFFFF00ull) return fail(ctx, FRT_ERR_INVALID, "frt_trace_rays: too many rays in one call");
+    if (mode & ~(FRT_TRACE_ANY_HIT | FRT_TRACE_SORT)) return fail(ctx, FRT_ERR_INVALID, "frt_trace_rays: unknown mode bits %d", mode);
     if (n == 0) { if (device_ms) *device_ms = 0; return FRT_OK; }
     Device &d = ctx->dev[dev];
     CU(cudaSetDevice(d.ordinal));
     const DevScene sc = device_view(ctx, d);
-    const bool count = ctx->flags & FRT_FLAG_COUNTERS;
-    cudaEvent_t e0, e1;
-    CU(cudaEventCreate(&e0));
-    CU(cudaEventCreate(&e1));
-    CU(cudaMemsetAsync(&d.d_ctr->trace_next, 0, sizeof(unsigned int), d.stream));
-    CU(cudaEventRecord(e0, d.stream));
+    const bool count = ctx->flags & FRT_FLAG_COUNTERS, any_hit = mode & FRT_TRACE_ANY_HIT;
     const float2 *r = (const float2 *)d_rays;
     frt_hit *h = (frt_hit *)d_hits;
-    if (any_hit)
+    const uint32_t *order = nullptr;
+    CU(cudaMemsetAsync(&d.d_ctr->trace_next, 0, sizeof(unsigned int), d.stream));
+    if (mode & FRT_TRACE_SORT)
     {
-        if (count) k_trace<true, true><<<d.blocks_trace_any, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, (unsigned int)n, ctx->wf_refill);
-        else k_trace<true, false><<<d.blocks_trace_any, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, (unsigned int)n, ctx->wf_refill);
+        const size_t words = frt_sort_scratch_words(n);
+        if (d.sort_cap < words)
+        {
+            if (d.d_sort) { cudaFree(d.d_sort); d.d_sort = nullptr; d.sort_cap = 0; }
+            CU(cudaMalloc(&d.d_sort, words * sizeof(uint32_t)));
+            d.sort_cap = words;
+        }
+    }
+    CU(cudaEventRecord(d.ev_t0, d.stream));
+    if (mode & FRT_TRACE_SORT) // the ordering is part of the call and of its device time
+        CU(frt_sort_rays(r, (unsigned int)n, ctx->bounds_lo, ctx->bounds_hi, (uint32_t *)d.d_sort, &order, d.stream, &d.launches));
+    const int refill = any_hit ? 0 : ctx->wf_refill;
+    if (ctx->have_wide8)
+    {
+        const int blocks = any_hit ? d.blocks_trace8_any : d.blocks_trace8;
+        if (any_hit)
+        {
+            if (count) k_trace8<true, true><<<blocks, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
+            else k_trace8<true, false><<<blocks, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
+        }
+        else
+        {
+            if (count) k_trace8<false, true><<<blocks, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
+            else k_trace8<false, false><<<blocks, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
+        }
+    }
+    else if (any_hit)
+    {
+        if (count) k_trace<true, true><<<d.blocks_trace_any, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
+        else k_trace<true, false><<<d.blocks_trace_any, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
     }
     else
     {
-        if (count) k_trace<false, true><<<d.blocks_trace, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, (unsigned int)n, ctx->wf_refill);
-        else k_trace<false, false><<<d.blocks_trace, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, (unsigned int)n, ctx->wf_refill);
+        if (count) k_trace<false, true><<<d.blocks_trace, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
+        else k_trace<false, false><<<d.blocks_trace, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
     }
-    CU(cudaEventRecord(e1, d.stream));
-    CU(cudaEventSynchronize(e1));
     CU(cudaGetLastError());
-    float ms = 0.f;
-    CU(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
+    CU(cudaEventRecord(d.ev_t1, d.stream));
     d.launches += 1;
-    if (device_ms) *device_ms = ms;
+    if (device_ms) // NULL = asynchronous: the caller synchronises the stream (frt_trace_rays does, once, for all devices)
+    {
+        CU(cudaEventSynchronize(d.ev_t1));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, d.ev_t0, d.ev_t1));
+        *device_ms = ms;
+    }
     return FRT_OK;
 }
 
-int frt_trace_rays(frt_ctx *ctx, const frt_ray *rays, size_t n, frt_hit *hits, int any_hit, double *device_ms)
+int frt_trace_rays(frt_ctx *ctx, const frt_ray *rays, size_t n, frt_hit *hits, int mode, double *device_ms)
 {
     if (!ctx || (n && (!rays || !hits))) return FRT_ERR_INVALID;
     if (!ctx->have_scene) return fail(ctx, FRT_ERR_STATE, "frt_trace_rays: no scene uploaded");
     const int nd = (int)ctx->dev.size();
-    double worst = 0;
-    // block partition over devices (no exchange)
+    if (device_ms) *device_ms = 0;
+    if (n == 0) return FRT_OK;
+    // Block partition over the devices (no exchange).  Every device's copy in, kernel and copy out are
+    // enqueued on its own stream before anything is waited for, so the devices work at the same time.  Pinned caller
+    // buffers (frt_host_alloc, cudaHostAlloc, cudaHostRegister) are copied asynchronously straight from / to the
+    // caller; pageable ones are staged by the runtime inside cudaMemcpyAsync, which blocks the issuing thread, so
+    // each device then gets its own host thread.
+    struct Part { size_t b, e; int rc; };
+    std::vector<Part> parts(nd);
+    for (int i = 0; i < nd; ++i) { parts[i].b = n * i / nd; parts[i].e = n * (i + 1) / nd; parts[i].rc = FRT_OK; }
     for (int i = 0; i < nd; ++i)
     {
-        const size_t b = n * i / nd, e = n * (i + 1) / nd;
-        if (e == b) continue;
         Device &d = ctx->dev[i];
+        const size_t m = parts[i].e - parts[i].b;
+        if (m == 0 || d.trace_cap >= m) continue;
         CU(cudaSetDevice(d.ordinal));
-        void *dr = nullptr, *dh = nullptr;
-        CU(cudaMalloc(&dr, (e - b) * sizeof(frt_ray)));
-        CU(cudaMalloc(&dh, (e - b) * sizeof(frt_hit)));
-        CU(cudaMemcpyAsync(dr, rays + b, (e - b) * sizeof(frt_ray), cudaMemcpyHostToDevice, d.stream));
-        double ms = 0;
-        int rc = frt_trace_rays_device(ctx, i, dr, e - b, dh, any_hit, &ms);
-        if (rc == FRT_OK)
-        {
-            cudaError_t ce = cudaMemcpyAsync(hits + b, dh, (e - b) * sizeof(frt_hit), cudaMemcpyDeviceToHost, d.stream);
-            if (ce == cudaSuccess) ce = cudaStreamSynchronize(d.stream);
-            if (ce != cudaSuccess) rc = fail(ctx, FRT_ERR_CUDA, "frt_trace_rays: copy back failed: %s", cudaGetErrorString(ce));
-        }
-        cudaFree(dr);
-        cudaFree(dh);
-        if (rc != FRT_OK) return rc;
-        worst = std::max(worst, ms);
+        if (d.d_rays) { cudaFree(d.d_rays); d.d_rays = nullptr; }
+        if (d.d_hits) { cudaFree(d.d_hits); d.d_hits = nullptr; }
+        d.trace_cap = 0;
+        CU(cudaMalloc(&d.d_rays, m * sizeof(frt_ray)));
+        CU(cudaMalloc(&d.d_hits, m * sizeof(frt_hit)));
+        d.trace_cap = m;
+    }
+    cudaPointerAttributes pa_r{}, pa_h{};
+    const bool pinned = cudaPointerGetAttributes(&pa_r, rays) == cudaSuccess && pa_r.type == cudaMemoryTypeHost &&
+                        cudaPointerGetAttributes(&pa_h, hits) == cudaSuccess && pa_h.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    auto enqueue = [&](int i) {
+        Device &d = ctx->dev[i];
+        const size_t b = parts[i].b, m = parts[i].e - b;
+        if (m == 0) return;
+        if (cudaSetDevice(d.ordinal) != cudaSuccess || cudaMemcpyAsync(d.d_rays, rays + b, m * sizeof(frt_ray), cudaMemcpyHostToDevice, d.stream) != cudaSuccess)
+        { parts[i].rc = FRT_ERR_CUDA; return; }
+        parts[i].rc = frt_trace_rays_device(ctx, i, d.d_rays, m, d.d_hits, mode, nullptr);
+        if (parts[i].rc != FRT_OK) return;
+        if (cudaMemcpyAsync(hits + b, d.d_hits, m * sizeof(frt_hit), cudaMemcpyDeviceToHost, d.stream) != cudaSuccess) parts[i].rc = FRT_ERR_CUDA;
+        if (!pinned && cudaStreamSynchronize(d.stream) != cudaSuccess) parts[i].rc = FRT_ERR_CUDA;
+    };
+    if (pinned || nd == 1)
+        for (int i = 0; i < nd; ++i) enqueue(i);
+    else
+    {
+        std::vector<std::thread> workers;
+        for (int i = 1; i < nd; ++i) workers.emplace_back(enqueue, i);
+        enqueue(0);
+        for (std::thread &t : workers) t.join();
+    }
+    double worst = 0;
+    for (int i = 0; i < nd; ++i)
+    {
+        Device &d = ctx->dev[i];
+        if (parts[i].e == parts[i].b) continue;
+        if (parts[i].rc != FRT_OK) return parts[i].rc == FRT_ERR_CUDA ? fail(ctx, FRT_ERR_CUDA, "frt_trace_rays: device %d: %s", i, cudaGetErrorString(cudaGetLastError())) : parts[i].rc;
+        CU(cudaSetDevice(d.ordinal));
+        CU(cudaStreamSynchronize(d.stream));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, d.ev_t0, d.ev_t1));
+        worst = std::max<double>(worst, ms);
     }
     if (device_ms) *device_ms = worst;
     return FRT_OK;

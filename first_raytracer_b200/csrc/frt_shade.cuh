@@ -111,8 +111,7 @@ __device__ __forceinline__ void end_path(const KernelArgs &a, const PathPool &po
     pool.ray_d[slot].w = __uint_as_float(0u);
 }
 
-// One path vertex of slot `slot` of `pool` (global memory for the streamed pool, shared memory for
-// the CTA-resident pool): bit 0 of the result = the path ended here (splatted, slot dead), bit 1 =
+// One path vertex of slot `slot` of `pool` (the CTA's shared-memory pool): bit 0 of the result = the path ended here (splatted, slot dead), bit 1 =
 // a shadow ray was written to sh_a / sh_b / sh_c.  A dead slot returns 0.
 #define FRT_SHADE_TERMINATED 1u
 #define FRT_SHADE_SHADOW 2u
@@ -408,32 +407,4 @@ __device__ __forceinline__ unsigned int frt_shade_vertex(const KernelArgs &a, co
         }
         return (terminated ? FRT_SHADE_TERMINATED : 0u) | (want_shadow ? FRT_SHADE_SHADOW : 0u) |
                ((flags & FRT_FLAG_ALIVE) ? FRT_SHADE_WAS_ALIVE : 0u) | (origin_prim << FRT_SHADE_PRIM_SHIFT);
-}
-
-__global__ void __launch_bounds__(128) k_shade(const KernelArgs a, const int parity_out)
-{
-    const unsigned int n = a.pool.n_slots;
-    unsigned int nonfinite = 0;
-    int ended = 0;
-    const unsigned int n_round = (n + 31u) & ~31u;
-    for (unsigned int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n_round; slot += gridDim.x * blockDim.x)
-    {
-        const unsigned int r = slot < n ? frt_shade_vertex<false>(a, a.pool, slot, nonfinite) : 0u;
-        const bool terminated = r & FRT_SHADE_TERMINATED, want_shadow = r & FRT_SHADE_SHADOW;
-        // queue compaction: warp ballot + one atomic per warp per queue
-        const unsigned int qi = warp_append(want_shadow, &a.ctr->n_shadow);
-        if (want_shadow) a.pool.shadow_q[qi] = slot;
-        const unsigned int fi = warp_append(terminated, &a.ctr->n_free[parity_out]);
-        if (terminated) { a.pool.free_q[parity_out][fi] = slot; ++ended; }
-    }
-    for (int off = 16; off > 0; off >>= 1)
-    {
-        ended += __shfl_down_sync(0xFFFFFFFFu, ended, off);
-        nonfinite += __shfl_down_sync(0xFFFFFFFFu, nonfinite, off);
-    }
-    if (lane_id() == 0)
-    {
-        if (ended) atomicSub(&a.ctr->n_alive, ended);
-        if (nonfinite) atomicAdd(&a.ctr->nonfinite, (unsigned long long)nonfinite);
-    }
 }

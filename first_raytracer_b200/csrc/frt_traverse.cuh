@@ -16,7 +16,8 @@
 #pragma once
 #include "frt_device.cuh"
 
-#define FRT_STACK_SIZE 64 // 3 pushes per level: trees up to 21 levels deep
+#define FRT_STACK_SIZE 64 // 4-wide: 3 pushes per level, trees up to 21 levels deep
+#define FRT_STACK8_SIZE 96 // 8-wide: 7 pushes per level, trees up to 13 levels deep
 // Closest hit whose t, u, v are still the float32 estimate carries this bit in RayHit::prim; the
 // consumer (shade, with the whole warp converged) calls frt_resolve_hit before using them.
 #define FRT_HIT_INEXACT 0x20000000u
@@ -92,7 +93,7 @@ struct BestHit
 // to a leaf, test its primitives, pop the next postponed child), finish() gives the hit.  Splitting
 // the loop this way lets a persistent warp look at its lanes between rounds and hand finished
 // lanes a new ray (dynamic fetch) instead of idling until the slowest lane is done.
-template <bool ANY, bool COUNT>
+template <bool ANY, bool COUNT, int WIDE = 4>
 struct Walker
 {
     float3 o, d;
@@ -134,9 +135,10 @@ struct Walker
         active = sc.n_nodes != 0;
     }
 
-    __device__ __forceinline__ void round(const DevScene &sc, uint2 *stk, unsigned int &n_nodes, unsigned int &n_tris)
+    // ---- while-while, part 1 over the 4-wide nodes: descend through inner nodes (EMPTY carries the leaf bit and
+    // ends the loop)
+    __device__ __forceinline__ void descend4(const DevScene &sc, uint2 *stk, unsigned int &n_nodes)
     {
-        // ---- while-while, part 1: descend through inner nodes (EMPTY carries the leaf bit and ends the loop)
         while (!(cur & FRT_CHILD_LEAF))
         {
             // eight 128-bit loads, near/far planes picked by ray-direction sign
@@ -184,6 +186,92 @@ struct Walker
             if (k1 != 0xFFFFFFFFu) stk[sp++] = make_uint2(frt_pick(ch, k1 & 3u), k1 & ~3u);
             cur = (k0 != 0xFFFFFFFFu) ? frt_pick(ch, k0 & 3u) : FRT_CHILD_EMPTY;
         }
+    }
+
+    // ---- the same over the 8-wide compressed nodes of frt_wide8.cuh (96 B: box origin + per-axis power-of-two
+    // scale, 8 x 6 byte-quantised planes, 8 child references).  Plane k of an axis is origin + q * scale, so its
+    // slab distance is q * (scale / d) + (origin / d - o / d): one FFMA per plane after three per node.  The
+    // quantised boxes contain the float32 boxes of the 4-wide tree (floor / ceil), hits are decided by the same
+    // triangle code, so results do not depend on which tree is walked.
+    __device__ __forceinline__ void descend8(const DevScene &sc, uint2 *stk, unsigned int &n_nodes)
+    {
+        while (!(cur & FRT_CHILD_LEAF))
+        {
+            const uint4 *n = sc.nodes8 + 6 * (size_t)cur;
+            if (COUNT) ++n_nodes;
+            const uint4 hd = __ldg(n), qa = __ldg(n + 1), qb = __ldg(n + 2), qc = __ldg(n + 3);
+            const uint4 c0 = __ldg(n + 4), c1 = __ldg(n + 5);
+            const float sx_ = __uint_as_float((hd.w & 0xFFu) << 23) * idx, sy_ = __uint_as_float(((hd.w >> 8) & 0xFFu) << 23) * idy,
+                        sz_ = __uint_as_float(((hd.w >> 16) & 0xFFu) << 23) * idz;
+            const float ax = fmaf(__uint_as_float(hd.x), idx, -oox), ay = fmaf(__uint_as_float(hd.y), idy, -ooy),
+                        az = fmaf(__uint_as_float(hd.z), idz, -ooz);
+            // low / high plane bytes: x lo = qa.xy, y lo = qa.zw, z lo = qb.xy, x hi = qb.zw, y hi = qc.xy, z hi = qc.zw
+            const uint2 nxw = sx ? make_uint2(qb.z, qb.w) : make_uint2(qa.x, qa.y), fxw = sx ? make_uint2(qa.x, qa.y) : make_uint2(qb.z, qb.w);
+            const uint2 nyw = sy ? make_uint2(qc.x, qc.y) : make_uint2(qa.z, qa.w), fyw = sy ? make_uint2(qa.z, qa.w) : make_uint2(qc.x, qc.y);
+            const uint2 nzw = sz ? make_uint2(qc.z, qc.w) : make_uint2(qb.x, qb.y), fzw = sz ? make_uint2(qb.x, qb.y) : make_uint2(qc.z, qc.w);
+            uint32_t key[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+            {
+                const int sh = 8 * (k & 3);
+                const float qnx = (float)(((k < 4 ? nxw.x : nxw.y) >> sh) & 0xFFu), qfx = (float)(((k < 4 ? fxw.x : fxw.y) >> sh) & 0xFFu);
+                const float qny = (float)(((k < 4 ? nyw.x : nyw.y) >> sh) & 0xFFu), qfy = (float)(((k < 4 ? fyw.x : fyw.y) >> sh) & 0xFFu);
+                const float qnz = (float)(((k < 4 ? nzw.x : nzw.y) >> sh) & 0xFFu), qfz = (float)(((k < 4 ? fzw.x : fzw.y) >> sh) & 0xFFu);
+                const float tn = fmaxf(fmaxf(fmaf(qnx, sx_, ax), fmaf(qny, sy_, ay)), fmaxf(fmaf(qnz, sz_, az), tmin));
+                const float tf = fminf(fminf(fmaf(qfx, sx_, ax), fmaf(qfy, sy_, ay)), fminf(fmaf(qfz, sz_, az), tmax));
+                const uint32_t ref = k < 4 ? frt_pick(c0, k) : frt_pick(c1, k - 4);
+                // an empty slot stores inverted planes (255 / 0) AND the EMPTY reference: never entered
+                key[k] = (tf >= tn && ref != FRT_CHILD_EMPTY) ? ((__float_as_uint(tn) & ~7u) | (uint32_t)k) : 0xFFFFFFFFu;
+            }
+            if (ANY)
+            {
+                uint32_t next = FRT_CHILD_EMPTY;
+#pragma unroll
+                for (int k = 7; k >= 0; --k)
+                    if (key[k] != 0xFFFFFFFFu)
+                    {
+                        if (next != FRT_CHILD_EMPTY) stk[sp++] = make_uint2(next, 0u);
+                        next = k < 4 ? frt_pick(c0, k) : frt_pick(c1, k - 4);
+                    }
+                cur = next;
+                continue;
+            }
+            // sort the entered children near-to-far: 19-comparator network on tnear | slot keys
+#define FRT_CSWAP(i, j) { const uint32_t a_ = min(key[i], key[j]), b_ = max(key[i], key[j]); key[i] = a_; key[j] = b_; }
+            FRT_CSWAP(0, 1) FRT_CSWAP(2, 3) FRT_CSWAP(4, 5) FRT_CSWAP(6, 7)
+            FRT_CSWAP(0, 2) FRT_CSWAP(1, 3) FRT_CSWAP(4, 6) FRT_CSWAP(5, 7)
+            FRT_CSWAP(1, 2) FRT_CSWAP(5, 6) FRT_CSWAP(0, 4) FRT_CSWAP(3, 7)
+            FRT_CSWAP(1, 5) FRT_CSWAP(2, 6)
+            FRT_CSWAP(1, 4) FRT_CSWAP(3, 6)
+            FRT_CSWAP(2, 4) FRT_CSWAP(3, 5)
+            FRT_CSWAP(3, 4)
+#undef FRT_CSWAP
+            // invalid keys sort last: push the far ones (farthest first), continue with the nearest
+#pragma unroll
+            for (int j = 7; j >= 1; --j)
+                if (key[j] != 0xFFFFFFFFu)
+                {
+                    const uint32_t slot = key[j] & 7u;
+                    const uint32_t ref = slot < 4u ? frt_pick(c0, slot) : frt_pick(c1, slot - 4u);
+                    stk[sp++] = make_uint2(ref, key[j] & ~7u);
+                    // the node will be wanted when this entry is popped: pull it towards L2 now (latency, not bandwidth,
+                    // bounds a large incoherent scene)
+                    if (sc.prefetch && !(ref & FRT_CHILD_LEAF))
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(sc.nodes8 + 6 * (size_t)ref));
+                }
+            if (key[0] != 0xFFFFFFFFu)
+            {
+                const uint32_t slot = key[0] & 7u;
+                cur = slot < 4u ? frt_pick(c0, slot) : frt_pick(c1, slot - 4u);
+            }
+            else
+                cur = FRT_CHILD_EMPTY;
+        }
+    }
+
+    __device__ __forceinline__ void round(const DevScene &sc, uint2 *stk, unsigned int &n_nodes, unsigned int &n_tris)
+    {
+        if (WIDE == 8) descend8(sc, stk, n_nodes); else descend4(sc, stk, n_nodes);
 
         // ---- part 2: one leaf
         if (cur != FRT_CHILD_EMPTY)
@@ -268,7 +356,13 @@ struct Walker
                     else best.t = 0.5 * ((double)best.lo + (double)best.hi); // not reachable while the margins hold
                     best.exact = true;
                 }
-                const bool closer = is_sphere ? !(e.t > best.t) : (e.t < best.t || (e.t == best.t && prim < best.prim));
+                // Exact ties as the reference's visiting order decides them: a sphere accepts t <= t_max (sphere.h:41), a
+                // triangle only t < t_max (triangle.h:88-89), so at equal t a sphere beats a triangle whichever is met
+                // first, the later-met (higher leaf index) of two spheres stays, and the earlier-met of two triangles.
+                const bool best_none = best.prim == 0xFFFFFFFFu, best_sph = !best_none && (best.prim & FRT_CHILD_SPHERE);
+                const bool closer = e.t < best.t ||
+                                    (e.t == best.t && (is_sphere ? (best_none || !best_sph || prim > best.prim)
+                                                                 : (!best_none && !best_sph && prim < best.prim)));
                 if (closer)
                 {
                     best.prim = prim; best.t = e.t; best.exact = true; best.u = e.u; best.v = e.v;

@@ -26,7 +26,7 @@ struct WfShared
     unsigned int hist_ext[FRT_WF_BINS], hist_sh[FRT_WF_BINS]; // ray-origin bins: counts, then write offsets
     unsigned int hist_mat[8];                                 // shade order: miss + the six material types
     unsigned long long base; // first sample index of this iteration's run
-    unsigned int n_ext, n_free, n_shadow, n_new, cur_ext, cur_shadow, exhausted, pad;
+    unsigned int n_ext, n_free, n_shadow, n_new, cur_ext, cur_shadow, exhausted, cancelled;
 };
 
 __device__ __forceinline__ unsigned long long frt_globaltimer()
@@ -87,6 +87,39 @@ __device__ __forceinline__ void wf_trace_queue(const DevScene &sc, const PathPoo
     frt_persistent_trace<ANY, COUNT>(sc, io, n_items, cursor, refill_below, n_rays, n_nodes, n_tris);
 }
 
+// Statistics: one set of 64-bit atomics per warp; the per-thread counters restart from zero.
+template <bool COUNT>
+__device__ __forceinline__ void wf_flush_counters(Counters *ctr, unsigned int &n_closest, unsigned int &n_shadow_rays, unsigned int &n_started,
+                                                  unsigned int &nonfinite, unsigned int &n_nodes, unsigned int &n_tris)
+{
+    unsigned long long c = n_closest, s = n_shadow_rays, g = n_started, f = nonfinite, nn = n_nodes, nt = n_tris;
+    for (int off = 16; off > 0; off >>= 1)
+    {
+        c += __shfl_down_sync(0xFFFFFFFFu, c, off);
+        s += __shfl_down_sync(0xFFFFFFFFu, s, off);
+        g += __shfl_down_sync(0xFFFFFFFFu, g, off);
+        f += __shfl_down_sync(0xFFFFFFFFu, f, off);
+        if (COUNT)
+        {
+            nn += __shfl_down_sync(0xFFFFFFFFu, nn, off);
+            nt += __shfl_down_sync(0xFFFFFFFFu, nt, off);
+        }
+    }
+    if (lane_id() == 0)
+    {
+        if (c) atomicAdd(&ctr->closest_rays, c);
+        if (s) atomicAdd(&ctr->shadow_rays, s);
+        if (g) atomicAdd(&ctr->samples_started, g);
+        if (f) atomicAdd(&ctr->nonfinite, f);
+        if (COUNT)
+        {
+            atomicAdd(&ctr->node_visits, nn);
+            atomicAdd(&ctr->tri_tests, nt);
+        }
+    }
+    n_closest = n_shadow_rays = n_started = nonfinite = n_nodes = n_tris = 0;
+}
+
 // P = slots per CTA (a multiple of 32); refill_below = a warp fetches new rays once this many lanes or
 // fewer are still traversing.
 template <bool COUNT, int THREADS, int MIN_BLOCKS, bool OTHER>
@@ -101,7 +134,6 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelA
     lp.prev_p = lp.rad + P; lp.sh_a = lp.prev_p + P; lp.sh_b = lp.sh_a + P;
     lp.sh_c = reinterpret_cast<float *>(lp.sh_b + P);
     unsigned int *ext_q = reinterpret_cast<unsigned int *>(lp.sh_c + P), *free_q = ext_q + P, *shadow_q = free_q + P;
-    lp.free_q[0] = free_q; lp.free_q[1] = free_q; lp.shadow_q = shadow_q;
 
     const unsigned int tid = threadIdx.x;
     for (unsigned int i = tid; i < P; i += THREADS)
@@ -127,7 +159,11 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelA
         {
             const unsigned int want = sh.n_free;
             unsigned long long base = total;
-            if (want && !sh.exhausted)
+            // frt_cancel (viewer::to_exit, viewer.cpp:101-104; path.cpp:127 leaves its row loop): polled once per
+            // CTA iteration; a cancelled tile takes no more samples and drops the paths in flight
+            const bool cancelled = *a.cancel != 0;
+            sh.cancelled = cancelled;
+            if (want && !sh.exhausted && !cancelled)
             {
                 base = atomicAdd(&a.ctr->next_sample, (unsigned long long)want);
                 if (base + want >= total) sh.exhausted = 1;
@@ -137,6 +173,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelA
             sh.cur_ext = 0; sh.cur_shadow = 0;
         }
         __syncthreads();
+        if (sh.cancelled) break;
         const unsigned int n_new = sh.n_new, n_bounce = sh.n_ext, n_sh = sh.n_shadow;
         const unsigned long long base = sh.base;
         for (unsigned int i = tid; i < n_new; i += THREADS)
@@ -292,33 +329,11 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelA
         __syncthreads();
         if (tid == 0) { const unsigned long long t = frt_globaltimer(); t_shade += t - t0; t0 = t; }
         ++n_iter;
+        // the per-thread counters are 32-bit: fold them into the 64-bit device counters long before they can wrap
+        if ((n_iter & 0xFFFFu) == 0u) wf_flush_counters<COUNT>(a.ctr, n_closest, n_shadow_rays, n_started, nonfinite, n_nodes, n_tris);
     }
 
-    // ---- statistics: one set of atomics per warp ------------------------------------------------
-    for (int off = 16; off > 0; off >>= 1)
-    {
-        n_closest += __shfl_down_sync(0xFFFFFFFFu, n_closest, off);
-        n_shadow_rays += __shfl_down_sync(0xFFFFFFFFu, n_shadow_rays, off);
-        n_started += __shfl_down_sync(0xFFFFFFFFu, n_started, off);
-        nonfinite += __shfl_down_sync(0xFFFFFFFFu, nonfinite, off);
-        if (COUNT)
-        {
-            n_nodes += __shfl_down_sync(0xFFFFFFFFu, n_nodes, off);
-            n_tris += __shfl_down_sync(0xFFFFFFFFu, n_tris, off);
-        }
-    }
-    if (lane_id() == 0)
-    {
-        if (n_closest) atomicAdd(&a.ctr->closest_rays, (unsigned long long)n_closest);
-        if (n_shadow_rays) atomicAdd(&a.ctr->shadow_rays, (unsigned long long)n_shadow_rays);
-        if (n_started) atomicAdd(&a.ctr->samples_started, (unsigned long long)n_started);
-        if (nonfinite) atomicAdd(&a.ctr->nonfinite, (unsigned long long)nonfinite);
-        if (COUNT)
-        {
-            atomicAdd(&a.ctr->node_visits, (unsigned long long)n_nodes);
-            atomicAdd(&a.ctr->tri_tests, (unsigned long long)n_tris);
-        }
-    }
+    wf_flush_counters<COUNT>(a.ctr, n_closest, n_shadow_rays, n_started, nonfinite, n_nodes, n_tris);
     if (tid == 0)
     {
         atomicAdd(&a.ctr->stage_ns[0], t_gen);

@@ -22,7 +22,7 @@ struct Vector3f
     Vector3f operator-() const { return {-e[0], -e[1], -e[2]}; }
     Vector3f &operator+=(const Vector3f &o) { e[0] += o.e[0]; e[1] += o.e[1]; e[2] += o.e[2]; return *this; }
     Vector3f &operator*=(double s) { e[0] *= s; e[1] *= s; e[2] *= s; return *this; }
-    Vector3f &operator/=(double s) { e[0] /= s; e[1] /= s; e[2] /= s; return *this; }
+    Vector3f &operator/=(double s) { const double k = 1.0 / s; e[0] *= k; e[1] *= k; e[2] *= k; return *this; } // geometry.h:533-538: by the reciprocal
     double squared_length() const { return e[0] * e[0] + e[1] * e[1] + e[2] * e[2]; }
     double length() const { return std::sqrt(squared_length()); }
 };

@@ -35,6 +35,8 @@ struct gpu_path_integrator
     uint32_t spp_begin = 0;
     const std::vector<float> *resume_sums = nullptr;
     std::vector<float> *film_sums_out = nullptr;
+    float *mean_rgb_out = nullptr; // optional float32 copy of the mean image (nx * ny * 3, row 0 = bottom)
+    bool cancelled = false;        // the last render was stopped by viewer::to_exit
     frt_stats stats{};
     const std::unordered_map<const hitable *, int> *prim_ids = nullptr;
 
@@ -96,6 +98,7 @@ private:
             std::fprintf(stderr, "[frt host] %-10s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_prev).count());
             t_prev = now;
         };
+        cancelled = false;
         frt_flattener flattener(prim_ids, max_leaf);
         const frt_flat_scene flat = flattener.flatten(scene);
         const frt_scene_desc desc = flat.desc();
@@ -117,33 +120,34 @@ private:
         lap("upload");
         check(ctx, frt_render_tile(ctx, &tile), "frt_render_tile");
         lap("launch");
-        std::vector<float> sums((size_t)film->nx * film->ny * 3);
-        check(ctx, frt_readback(ctx, sums.data(), sums.size(), &stats), "frt_readback");
+        // viewer::to_exit (set by the window's close button, viewer.cpp:101-104) is what path.cpp:127 polls per row:
+        // here the host watches it while the tile runs and forwards it to the device (frt_cancel), so a render
+        // of any length stops within milliseconds
+        for (;;)
+        {
+            int done = 0;
+            check(ctx, frt_poll(ctx, &done), "frt_poll");
+            if (done) break;
+            if (film->to_exit) { check(ctx, frt_cancel(ctx), "frt_cancel"); cancelled = true; break; }
+            std::this_thread::sleep_for(std::chrono::microseconds(200));
+        }
+        // path.cpp:143 / viewer.cpp:109-132 for every pixel at once: the film's mean goes to viewer::fout_image, the
+        // tone-mapped bytes (computed on the device, in double like the reference) to viewer::out_image; with
+        // film_sums_out the raw sums are fetched as well (checkpoints)
+        if (film_sums_out)
+        {
+            film_sums_out->resize((size_t)film->nx * film->ny * 3);
+            check(ctx, frt_readback(ctx, film_sums_out->data(), film_sums_out->size(), nullptr), "frt_readback");
+        }
+        check(ctx, frt_readback_film(ctx, (uint64_t)film->ns, film->fout_image.get(), film->out_image.get(), mean_rgb_out, &stats), "frt_readback_film");
         lap("readback");
-        if (film_sums_out) *film_sums_out = sums;
         give_back(ctx, n_gpus);
-        // path.cpp:143 / viewer.cpp:109-132: the film divides the sum by ns and tonemaps.  As in the
-        // reference every pixel is written by exactly one thread; rows are dealt to the host cores
-        // (the per-pixel pow/exp of the tonemap is ~0.1 s for a 1080p film on one core).
-        const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-        const int n_workers = (int)std::min<unsigned>(hw, (unsigned)std::max(1, film->ny / 16));
-        auto feed = [&](int w) {
-            for (int y = w; y < film->ny; y += n_workers)
-                for (int x = 0; x < film->nx; ++x)
-                {
-                    const float *p = &sums[((size_t)y * film->nx + x) * 3];
-                    Vector3f col(p[0], p[1], p[2]);
-                    film->add_sample(Vector2i(x, y), col);
-                }
-        };
-        std::vector<std::thread> workers;
-        for (int w = 1; w < n_workers; ++w) workers.emplace_back(feed, w);
-        feed(0);
-        for (std::thread &t : workers) t.join();
-        lap("film");
-        Scene::num_rays_traversed = (unsigned int)(stats.closest_rays + stats.shadow_rays);
-        Scene::num_ray_box_intersections = (unsigned int)stats.node_visits;
-        Scene::num_ray_tri_intersections = (unsigned int)stats.tri_tests;
+        // the reference's statistics block reads these 32-bit statics (integrator.h:33-43); a 1080p x 1024 spp frame
+        // traces 1.4e10 rays, so they saturate instead of wrapping and `stats` (64-bit) is what the renderer prints
+        auto sat = [](uint64_t v) { return (unsigned int)std::min<uint64_t>(v, 0xFFFFFFFFull); };
+        Scene::num_rays_traversed = sat(stats.closest_rays + stats.shadow_rays);
+        Scene::num_ray_box_intersections = sat(stats.node_visits);
+        Scene::num_ray_tri_intersections = sat(stats.tri_tests);
     }
 };
 

@@ -6,6 +6,7 @@
 #include <chrono>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <string>
 #include "fast_bvh.h"
 #include "gpu_path_integrator.h"
@@ -152,6 +153,23 @@ int frth_camera_rays(const frth_scene *s, int nx, int ny, frt_ray *out)
     return FRT_OK;
 }
 
+// The film of the render in flight (frth_cancel sets its to_exit, what the window's close button does in the
+// reference, viewer.cpp:101-104) and a film kept between renders of one size: constructing a viewer zero-fills
+// 56 MB at 1080p (viewer.cpp:10-16), more than the device needs to copy a finished frame back.
+namespace {
+std::mutex g_film_mutex;
+viewer *g_rendering = nullptr;
+std::unique_ptr<viewer> g_film_cache;
+}
+
+int frth_cancel(void)
+{
+    std::lock_guard<std::mutex> lock(g_film_mutex);
+    if (!g_rendering) return FRT_ERR_STATE;
+    g_rendering->to_exit = true;
+    return FRT_OK;
+}
+
 int frth_render(frth_scene *s, int n_gpus, int nx, int ny, uint32_t ns, uint32_t seed, uint32_t flags, float *rgb_mean,
                 frt_stats *stats, double *wall_seconds)
 {
@@ -159,7 +177,13 @@ int frth_render(frth_scene *s, int n_gpus, int nx, int ny, uint32_t ns, uint32_t
     if (!s->scene) { g_error = "frth_render: scene was built by frth_bvh4_build (ray casting only)"; return FRT_ERR_STATE; }
     try
     {
-        viewer film(nx, ny, ns, 3);
+        std::unique_ptr<viewer> film;
+        {
+            std::lock_guard<std::mutex> lock(g_film_mutex);
+            if (g_film_cache && g_film_cache->nx == nx && g_film_cache->ny == ny && g_film_cache->ns == ns) film = std::move(g_film_cache);
+        }
+        if (!film) film.reset(new viewer(nx, ny, ns, 3));
+        film->to_exit = false;
         renderer<gpu_path_integrator> render;
         render.n_gpus = n_gpus;
         render.seed = seed;
@@ -167,25 +191,26 @@ int frth_render(frth_scene *s, int n_gpus, int nx, int ny, uint32_t ns, uint32_t
         render.integrator = (flags >> 8) & 0xFFu; // FRTH_RENDER_* in frt_host.h
         render.max_leaf = s->max_leaf;
         render.prim_ids = &s->ids.id;
-        const double secs = render.Render(s->scene.get(), film);
-        if (rgb_mean)
-        {
-            // viewer::fout_image (double) -> caller's float32 buffer, dealt to the host cores
-            const size_t n = (size_t)nx * ny * 3;
-            const unsigned n_workers = std::max(1u, std::min(std::thread::hardware_concurrency(), (unsigned)(n >> 18) + 1u));
-            auto convert = [&](unsigned w) {
-                for (size_t i = n * w / n_workers, e = n * (w + 1) / n_workers; i < e; ++i) rgb_mean[i] = (float)film.fout_image[i];
-            };
-            std::vector<std::thread> workers;
-            for (unsigned w = 1; w < n_workers; ++w) workers.emplace_back(convert, w);
-            convert(0);
-            for (std::thread &t : workers) t.join();
-        }
+        render.mean_rgb_out = rgb_mean; // viewer::fout_image as float32, written by frt_readback_film beside the film
+        { std::lock_guard<std::mutex> lock(g_film_mutex); g_rendering = film.get(); }
+        double secs = 0;
+        try { secs = render.Render(s->scene.get(), *film); }
+        catch (...) { std::lock_guard<std::mutex> lock(g_film_mutex); g_rendering = nullptr; throw; }
+        { std::lock_guard<std::mutex> lock(g_film_mutex); g_rendering = nullptr; g_film_cache = std::move(film); }
         if (stats) *stats = render.stats;
         if (wall_seconds) *wall_seconds = secs;
-        return FRT_OK;
+        return render.cancelled ? FRTH_CANCELLED : FRT_OK;
     }
     catch (const std::exception &e) { g_error = e.what(); return FRT_ERR_CUDA; }
+}
+
+// viewer::out_image of the last frth_render (the 8-bit tone-mapped film, viewer.cpp:117-125): nx * ny * 3 bytes
+int frth_last_ldr(unsigned char *out, size_t n_bytes)
+{
+    std::lock_guard<std::mutex> lock(g_film_mutex);
+    if (!g_film_cache || !out || n_bytes != (size_t)g_film_cache->nx * g_film_cache->ny * 3) return FRT_ERR_STATE;
+    std::memcpy(out, g_film_cache->out_image.get(), n_bytes);
+    return FRT_OK;
 }
 
 } // extern "C"

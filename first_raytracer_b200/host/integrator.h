@@ -14,6 +14,16 @@
 template <typename integrator>
 struct renderer : public integrator
 {
+private:
+    // integrators with a `stats` member (frt_stats, 64-bit) vs. the reference's own (32-bit statics of Scene)
+    template <class I> static auto ray_count(I *i) -> decltype((unsigned long long)i->stats.closest_rays) { return i->stats.closest_rays + i->stats.shadow_rays; }
+    static unsigned long long ray_count(...) { return Scene::num_rays_traversed; }
+    template <class I> static auto box_count(I *i) -> decltype((unsigned long long)i->stats.node_visits) { return i->stats.node_visits; }
+    static unsigned long long box_count(...) { return Scene::num_ray_box_intersections; }
+    template <class I> static auto tri_count(I *i) -> decltype((unsigned long long)i->stats.tri_tests) { return i->stats.tri_tests; }
+    static unsigned long long tri_count(...) { return Scene::num_ray_tri_intersections; }
+
+public:
     double Render(Scene *scene, viewer &film_viewer)
     {
         GLFWwindow *window = film_viewer.init();
@@ -29,12 +39,15 @@ struct renderer : public integrator
         const auto t2 = std::chrono::high_resolution_clock::now();
         const double secs = std::chrono::duration<double>(t2 - t1).count();
         std::cout << "\nIt took me " << secs << " seconds to render." << std::endl;
-        std::cout << "\n Number of ray traversals: " << Scene::num_rays_traversed;
-        std::cout << "\n Number of ray-box intersections: " << Scene::num_ray_box_intersections;
-        std::cout << "\n Number of ray-triangle intersections: " << Scene::num_ray_tri_intersections;
+        // the reference prints its 32-bit atomics here; a GPU frame overflows them (1.4e10 rays at 1080p x 1024 spp),
+        // so integrators that carry 64-bit device counters (frt_stats) are printed from those
+        const unsigned long long rays = ray_count(this), boxes = box_count(this), tris = tri_count(this);
+        std::cout << "\n Number of ray traversals: " << rays;
+        std::cout << "\n Number of ray-box intersections: " << boxes;
+        std::cout << "\n Number of ray-triangle intersections: " << tris;
         std::cout << "\n Number of BVH nodes: " << Scene::num_bvh_nodes;
         std::cout << "\n Number of BVH leaves: " << Scene::num_bvh_leaf_nodes;
-        std::cout << "\n Rays/second: " << (Scene::num_rays_traversed / secs) / 1e+6 << "M/sec" << std::endl;
+        std::cout << "\n Rays/second: " << ((double)rays / secs) / 1e+6 << "M/sec" << std::endl;
         return secs;
     }
 };

@@ -19,24 +19,39 @@
 
 namespace
 {
-struct ckpt_header { char magic[8]; uint32_t nx, ny, spp_done, seed; };
+// Film checkpoint, version 2: besides the film size and the samples it holds, everything that decides WHICH estimator
+// those samples came from — scene (FNV-1a hash of its name), integrator, depth cap — so that --resume cannot add
+// samples of another scene / integrator onto saved sums.
+struct ckpt_header { char magic[8]; uint32_t nx, ny, spp_done, seed; uint32_t version, integrator, max_depth, scene_hash; };
 
-void write_checkpoint(const std::string &path, int nx, int ny, uint32_t spp_done, uint32_t seed, const std::vector<float> &sums)
+uint32_t fnv1a(const std::string &s)
 {
-    ckpt_header h{{'F', 'R', 'T', 'C', 'K', 'P', 'T', '1'}, (uint32_t)nx, (uint32_t)ny, spp_done, seed};
+    uint32_t h = 2166136261u;
+    for (unsigned char c : s) { h ^= c; h *= 16777619u; }
+    return h;
+}
+
+void write_checkpoint(const std::string &path, int nx, int ny, uint32_t spp_done, uint32_t seed, uint32_t integrator, uint32_t max_depth,
+                      const std::string &scene, const std::vector<float> &sums)
+{
+    ckpt_header h{{'F', 'R', 'T', 'C', 'K', 'P', 'T', '2'}, (uint32_t)nx, (uint32_t)ny, spp_done, seed, 2u, integrator, max_depth, fnv1a(scene)};
     std::ofstream f(path, std::ios::binary);
     f.write((const char *)&h, sizeof h);
     f.write((const char *)sums.data(), (std::streamsize)(sums.size() * sizeof(float)));
     if (!f) throw std::runtime_error("cannot write checkpoint " + path);
 }
 
-ckpt_header read_checkpoint(const std::string &path, int nx, int ny, std::vector<float> &sums)
+ckpt_header read_checkpoint(const std::string &path, int nx, int ny, uint32_t integrator, uint32_t max_depth, const std::string &scene,
+                            std::vector<float> &sums)
 {
     ckpt_header h{};
     std::ifstream f(path, std::ios::binary);
     f.read((char *)&h, sizeof h);
-    if (!f || std::memcmp(h.magic, "FRTCKPT1", 8) != 0) throw std::runtime_error("not a film checkpoint: " + path);
+    if (!f || std::memcmp(h.magic, "FRTCKPT2", 8) != 0 || h.version != 2u) throw std::runtime_error("not a version-2 film checkpoint: " + path);
     if ((int)h.nx != nx || (int)h.ny != ny) throw std::runtime_error("checkpoint resolution differs from --res");
+    if (h.scene_hash != fnv1a(scene)) throw std::runtime_error("checkpoint was rendered from another --scene");
+    if (h.integrator != integrator) throw std::runtime_error("checkpoint was rendered by another --integrator");
+    if (h.max_depth != max_depth) throw std::runtime_error("checkpoint was rendered with another depth cap");
     sums.resize((size_t)nx * ny * 3);
     f.read((char *)sums.data(), (std::streamsize)(sums.size() * sizeof(float)));
     if (!f) throw std::runtime_error("truncated checkpoint " + path);
@@ -93,20 +108,20 @@ int main(int argc, const char **argv)
         std::vector<float> resume_sums, final_sums;
         if (!resume.empty())
         {
-            const ckpt_header h = read_checkpoint(resume, nx, ny, resume_sums);
+            const ckpt_header h = read_checkpoint(resume, nx, ny, li, render.max_depth, scene_name, resume_sums);
             if (h.spp_done > ns) throw std::runtime_error("checkpoint already holds more samples than --ns");
             render.seed = h.seed;
             render.spp_begin = h.spp_done;
             render.resume_sums = &resume_sums;
             std::cout << "\nResuming at sample " << h.spp_done << " of " << ns << " (seed " << h.seed << ")";
         }
-        render.film_sums_out = &final_sums;
+        if (!checkpoint.empty()) render.film_sums_out = &final_sums;
         const double render_time = render.Render(scene.get(), film_viewer);
         const frt_stats &st = render.stats;
         std::cout << " GPU: " << st.samples << " samples, " << st.closest_rays << " closest + " << st.shadow_rays
                   << " shadow rays in " << st.render_ms << " ms device time = "
                   << (st.closest_rays + st.shadow_rays) / (st.render_ms * 1e3) << " Mrays/s" << std::endl;
-        if (!checkpoint.empty()) write_checkpoint(checkpoint, nx, ny, (uint32_t)ns, render.seed, final_sums);
+        if (!checkpoint.empty()) write_checkpoint(checkpoint, nx, ny, (uint32_t)ns, render.seed, li, render.max_depth, scene_name, final_sums);
         film_viewer.save_and_destroy(out + "_" + std::to_string(render_time) + "s");
         gpu_path_integrator::release_cached_context();
     }

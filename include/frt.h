@@ -177,7 +177,7 @@ typedef struct frt_tile {
 } frt_tile;
 
 typedef struct frt_stats {
-    uint64_t samples;        /* camera paths started */
+    uint64_t samples;        /* camera paths started (all counters are 64-bit: a 1080p x 1024 spp frame traces 1.4e10 rays) */
     uint64_t closest_rays;   /* world->hit(r, EPSILON, FLT_MAX) equivalents, path.cpp:10 */
     uint64_t shadow_rays;    /* world->hit(shadow_ray, EPSILON, 1-SHADOW_EPSILON), path.cpp:50 */
     uint64_t node_visits;    /* wide-node fetches (0 unless counters enabled) */
@@ -185,8 +185,7 @@ typedef struct frt_stats {
     uint64_t iterations;     /* wavefront iterations */
     uint64_t kernel_launches;
     double render_ms;        /* device time between first and last kernel, max over devices */
-    double extend_ms, shade_ms, connect_ms, generate_ms; /* per stage: mean over CTAs (CTA-resident pool), or
-                                                            CUDA events with FRT_FLAG_KERNEL_TIMERS (streamed pool) */
+    double extend_ms, shade_ms, connect_ms, generate_ms; /* per stage of the persistent kernel: mean over its CTAs */
 } frt_stats;
 
 typedef struct frt_ray { float ox, oy, oz, dx, dy, dz; } frt_ray; /* ray.h:6-17, d not normalised */
@@ -195,11 +194,8 @@ typedef struct frt_hit {
     int32_t prim_id;  /* creation-order primitive id, -1 = miss */
 } frt_hit;
 
-#define FRT_FLAG_COUNTERS 1u      /* count node visits / triangle tests (slower) */
-#define FRT_FLAG_KERNEL_TIMERS 2u /* streamed pool only: per-kernel CUDA-event timing (serialises the loop) */
-#define FRT_FLAG_STREAMED_POOL 4u /* path state in a global-memory pool, four kernels per wavefront iteration
-                                     (the first implementation, kept for A/B measurements); default is the
-                                     CTA-resident pool: one persistent kernel, path state in shared memory */
+#define FRT_FLAG_COUNTERS 1u /* count node visits / triangle tests (slower); bits 1 and 2 belonged to the round-1
+                                global-memory path pool, which is gone: frt_set_flags rejects them */
 
 /* Create a context on `n` CUDA devices (ordinals in `devices`, NULL = device 0..n-1). */
 FRT_API int frt_create(frt_ctx **out, const int *devices, int n);
@@ -219,9 +215,29 @@ FRT_API int frt_render_tile(frt_ctx *ctx, const frt_tile *tile);
 FRT_API int frt_clear_film(frt_ctx *ctx);
 
 /* Replaces viewer::add_sample's store (viewer.cpp:109-132): waits for rendering, sums the
- * per-device films on device 0, copies nx*ny*3 float32 radiance SUMS (row 0 = bottom) to
- * `rgb_sum` (may be NULL to only synchronise) and fills `stats` (may be NULL). */
+ * per-device films into device 0's, copies nx*ny*3 float32 radiance SUMS (row 0 = bottom) to
+ * `rgb_sum` (may be NULL to only synchronise) and fills `stats` (may be NULL).
+ * The sum over the context's devices is a reduce-scatter over peer memory (device g adds range g of every film with
+ * NVLink loads and stores it into device 0's film), NOT an NCCL call: libfrt.so links no NCCL.  BASELINE.json's "one
+ * NCCL reduce" is what a one-process-per-GPU launcher does between frt_film_device_ptr and frt_readback (bench.py
+ * under torchrun does); both give the same film. */
 FRT_API int frt_readback(frt_ctx *ctx, float *rgb_sum, size_t n_floats, frt_stats *stats);
+
+/* The same wait + sum, then the whole of viewer::add_sample for every pixel (viewer.cpp:109-132) instead of one call
+ * per pixel from path.cpp:143: mean c = sum * (1 / ns) to fout_image (double, the viewer's own buffer) and / or
+ * mean_rgb (float32); out_image = (GLubyte) int(pow(1 - exp(-c), 1 / 2.2) * 255 + .5), evaluated in double on
+ * device 0.  Each of the three outputs may be NULL; nx*ny*3 elements, row 0 = bottom. */
+FRT_API int frt_readback_film(frt_ctx *ctx, uint64_t ns, double *fout_image, unsigned char *out_image, float *mean_rgb,
+                              frt_stats *stats);
+
+/* viewer::to_exit (viewer.cpp:101-104), which path.cpp:127 polls per row: the tiles launched so far stop taking
+ * samples and drop their paths in flight (each CTA looks at the flag once per wavefront iteration); frt_readback
+ * then returns within milliseconds with what the film holds.  The next frt_render_tile clears the request.
+ * Callable from any thread while another one is inside frt_readback / frt_poll. */
+FRT_API int frt_cancel(frt_ctx *ctx);
+/* Non-blocking: *done = 1 when every tile launched so far has finished on every device (what a caller polls while
+ * it watches viewer::to_exit). */
+FRT_API int frt_poll(frt_ctx *ctx, int *done);
 
 /* Resume: load radiance SUMS saved from an earlier frt_readback (nx*ny*3 float32, row 0 =
  * bottom) as the film's starting state, so that rendering the remaining sample range continues an interrupted
@@ -241,15 +257,31 @@ FRT_API int frt_film_device_ptr(frt_ctx *ctx, int dev, void **ptr, size_t *n_flo
  * bracket calls with its own events or enqueue a collective behind the render. */
 FRT_API int frt_stream_handle(frt_ctx *ctx, int dev, void **stream);
 
-/* Test / ray-cast entry: what scene->world->hit(r, EPSILON, FLT_MAX, rec) (any_hit = 0,
- * path.cpp:10) or world->hit(r, EPSILON, 1 - SHADOW_EPSILON, rec) (any_hit = 1, path.cpp:50;
- * only prim_id >= 0 / -1 is meaningful) return for each ray.  Host buffers; rays are block-
- * partitioned over the devices.  `device_ms` (may be NULL) = kernel time, max over devices. */
-FRT_API int frt_trace_rays(frt_ctx *ctx, const frt_ray *rays, size_t n, frt_hit *hits, int any_hit, double *device_ms);
+/* Test / ray-cast entry: what scene->world->hit(r, EPSILON, FLT_MAX, rec) (mode 0, path.cpp:10) or
+ * world->hit(r, EPSILON, 1 - SHADOW_EPSILON, rec) (FRT_TRACE_ANY_HIT, path.cpp:50; only prim_id >= 0 / -1 is
+ * meaningful) return for each ray.  Host buffers; the rays are block-partitioned over the context's devices, which
+ * copy, trace and copy back AT THE SAME TIME (per-device streams and ctx-owned device buffers that persist between
+ * calls).  Buffers from frt_host_alloc (or any pinned memory) are copied asynchronously at link speed; pageable ones
+ * go through one host thread per device.  FRT_TRACE_SORT: the rays are first put in Morton order of (origin cell,
+ * direction octant) by a device radix sort — only the order they are traced in changes, every hit lands at its ray's
+ * index.  `device_ms` (may be NULL) = sort + kernel time, max over devices.  Scenes of >= 65 536 triangles are walked
+ * over 8-wide compressed nodes derived at upload (same hits; FRT_WIDE8=0/1 forces the choice). */
+#define FRT_TRACE_ANY_HIT 1
+#define FRT_TRACE_SORT 2
+FRT_API int frt_trace_rays(frt_ctx *ctx, const frt_ray *rays, size_t n, frt_hit *hits, int mode, double *device_ms);
 
-/* Same on device-resident buffers of device `dev` (bench: inputs already in HBM). */
-FRT_API int frt_trace_rays_device(frt_ctx *ctx, int dev, const void *d_rays, size_t n, void *d_hits, int any_hit,
+/* Same on device-resident buffers of device `dev` (bench: inputs already in HBM).  device_ms == NULL: asynchronous
+ * on the device's stream (frt_stream_handle). */
+FRT_API int frt_trace_rays_device(frt_ctx *ctx, int dev, const void *d_rays, size_t n, void *d_hits, int mode,
                           double *device_ms);
+
+/* Pinned host memory for ray / hit / film buffers (cudaHostAlloc, portable); NULL on failure. */
+FRT_API void *frt_host_alloc(size_t bytes);
+FRT_API void frt_host_free(void *p);
+
+/* Host utility (no device needed): the 8-wide compressed nodes frt_upload_scene derives from `scene->nodes` for large
+ * scenes (24 uint32 words per node, layout in csrc/frt_wide8.cuh).  words may be NULL to only count. */
+FRT_API int frt_build_wide8(const frt_scene_desc *scene, uint32_t *words, size_t cap_words, uint32_t *n_nodes8, int *depth);
 
 #ifdef __cplusplus
 }

@@ -21,7 +21,8 @@ typedef struct frth_info {
 } frth_info;
 
 FRT_API const char *frth_last_error(void);
-/* name: cornell | cornell_glossy | cornell_sphere | veach | teapot | soup:<N>; assets are read
+/* name: cornell | cornell_glossy | cornell_sphere | cornell_metal | cornell_lens | veach | veach_beckmann | teapot |
+ * textured | soup:<N>, optionally followed by +sky or +hdr (environment); assets are read
  * from $FRT_ASSETS (default ./assets).  max_leaf = triangles per wide-BVH leaf (1..16). */
 FRT_API int frth_scene_create(const char *name, double aspect, int max_leaf, frth_scene **out);
 /* Triangle soup given as n*9 floats (v0,v1,v2). */
@@ -44,6 +45,13 @@ FRT_API int frth_camera_rays(const frth_scene *s, int nx, int ny, frt_ray *out);
 #define FRTH_RENDER_DIRECT (FRT_INTEGRATOR_DIRECT << 8)   /* or into `flags`: renderer<gpu_ass_1_integrator> */
 FRT_API int frth_render(frth_scene *s, int n_gpus, int nx, int ny, uint32_t ns, uint32_t seed, uint32_t flags,
                         float *rgb_mean, frt_stats *stats, double *wall_seconds);
+/* What closing the preview window does in the reference (viewer.cpp:101-104 sets viewer::to_exit, path.cpp:127 polls
+ * it): stops the frth_render in flight on another thread, which then returns FRTH_CANCELLED with a partial film.
+ * FRT_ERR_STATE when nothing is rendering. */
+#define FRTH_CANCELLED 1
+FRT_API int frth_cancel(void);
+/* viewer::out_image of the last frth_render: the 8-bit tone-mapped film (viewer.cpp:117-125), nx*ny*3 bytes. */
+FRT_API int frth_last_ldr(unsigned char *out, size_t n_bytes);
 
 #ifdef __cplusplus
 }

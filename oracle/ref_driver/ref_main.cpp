@@ -40,6 +40,14 @@
 #include "assignment_1.hpp"
 #include "debug_renderer.h"
 
+#ifdef FRT_DROPIN
+// The drop-in build: the product's integrator and flattener compiled against the REFERENCE's own headers
+// (Scene.h, triangle.h, material.h, texture.h, integrator.h ...), the way a maintainer of the reference would add
+// them: renderer<gpu_path_integrator> is the reference's renderer<> (integrator.h:11-47).
+#define FRT_WITH_REFERENCE_HEADERS
+#include "../../first_raytracer_b200/host/gpu_path_integrator.h"
+#endif
+
 static std::string g_assets = "assets";
 
 // ------------------------------------------------------------------------------------------
@@ -745,6 +753,90 @@ static int cmd_bsdf(int argc, char **argv)
     return 0;
 }
 
+#ifdef FRT_DROPIN
+// frt_dropin flatten <scene> <aspect> <max_leaf> <out.bin>: the frt_scene_desc arrays the flattener produces when it
+// walks the REFERENCE's Scene (real parallel_bvh_node / triangle / material / texture objects), one after the other:
+// header of 16 uint32 (counts), then nodes, tris, tri_normals, spheres, materials, lights, camera, env, textures,
+// tex_texels, tri_uv.  tests/test_host.py compares them byte for byte with the host layer's own.
+static int cmd_flatten(int argc, char **argv)
+{
+    if (argc < 6) return 2;
+    built_scene &b = build_scene(argv[2], std::atof(argv[3]));
+    std::unordered_map<const hitable *, int> ids;
+    for (size_t i = 0; i < b.creation_order.size(); ++i) ids[b.creation_order[i]] = (int)i;
+    frt_flattener fl(&ids, std::atoi(argv[4]));
+    const frt_flat_scene flat = fl.flatten(b.scene.get());
+    const frt_scene_desc d = flat.desc();
+    std::ofstream os(argv[5], std::ios::binary | std::ios::trunc);
+    const uint32_t head[16] = {d.n_nodes, d.n_tris, d.n_spheres, d.n_materials, d.n_lights, d.tri_normals ? 1u : 0u, d.env_image ? 1u : 0u,
+                               d.env_nx, d.env_ny, d.n_textures, (uint32_t)d.n_texels, d.tri_uv ? 1u : 0u, 0, 0, 0, 0};
+    os.write((const char *)head, sizeof head);
+    os.write((const char *)d.nodes, sizeof(frt_bvh4_node) * (size_t)d.n_nodes);
+    os.write((const char *)d.tris, sizeof(frt_float4) * 3 * (size_t)d.n_tris);
+    if (d.tri_normals) os.write((const char *)d.tri_normals, sizeof(frt_float4) * 3 * (size_t)d.n_tris);
+    os.write((const char *)d.spheres, sizeof(frt_sphere) * (size_t)d.n_spheres);
+    os.write((const char *)d.materials, sizeof(frt_material) * (size_t)d.n_materials);
+    os.write((const char *)d.lights, sizeof(frt_light) * (size_t)d.n_lights);
+    os.write((const char *)&d.camera, sizeof d.camera);
+    os.write((const char *)d.env_color, sizeof d.env_color);
+    os.write((const char *)&d.ao_t_max, sizeof d.ao_t_max);
+    os.write((const char *)d.textures, sizeof(frt_texture) * (size_t)d.n_textures);
+    os.write((const char *)d.tex_texels, sizeof(float) * 3 * (size_t)d.n_texels);
+    if (d.tri_uv) os.write((const char *)d.tri_uv, sizeof(float) * 6 * (size_t)d.n_tris);
+    std::printf("{\"cmd\": \"flatten\", \"n_nodes\": %u, \"n_tris\": %u, \"n_spheres\": %u, \"n_textures\": %u}\n", d.n_nodes, d.n_tris,
+                d.n_spheres, d.n_textures);
+    return 0;
+}
+
+// frt_dropin gpurender <scene> <w> <h> <spp> <out.pfm> [--seed S] [--gpus N] [--integrator path|ao|normals|direct]:
+// the reference's renderer<> (integrator.h:11-47) instantiated with gpu_path_integrator on the reference's Scene.
+static int cmd_gpurender(int argc, char **argv)
+{
+    if (argc < 7) return 2;
+    const int nx = std::atoi(argv[3]), ny = std::atoi(argv[4]);
+    const uint_fast64_t ns = std::atoll(argv[5]);
+    uint32_t seed = 1, integ = FRT_INTEGRATOR_PATH;
+    int gpus = 1;
+    for (int i = 7; i < argc; ++i)
+    {
+        const std::string a = argv[i];
+        if (a == "--seed") seed = (uint32_t)std::atoll(argv[++i]);
+        else if (a == "--gpus") gpus = std::atoi(argv[++i]);
+        else if (a == "--integrator")
+        {
+            const std::string v = argv[++i];
+            integ = v == "ao" ? FRT_INTEGRATOR_AO : v == "normals" ? FRT_INTEGRATOR_NORMALS : v == "direct" ? FRT_INTEGRATOR_DIRECT : FRT_INTEGRATOR_PATH;
+        }
+    }
+    built_scene &b = build_scene(argv[2], double(nx) / double(ny));
+    std::unordered_map<const hitable *, int> ids;
+    for (size_t i = 0; i < b.creation_order.size(); ++i) ids[b.creation_order[i]] = (int)i;
+    viewer film(nx, ny, ns, 3);
+    renderer<gpu_path_integrator> render;
+    render.seed = seed; render.n_gpus = gpus; render.integrator = integ; render.prim_ids = &ids;
+    std::streambuf *keep = std::cout.rdbuf(std::cerr.rdbuf()); // the reference's timing block goes to stderr: stdout is one JSON line
+    const double secs = render.Render(b.scene.get(), film);
+    std::cout.rdbuf(keep);
+    {
+        std::ofstream os(argv[6], std::ios::binary | std::ios::trunc);
+        os << "PF\n" << nx << " " << ny << "\n-1\n";
+        std::vector<float> row(size_t(nx) * 3);
+        for (int y = 0; y < ny; ++y)
+        {
+            for (int i = 0; i < nx * 3; ++i) row[i] = (float)film.fout_image[size_t(y) * nx * 3 + i];
+            os.write((char *)row.data(), row.size() * 4);
+        }
+    }
+    unsigned long long ldr_sum = 0;
+    for (size_t i = 0; i < size_t(nx) * ny * 3; ++i) ldr_sum += film.out_image[i];
+    std::printf("{\"cmd\": \"gpurender\", \"seconds\": %.6f, \"samples\": %llu, \"closest_rays\": %llu, \"shadow_rays\": %llu, "
+                "\"ldr_sum\": %llu}\n", secs, (unsigned long long)render.stats.samples, (unsigned long long)render.stats.closest_rays,
+                (unsigned long long)render.stats.shadow_rays, ldr_sum);
+    gpu_path_integrator::release_cached_context();
+    return 0;
+}
+#endif
+
 int main(int argc, char **argv)
 {
     if (const char *a = std::getenv("FRT_ASSETS")) g_assets = a;
@@ -759,6 +851,10 @@ int main(int argc, char **argv)
         else if (cmd == "render") rc = cmd_render(argc, argv);
         else if (cmd == "dump") rc = cmd_dump(argc, argv);
         else if (cmd == "bsdf") rc = cmd_bsdf(argc, argv);
+#ifdef FRT_DROPIN
+        else if (cmd == "flatten") rc = cmd_flatten(argc, argv);
+        else if (cmd == "gpurender") rc = cmd_gpurender(argc, argv);
+#endif
         std::fflush(stdout);
         std::_Exit(rc);
     }

@@ -128,3 +128,43 @@ def segment_rays(n: int, lo, hi, seed: int) -> np.ndarray:
     rays["o"] = p.astype(np.float32)
     rays["d"] = (q - p).astype(np.float32)
     return rays
+
+
+DROPIN_BIN = REPO / "oracle" / "_ref" / "frt_dropin"
+
+
+def dropin_flatten(scene: str, aspect: float, max_leaf: int) -> dict:
+    """oracle/_ref/frt_dropin flatten: the product's flattener compiled against the REFERENCE's headers, walking the
+    reference's own Scene → raw bytes of each frt_scene_desc array."""
+    with tempfile.TemporaryDirectory() as td:
+        out = Path(td) / "flat.bin"
+        _run([DROPIN_BIN, "flatten", scene, aspect, max_leaf, out])
+        raw = out.read_bytes()
+    head = np.frombuffer(raw, "<u4", 16)
+    n_nodes, n_tris, n_sph, n_mat, n_lights, has_n, has_env, env_nx, env_ny, n_tex, n_texels, has_uv = (int(x) for x in head[:12])
+    pos = 64
+    parts = {}
+
+    def take(name, nbytes):
+        nonlocal pos
+        parts[name] = raw[pos:pos + nbytes]
+        pos += nbytes
+
+    take("nodes", 128 * n_nodes); take("tris", 48 * n_tris)
+    take("tri_normals", 48 * n_tris if has_n else 0)
+    take("spheres", 32 * n_sph); take("materials", 64 * n_mat); take("lights", 128 * n_lights)
+    take("camera", 22 * 4); take("env_color", 12); take("ao_t_max", 4)
+    take("textures", 32 * n_tex); take("tex_texels", 12 * n_texels); take("tri_uv", 24 * n_tris if has_uv else 0)
+    assert pos == len(raw)
+    parts["has_env_image"] = bool(has_env)
+    return parts
+
+
+def dropin_render(scene: str, nx: int, ny: int, spp: int, seed: int = 1, gpus: int = 1, integrator: str = "path"):
+    """oracle/_ref/frt_dropin gpurender: the reference's own renderer<> (integrator.h:11-47) instantiated with
+    gpu_path_integrator, on the reference's Scene → (mean image, info)."""
+    with tempfile.TemporaryDirectory() as td:
+        out = Path(td) / "img.pfm"
+        info = _run([DROPIN_BIN, "gpurender", scene, nx, ny, spp, out, "--seed", seed, "--gpus", gpus, "--integrator", integrator])
+        img = read_pfm(out)
+    return img, info

@@ -284,3 +284,96 @@ def test_round2_scene_variants_equal_reference_driver(built):
             assert len(rc) == 4 and (rc["p"][:, 10] == 1.0).all()
         if name == "cornell_lens":
             assert abs(d.camera.lens_radius - 0.1) < 1e-7
+
+
+@pytest.mark.parametrize("name,aspect,max_leaf", [("cornell", 1.0, 2), ("veach", 1.5, 2), ("teapot", 16 / 9, 2), ("cornell_sphere", 1.0, 4),
+                                                  ("textured", 1.5, 2), ("cornell_lens", 1.0, 2), ("veach_beckmann+sky", 1.5, 2)])
+def test_drop_in_build_flattens_the_reference_scene_identically(built, name, aspect, max_leaf):
+    """The drop-in claim of INTEGRATION.md, guarded: host/flatten.h + host/gpu_path_integrator.h compile with
+    -DFRT_WITH_REFERENCE_HEADERS against the reference's own headers (oracle/Makefile target `dropin`), and the
+    flattener, walking the REFERENCE's Scene (its parallel_bvh_node / triangle / sphere / material / texture objects,
+    built by the reference's own create_bvh), produces byte for byte the description the host layer produces."""
+    if not refutil.DROPIN_BIN.exists():
+        pytest.skip("oracle/_ref/frt_dropin not built (needs /root/reference)")
+    ref = refutil.dropin_flatten(name, aspect, max_leaf)
+    scene = api.HostScene(name, aspect, max_leaf)
+    d = scene.desc
+
+    def raw(ptr, nbytes):
+        return bytes((C.c_char * nbytes).from_address(ptr)) if ptr and nbytes else b""
+
+    assert raw(d.nodes, 128 * d.n_nodes) == ref["nodes"], "wide nodes differ"
+    assert raw(d.tris, 48 * d.n_tris) == ref["tris"], "triangles differ"
+    assert raw(d.tri_normals, 48 * d.n_tris) == ref["tri_normals"]
+    assert raw(d.spheres, 32 * d.n_spheres) == ref["spheres"]
+    assert raw(d.materials, 64 * d.n_materials) == ref["materials"]
+    assert raw(d.lights, 128 * d.n_lights) == ref["lights"]
+    assert bytes(d.camera) == ref["camera"]
+    assert bytes(d.env_color) == ref["env_color"]
+    assert raw(d.textures, 32 * d.n_textures) == ref["textures"]
+    assert raw(d.tex_texels, 12 * d.n_texels) == ref["tex_texels"]
+    assert raw(d.tri_uv, 24 * d.n_tris) == ref["tri_uv"]
+    assert bool(d.env_image) == ref["has_env_image"]
+
+
+def _decode_wide8(words):
+    """csrc/frt_wide8.cuh layout -> per node: origin (3), spacing (3), lo/hi planes [3][8] in world units, child refs [8]."""
+    w = np.ascontiguousarray(words)
+    origin = w[:, 0:3].copy().view(np.float32)
+    exps = w[:, 3]
+    spacing = np.stack([np.ldexp(1.0, ((exps >> (8 * a)) & 0xFF).astype(np.int64) - 127) for a in range(3)], axis=1)
+    planes = w[:, 4:16].copy().view(np.uint8).reshape(-1, 6, 8).astype(np.float64)
+    lo = origin[:, :, None].astype(np.float64) + planes[:, 0:3] * spacing[:, :, None]
+    hi = origin[:, :, None].astype(np.float64) + planes[:, 3:6] * spacing[:, :, None]
+    return lo, hi, w[:, 16:24]
+
+
+@pytest.mark.parametrize("name,aspect,soup", [("teapot", 16 / 9, 0), ("cornell_sphere", 1.0, 0), ("textured", 1.5, 0), (None, 1.0, 50_000)])
+def test_wide8_nodes_contain_the_wide4_tree(built, name, aspect, soup):
+    """frt_build_wide8 (what frt_upload_scene derives for large scenes): every primitive range of the 4-wide tree is
+    reachable exactly once, every child box CONTAINS the 4-wide tree's float32 box of the same subtree (so a walk of
+    either tree decides the same candidates), inner children are wider than the 4-wide tree's (<= 8, mean > 4)."""
+    scene = api.HostScene(soup=api.soup_triangles(soup), fast_bvh=True, max_leaf=4) if soup else api.HostScene(name, aspect, 2)
+    a = scene.arrays()
+    n4 = a["nodes"]
+    words, depth = api.build_wide8(scene)
+    lo, hi, child = _decode_wide8(words)
+    assert depth >= 1 and 7 * depth + 1 <= 96
+    # 4-wide boxes of every leaf reference and of every inner node (union of its children)
+    def box4(i, k):
+        return (np.array([n4[i]["lo_x"][k], n4[i]["lo_y"][k], n4[i]["lo_z"][k]], np.float64),
+                np.array([n4[i]["hi_x"][k], n4[i]["hi_y"][k], n4[i]["hi_z"][k]], np.float64))
+    leaf_box = {}
+    for i in range(len(n4)):
+        for k in range(4):
+            c = int(n4[i]["child"][k])
+            if c != 0xFFFFFFFF and c & 0x80000000:
+                leaf_box[c] = box4(i, k)
+    seen = []
+    n_children = []
+    stack = [0]
+    visited = set()
+    while stack:
+        i = stack.pop()
+        assert i not in visited
+        visited.add(i)
+        kids = 0
+        for k in range(8):
+            c = int(child[i, k])
+            if c == 0xFFFFFFFF:
+                assert (lo[i, :, k] > hi[i, :, k]).all(), "an empty slot must hold inverted planes"
+                continue
+            kids += 1
+            if c & 0x80000000:
+                seen.append(c)
+                blo, bhi = leaf_box[c]
+                assert (lo[i, :, k] <= blo).all() and (hi[i, :, k] >= bhi).all(), "leaf box not contained"
+            else:
+                assert c > i and c < len(words)
+                stack.append(c)
+        n_children.append(kids)
+    assert len(visited) == len(words)
+    assert sorted(seen) == sorted(leaf_box.keys()), "every leaf range exactly once"
+    assert max(n_children) <= 8 and (len(n4) < 100 or np.mean(n_children) > 4.5)
+    print(f"{name or 'soup'}: {len(n4)} 4-wide nodes ({128 * len(n4)} B) -> {len(words)} 8-wide nodes ({96 * len(words)} B), "
+          f"depth {depth}, mean children {np.mean(n_children):.2f}")
