@@ -293,11 +293,11 @@ def roofline_pass(rig: Rig, spp_range, peaks, clocks):
     traffic = secondary = l2 = None
     if m:
         k = m.get("k_wavefront", {})
-        if k.get("dram_bytes") is not None:
-            # DRAM bytes of the captured launch scaled to this launch by the samples it rendered (the film eviction
-            # traffic is per sample; stated with the capture it comes from)
-            scale = (NX * NY * (s1 - s0)) / max(1.0, k.get("samples", NX * NY * (s1 - s0)))
-            traffic = k["dram_bytes"] * scale
+        full = k.get("traffic")
+        if full and full.get("dram_bytes") is not None and (s1 - s0) == SPP:
+            # dram__bytes_read.sum + dram__bytes_write.sum of the very launch timed here (1080p x 1024 spp on one GPU),
+            # from the ncu pass of scripts/gpu_traffic.sh; other launch shapes: not captured -> null
+            traffic = full["dram_bytes"]
         if k.get("issue_active_pct") is not None:
             secondary = {"bound": "issue", "issue_active_frac": k["issue_active_pct"] / 100.0,
                          "active_lanes_per_inst": k.get("lanes_per_inst"), "lane_issue_frac": k["issue_active_pct"] / 100.0 * (k.get("lanes_per_inst") or 32) / 32.0,

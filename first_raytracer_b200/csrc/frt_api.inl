@@ -38,8 +38,14 @@ int frt_create(frt_ctx **out, const int *devices, int n)
     if (const char *s = getenv("FRT_WF_SORT")) c->wf_sort = atoi(s) & 3;
     if (const char *s = getenv("FRT_WF_REFILL")) c->wf_refill = std::min(31, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_WIDE8")) c->wide8 = atoi(s) ? 1 : 0;
+    // ray-cast tuning knobs (measured defaults; the sweeps of scripts/soup_sweep.py set them)
+    if (const char *s = getenv("FRT_TRACE_OCC")) c->trace_occ[0] = std::min(2, std::max(0, atoi(s)));
+    if (const char *s = getenv("FRT_TRACE_OCC_ANY")) c->trace_occ[1] = std::min(2, std::max(0, atoi(s)));
+    if (const char *s = getenv("FRT_TRACE_REFILL")) c->trace_refill[0] = std::min(31, std::max(0, atoi(s)));
+    if (const char *s = getenv("FRT_TRACE_REFILL_ANY")) c->trace_refill[1] = std::min(31, std::max(-1, atoi(s)));
+    if (const char *s = getenv("FRT_TRACE_STEP")) c->trace_step = std::max(0, atoi(s));
     if (const char *s = getenv("FRT_WIDE8_MIN_TRIS")) c->wide8_min_tris = (uint32_t)std::max(0ll, atoll(s));
-    CU(cudaHostAlloc((void **)&c->h_cancel, sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable));
+    CU(cudaHostAlloc((void **)&c->h_cancel, sizeof(unsigned int), cudaHostAllocPortable));
     *c->h_cancel = 0;
     for (int i = 0; i < n; ++i)
     {
@@ -53,20 +59,20 @@ int frt_create(frt_ctx **out, const int *devices, int n)
                         d.ordinal, prop.major, prop.minor);
         d.sms = prop.multiProcessorCount;
         CU(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&d.side_stream, cudaStreamNonBlocking));
         for (cudaEvent_t *ev : {&d.ev_begin, &d.ev_end, &d.ev_sum, &d.ev_t0, &d.ev_t1}) CU(cudaEventCreate(ev));
         CU(cudaMalloc((void **)&d.d_ctr, sizeof(Counters)));
         CU(cudaMemset(d.d_ctr, 0, sizeof(Counters)));
         CU(cudaMallocHost((void **)&d.h_ctr, sizeof(Counters)));
         memset(d.h_ctr, 0, sizeof(Counters));
         int per_sm = 0;
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<false, false>, 128, 0));
-        d.blocks_trace = std::max(1, per_sm) * d.sms;
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<true, false>, 128, 0));
-        d.blocks_trace_any = std::max(1, per_sm) * d.sms;
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace8<false, false>, 128, 0));
-        d.blocks_trace8 = std::max(1, per_sm) * d.sms;
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace8<true, false>, 128, 0));
-        d.blocks_trace8_any = std::max(1, per_sm) * d.sms;
+        for (int w8 = 0; w8 < 2; ++w8)
+            for (int any = 0; any < 2; ++any)
+                for (int occ = 0; occ < 3; ++occ)
+                {
+                    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_kernels[w8][any][0][occ], 128, 0));
+                    d.blocks_trace[w8][any][occ] = std::max(1, per_sm) * d.sms;
+                }
         const size_t wf_smem = (size_t)c->wf_slots * FRT_WF_SLOT_BYTES;
         const WfConfig &wc = wf_configs[c->wf_config];
         CU(cudaFuncSetAttribute(wc.plain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
@@ -112,6 +118,7 @@ void frt_destroy(frt_ctx *ctx)
         if (d.h_ctr) cudaFreeHost(d.h_ctr);
         for (cudaEvent_t ev : {d.ev_begin, d.ev_end, d.ev_sum, d.ev_t0, d.ev_t1}) if (ev) cudaEventDestroy(ev);
         if (d.stream) cudaStreamDestroy(d.stream);
+        if (d.side_stream) cudaStreamDestroy(d.side_stream);
     }
     if (!ctx->dev.empty()) cudaSetDevice(ctx->dev[0].ordinal);
     if (ctx->d_ldr) cudaFree(ctx->d_ldr);
@@ -286,6 +293,15 @@ int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *s)
         for (int a = 0; a < 3; ++a) m = std::fmax(m, std::fabs(s->camera.origin[a]));
         frt_wide8::build(s->nodes, s->n_nodes, 8e-7f * m, words, &depth8);
         n8 = (uint32_t)(words.size() / 24);
+        // FRT_WIDE8_STRIDE=8: every node on its own 128 B line (a packed 96 B node straddles two lines half of the time)
+        const uint32_t stride = (getenv("FRT_WIDE8_STRIDE") && atoi(getenv("FRT_WIDE8_STRIDE")) == 8) ? 8u : 6u;
+        if (stride == 8)
+        {
+            std::vector<uint32_t> padded((size_t)n8 * 32, 0u);
+            for (uint32_t i = 0; i < n8; ++i) memcpy(&padded[(size_t)i * 32], &words[(size_t)i * 24], 96);
+            words.swap(padded);
+        }
+        v.node8_stride = stride;
         if (7 * depth8 + 1 <= FRT_STACK8_SIZE)
         {
             for (Device &d : ctx->dev)
@@ -300,7 +316,7 @@ int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *s)
     if (!ctx->have_wide8)
         for (Device &d : ctx->dev)
             if (d.d_nodes8) { cudaSetDevice(d.ordinal); cudaFree(d.d_nodes8); d.d_nodes8 = nullptr; }
-    v.prefetch = getenv("FRT_PREFETCH") ? (uint32_t)atoi(getenv("FRT_PREFETCH")) : 1u;
+    v.prefetch = getenv("FRT_TUNE") ? (uint32_t)atoi(getenv("FRT_TUNE")) : 0u;
     uint32_t bsdf_types = 0;
     for (uint32_t i = 0; i < s->n_materials; ++i)
         if (s->materials[i].type != FRT_MAT_DIFFUSE_LIGHT) bsdf_types |= 1u << s->materials[i].type;

@@ -24,6 +24,7 @@ struct Device
 {
     int ordinal = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t side_stream = nullptr; // frt_cancel's 4-byte copy: runs beside the persistent kernel
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_sum = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
     // scene
     void *d_nodes = nullptr, *d_tris = nullptr, *d_normals = nullptr, *d_spheres = nullptr, *d_mats = nullptr,
@@ -38,7 +39,8 @@ struct Device
     void *d_rays = nullptr, *d_hits = nullptr, *d_sort = nullptr;
     size_t trace_cap = 0, sort_cap = 0;
     int sms = 0;
-    int blocks_trace = 0, blocks_trace_any = 0, blocks_trace8 = 0, blocks_trace8_any = 0, blocks_wavefront = 0, blocks_wavefront_other = 0;
+    int blocks_trace[2][2][3] = {}; // resident CTAs of trace_kernels[wide8][any][.][occupancy]
+    int blocks_wavefront = 0, blocks_wavefront_other = 0;
     unsigned int wf_ctas_launched = 0;
     bool rendered = false;
     unsigned long long launches = 0;
@@ -60,6 +62,9 @@ struct frt_ctx
     int wf_refill = 24;           // dynamic fetch threshold (lanes still traversing)
     int wf_sort = -1;             // bit 0: bin queued rays by where they start; bit 1: shade grouped by material;
                                   // -1 = bit 0 always, bit 1 when the scene has more than one BSDF type
+    int trace_occ[2] = {0, 2};    // ray casting: index into {4, 6, 8} CTAs per SM for closest / occlusion casts
+    int trace_refill[2] = {24, -1}; // dynamic fetch threshold for closest / occlusion casts (-1: plain batches of 32)
+    int trace_step = 0;           // inner nodes per traversal round (0 = run to the next leaf)
     int wide8 = -1;               // ray casting over the 8-wide compressed nodes: -1 = scenes of >= wide8_min_tris triangles
     uint32_t wide8_min_tris = 1u << 16;
     bool have_wide8 = false;
@@ -67,7 +72,8 @@ struct frt_ctx
     bool multi_bsdf = false;
     float ao_t_max = 0.f;
     float bounds_lo[3] = {0, 0, 0}, bounds_hi[3] = {0, 0, 0}; // scene box (root node): Morton keys of frt_trace_rays' sort
-    int *h_cancel = nullptr; // mapped pinned flag, read by the render kernels (frt_cancel)
+    unsigned int *h_cancel = nullptr; // pinned: the epoch frt_cancel copies into every device's Counters::cancel_epoch
+    unsigned int epoch = 0;           // launch number of the last tile
     // host staging of the film (pinned, ctx-owned): float sums and the 8-bit tonemapped image
     float *h_film = nullptr;
     unsigned char *h_ldr = nullptr;
@@ -224,13 +230,14 @@ __device__ __forceinline__ void frt_trace_count(Counters *ctr, unsigned int n_ra
 // global cursor with dynamic fetch (frt_persistent_trace).  Occlusion queries end early and carry little state; for
 // them plain batches of 32 rays measured faster, kept.  Register budget: closest hit 4 CTAs / SM (no spills);
 // occlusion queries 8 (64 registers).
-template <bool ANY, bool COUNT>
-__global__ void __launch_bounds__(128, ANY ? 8 : 4) k_trace(DevScene sc, Counters *ctr, const float2 *rays, frt_hit *hits,
-                                                                    const unsigned int *order, unsigned int n, int refill_below)
+// OCC = CTAs of 128 threads per SM the register budget is cut for (4: 128 registers, 6: 85, 8: 64).
+template <bool ANY, bool COUNT, int OCC>
+__global__ void __launch_bounds__(128, OCC) k_trace(DevScene sc, Counters *ctr, const float2 *rays, frt_hit *hits,
+                                                          const unsigned int *order, unsigned int n, int refill_below)
 {
     unsigned int n_rays = 0, n_nodes = 0, n_tris = 0;
     TraceIo io{rays, hits, order, 0u};
-    if (ANY)
+    if (ANY && refill_below < 0)
     {
         while (true)
         {
@@ -250,20 +257,28 @@ __global__ void __launch_bounds__(128, ANY ? 8 : 4) k_trace(DevScene sc, Counter
         }
     }
     else
-        frt_persistent_trace<ANY, COUNT>(sc, io, n, &ctr->trace_next, refill_below, n_rays, n_nodes, n_tris);
+        frt_persistent_trace<ANY, COUNT>(sc, io, n, &ctr->trace_next, refill_below, n_rays, n_nodes, n_tris, sc.trace_step);
     frt_trace_count<ANY, COUNT>(ctr, n_rays, n_nodes, n_tris);
 }
 
-// The same entry over the 8-wide compressed nodes (frt_wide8.cuh): scenes large enough to leave the caches.
-template <bool ANY, bool COUNT>
-__global__ void __launch_bounds__(128, ANY ? 6 : 4) k_trace8(DevScene sc, Counters *ctr, const float2 *rays, frt_hit *hits,
-                                                                     const unsigned int *order, unsigned int n, int refill_below)
+// The same entry over the 8-wide compressed nodes (frt_wide8.cuh).
+template <bool ANY, bool COUNT, int OCC>
+__global__ void __launch_bounds__(128, OCC) k_trace8(DevScene sc, Counters *ctr, const float2 *rays, frt_hit *hits,
+                                                           const unsigned int *order, unsigned int n, int refill_below)
 {
     unsigned int n_rays = 0, n_nodes = 0, n_tris = 0;
     TraceIo io{rays, hits, order, 0u};
-    frt_persistent_trace8<ANY, COUNT>(sc, io, n, &ctr->trace_next, refill_below, n_rays, n_nodes, n_tris);
+    frt_persistent_trace8<ANY, COUNT>(sc, io, n, &ctr->trace_next, refill_below < 0 ? 0 : refill_below, n_rays, n_nodes, n_tris, sc.trace_step);
     frt_trace_count<ANY, COUNT>(ctr, n_rays, n_nodes, n_tris);
 }
+
+// The launch shapes of the ray-cast kernels compiled into the library: [wide8][any][count][occupancy 4 / 6 / 8]
+typedef void (*TraceKernel)(DevScene, Counters *, const float2 *, frt_hit *, const unsigned int *, unsigned int, int);
+#define TRACE_OCC(K, A, C) {K<A, C, 4>, K<A, C, 6>, K<A, C, 8>}
+const TraceKernel trace_kernels[2][2][2][3] = {{{TRACE_OCC(k_trace, false, false), TRACE_OCC(k_trace, false, true)},
+                                                {TRACE_OCC(k_trace, true, false), TRACE_OCC(k_trace, true, true)}},
+                                               {{TRACE_OCC(k_trace8, false, false), TRACE_OCC(k_trace8, false, true)},
+                                                {TRACE_OCC(k_trace8, true, false), TRACE_OCC(k_trace8, true, true)}}};
 
 // Launch shapes of k_wavefront compiled into the library (threads per CTA, CTAs per SM the register
 // budget is cut for); FRT_WF_CONFIG picks one, the default is the measured best.
@@ -276,7 +291,9 @@ struct WfConfig
 #define WF_CFG(T, B) {T, B, k_wavefront<false, T, B, false>, k_wavefront<true, T, B, false>}
 const WfConfig wf_configs[] = {WF_CFG(256, 2), WF_CFG(128, 4), WF_CFG(128, 5), WF_CFG(256, 3), WF_CFG(512, 1), WF_CFG(128, 3),
                                WF_CFG(192, 3), WF_CFG(160, 4), WF_CFG(320, 2), WF_CFG(224, 3), WF_CFG(288, 2),
-                               WF_CFG(384, 1), WF_CFG(448, 1), WF_CFG(192, 2)};
+                               WF_CFG(384, 1), WF_CFG(448, 1), WF_CFG(192, 2),
+                               WF_CFG(576, 1), WF_CFG(640, 1), WF_CFG(704, 1), WF_CFG(768, 1), WF_CFG(1024, 1), WF_CFG(320, 2) /* = 8 */,
+                               WF_CFG(384, 2)};
 const int n_wf_configs = (int)(sizeof wf_configs / sizeof wf_configs[0]);
 // The general kernel: the integrators next to `path` (ao, normals_renderer, ass_1_renderer) and `path` over textured
 // surfaces.  Its own instantiation, so that the path kernel of the untextured scenes carries none of that code

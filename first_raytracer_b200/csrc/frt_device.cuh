@@ -15,7 +15,11 @@ struct DevScene
 {
     const float4 *nodes;       // 8 float4 per frt_bvh4_node
     const uint4 *nodes8;       // 6 uint4 per 8-wide compressed node (frt_wide8.cuh) or nullptr
-    uint32_t prefetch;         // 8-wide walk: L2-prefetch postponed children when they are pushed
+    uint32_t prefetch;         // ray casting: bit 0 = L2-prefetch the next-nearest child when it is pushed, bit 1 = L1-prefetch
+                               // the rest of a leaf's triangles when the leaf is entered, bit 2 = occlusion queries descend into the
+                               // nearest entered child first (FRT_TUNE)
+    uint32_t node8_stride;     // uint4 per 8-wide node: 6 (96 B, packed) or 8 (128 B, one cache line each)
+    int trace_step;            // ray casting: inner nodes per round before the warp looks for idle lanes again
     const float4 *tris;        // 3 float4 per triangle
     const float4 *tri_normals; // 3 float4 per triangle or nullptr
     const float4 *spheres;     // 2 float4 per frt_sphere
@@ -44,6 +48,8 @@ struct Counters // one per device, device memory; mirrored to pinned host memory
     unsigned long long closest_rays, shadow_rays, node_visits, tri_tests, samples_started, nonfinite;
     unsigned int trace_next;          // k_trace: persistent-warp work cursor
     unsigned int wf_iterations;       // wavefront: most iterations any CTA ran
+    unsigned int cancel_epoch;        // frt_cancel: tiles launched with an epoch <= this stop (written by an async copy)
+    unsigned int pad_;
     unsigned long long stage_ns[4];   // wavefront: generate, extend, shade, connect time summed over CTAs
 };
 

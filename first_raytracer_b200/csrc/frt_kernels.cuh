@@ -41,7 +41,8 @@ struct KernelArgs
     TileParams tile;
     Counters *ctr;
     float *film;                // nx*ny*3 radiance sums, row 0 = bottom
-    const volatile int *cancel; // mapped host flag set by frt_cancel (viewer::to_exit, viewer.cpp:101-104 / path.cpp:127)
+    unsigned int epoch;         // this tile's launch number: frt_cancel stops the tiles with epoch <= Counters::cancel_epoch
+                                // (viewer::to_exit, viewer.cpp:101-104 / path.cpp:127)
 };
 
 __device__ __forceinline__ unsigned int lane_id() { return threadIdx.x & 31u; }
@@ -70,7 +71,7 @@ __device__ __forceinline__ unsigned int warp_append(bool pred, unsigned int *cou
 template <bool ANY, bool COUNT, class Io, int WIDE = 4>
 __device__ __forceinline__ void frt_persistent_trace(const DevScene &sc, Io &io, const unsigned int n_items, unsigned int *cursor,
                                                      const int refill_below, unsigned int &n_rays, unsigned int &n_nodes,
-                                                     unsigned int &n_tris)
+                                                     unsigned int &n_tris, const int max_nodes = 0x7FFFFFFF)
 {
     if (n_items == 0) return;
     const unsigned int lane = lane_id();
@@ -100,7 +101,7 @@ __device__ __forceinline__ void frt_persistent_trace(const DevScene &sc, Io &io,
         unsigned int act = __ballot_sync(0xFFFFFFFFu, w.active);
         while (act)
         {
-            if (w.active) w.round(sc, stk, n_nodes, n_tris);
+            if (w.active) w.round(sc, stk, n_nodes, n_tris, max_nodes);
             act = __ballot_sync(0xFFFFFFFFu, w.active);
             if (more && __popc(act) <= refill_below) break;
         }
@@ -116,9 +117,9 @@ __device__ __forceinline__ void frt_persistent_trace(const DevScene &sc, Io &io,
 template <bool ANY, bool COUNT, class Io>
 __device__ __forceinline__ void frt_persistent_trace8(const DevScene &sc, Io &io, const unsigned int n_items, unsigned int *cursor,
                                                       const int refill_below, unsigned int &n_rays, unsigned int &n_nodes,
-                                                      unsigned int &n_tris)
+                                                      unsigned int &n_tris, const int max_nodes = 0x7FFFFFFF)
 {
-    frt_persistent_trace<ANY, COUNT, Io, 8>(sc, io, n_items, cursor, refill_below, n_rays, n_nodes, n_tris);
+    frt_persistent_trace<ANY, COUNT, Io, 8>(sc, io, n_items, cursor, refill_below, n_rays, n_nodes, n_tris, max_nodes);
 }
 
 // Camera path number `idx` of the tile (sample idx / npix of pixel idx % npix) into slot `slot`.

@@ -175,7 +175,7 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
         return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: ao needs frt_scene_desc::ao_t_max > 0");
     int rc = ensure_film(ctx, t->nx, t->ny);
     if (rc != FRT_OK) return rc;
-    *ctx->h_cancel = 0; // a cancel request applies to the tiles launched before it
+    ctx->epoch += 1; // frt_cancel stops the tiles launched up to its call: later tiles carry a larger epoch
 
     const int nd = (int)ctx->dev.size();
     const uint32_t spp = t->spp_end - t->spp_begin;
@@ -193,9 +193,7 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
         a.tile.spp_begin = s0; a.tile.seed = t->seed; a.tile.max_depth = t->max_depth; a.tile.integrator = t->integrator;
         a.ctr = d.d_ctr;
         a.film = d.d_film;
-        int *dc = nullptr;
-        CU(cudaHostGetDevicePointer((void **)&dc, ctx->h_cancel, 0));
-        a.cancel = dc;
+        a.epoch = ctx->epoch;
         const unsigned long long total = (unsigned long long)t->w * t->h * (s1 - s0);
         if (total == 0) continue;
         if (!d.rendered) CU(cudaEventRecord(d.ev_begin, d.stream));
@@ -226,7 +224,15 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
 int frt_cancel(frt_ctx *ctx)
 {
     if (!ctx || !ctx->h_cancel) return FRT_ERR_INVALID;
-    *(volatile int *)ctx->h_cancel = 1;
+    // The flag the kernels poll lives in DEVICE memory (a host-mapped flag costs every CTA a PCIe round trip per
+    // iteration: measured 4x on the whole render); the request travels as a 4-byte asynchronous copy on a side
+    // stream, which the copy engine runs while the persistent kernel occupies the SMs.
+    *ctx->h_cancel = ctx->epoch;
+    for (Device &d : ctx->dev)
+    {
+        CU(cudaSetDevice(d.ordinal));
+        CU(cudaMemcpyAsync(&d.d_ctr->cancel_epoch, ctx->h_cancel, sizeof(unsigned int), cudaMemcpyHostToDevice, d.side_stream));
+    }
     return FRT_OK;
 }
 
@@ -364,7 +370,8 @@ int frt_trace_rays_device(frt_ctx *ctx, int dev, const void *d_rays, size_t n, v
     if (n == 0) { if (device_ms) *device_ms = 0; return FRT_OK; }
     Device &d = ctx->dev[dev];
     CU(cudaSetDevice(d.ordinal));
-    const DevScene sc = device_view(ctx, d);
+    DevScene sc = device_view(ctx, d);
+    sc.trace_step = ctx->trace_step > 0 ? ctx->trace_step : 0x7FFFFFFF;
     const bool count = ctx->flags & FRT_FLAG_COUNTERS, any_hit = mode & FRT_TRACE_ANY_HIT;
     const float2 *r = (const float2 *)d_rays;
     frt_hit *h = (frt_hit *)d_hits;
@@ -383,30 +390,10 @@ int frt_trace_rays_device(frt_ctx *ctx, int dev, const void *d_rays, size_t n, v
     CU(cudaEventRecord(d.ev_t0, d.stream));
     if (mode & FRT_TRACE_SORT) // the ordering is part of the call and of its device time
         CU(frt_sort_rays(r, (unsigned int)n, ctx->bounds_lo, ctx->bounds_hi, (uint32_t *)d.d_sort, &order, d.stream, &d.launches));
-    const int refill = any_hit ? 0 : ctx->wf_refill;
-    if (ctx->have_wide8)
     {
-        const int blocks = any_hit ? d.blocks_trace8_any : d.blocks_trace8;
-        if (any_hit)
-        {
-            if (count) k_trace8<true, true><<<blocks, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
-            else k_trace8<true, false><<<blocks, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
-        }
-        else
-        {
-            if (count) k_trace8<false, true><<<blocks, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
-            else k_trace8<false, false><<<blocks, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
-        }
-    }
-    else if (any_hit)
-    {
-        if (count) k_trace<true, true><<<d.blocks_trace_any, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
-        else k_trace<true, false><<<d.blocks_trace_any, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
-    }
-    else
-    {
-        if (count) k_trace<false, true><<<d.blocks_trace, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
-        else k_trace<false, false><<<d.blocks_trace, 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n, refill);
+        const int a = any_hit ? 1 : 0, w8 = ctx->have_wide8 ? 1 : 0, occ = ctx->trace_occ[a];
+        trace_kernels[w8][a][count ? 1 : 0][occ]<<<d.blocks_trace[w8][a][occ], 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n,
+                                                                                             ctx->trace_refill[a]);
     }
     CU(cudaGetLastError());
     CU(cudaEventRecord(d.ev_t1, d.stream));

@@ -137,9 +137,9 @@ struct Walker
 
     // ---- while-while, part 1 over the 4-wide nodes: descend through inner nodes (EMPTY carries the leaf bit and
     // ends the loop)
-    __device__ __forceinline__ void descend4(const DevScene &sc, uint2 *stk, unsigned int &n_nodes)
+    __device__ __forceinline__ void descend4(const DevScene &sc, uint2 *stk, unsigned int &n_nodes, int max_nodes)
     {
-        while (!(cur & FRT_CHILD_LEAF))
+        for (int it = 0; it < max_nodes && !(cur & FRT_CHILD_LEAF); ++it)
         {
             // eight 128-bit loads, near/far planes picked by ray-direction sign
             const float4 *n = sc.nodes + 8 * (size_t)cur;
@@ -161,6 +161,22 @@ struct Walker
             {
                 // an occlusion query looks at every child the segment enters unless an occluder turns up
                 // first, so the order is free: no sort, no entry distances on the stack
+                if (sc.prefetch & 4u)
+                {
+                    // nearest entered child first (an occluder close to the origin ends the query soonest: shadow rays
+                    // leave a surface whose neighbourhood is where most occluders sit), the others postponed unordered
+                    const uint32_t a0 = (tf0 >= tn0) ? ((__float_as_uint(tn0) & ~3u) | 0u) : 0xFFFFFFFFu;
+                    const uint32_t a1 = (tf1 >= tn1) ? ((__float_as_uint(tn1) & ~3u) | 1u) : 0xFFFFFFFFu;
+                    const uint32_t a2 = (tf2 >= tn2) ? ((__float_as_uint(tn2) & ~3u) | 2u) : 0xFFFFFFFFu;
+                    const uint32_t a3 = (tf3 >= tn3) ? ((__float_as_uint(tn3) & ~3u) | 3u) : 0xFFFFFFFFu;
+                    const uint32_t amin = min(min(a0, a1), min(a2, a3));
+                    if (a3 != 0xFFFFFFFFu && a3 != amin) stk[sp++] = make_uint2(ch.w, 0u);
+                    if (a2 != 0xFFFFFFFFu && a2 != amin) stk[sp++] = make_uint2(ch.z, 0u);
+                    if (a1 != 0xFFFFFFFFu && a1 != amin) stk[sp++] = make_uint2(ch.y, 0u);
+                    if (a0 != 0xFFFFFFFFu && a0 != amin) stk[sp++] = make_uint2(ch.x, 0u);
+                    cur = amin != 0xFFFFFFFFu ? frt_pick(ch, amin & 3u) : FRT_CHILD_EMPTY;
+                    continue;
+                }
                 uint32_t next = FRT_CHILD_EMPTY;
                 if (tf3 >= tn3) next = ch.w;
                 if (tf2 >= tn2) { if (next != FRT_CHILD_EMPTY) stk[sp++] = make_uint2(next, 0u); next = ch.z; }
@@ -183,7 +199,13 @@ struct Walker
             // invalid keys sort last: push the far ones (farthest first), continue with the nearest
             if (k3 != 0xFFFFFFFFu) stk[sp++] = make_uint2(frt_pick(ch, k3 & 3u), k3 & ~3u);
             if (k2 != 0xFFFFFFFFu) stk[sp++] = make_uint2(frt_pick(ch, k2 & 3u), k2 & ~3u);
-            if (k1 != 0xFFFFFFFFu) stk[sp++] = make_uint2(frt_pick(ch, k1 & 3u), k1 & ~3u);
+            if (k1 != 0xFFFFFFFFu)
+            {
+                const uint32_t ref = frt_pick(ch, k1 & 3u);
+                stk[sp++] = make_uint2(ref, k1 & ~3u);
+                // the next-nearest child is the likeliest to be popped: pull it towards L2 while the nearest is walked
+                if ((sc.prefetch & 1u) && !(ref & FRT_CHILD_LEAF)) asm volatile("prefetch.global.L2 [%0];" ::"l"(sc.nodes + 8 * (size_t)ref));
+            }
             cur = (k0 != 0xFFFFFFFFu) ? frt_pick(ch, k0 & 3u) : FRT_CHILD_EMPTY;
         }
     }
@@ -193,11 +215,11 @@ struct Walker
     // slab distance is q * (scale / d) + (origin / d - o / d): one FFMA per plane after three per node.  The
     // quantised boxes contain the float32 boxes of the 4-wide tree (floor / ceil), hits are decided by the same
     // triangle code, so results do not depend on which tree is walked.
-    __device__ __forceinline__ void descend8(const DevScene &sc, uint2 *stk, unsigned int &n_nodes)
+    __device__ __forceinline__ void descend8(const DevScene &sc, uint2 *stk, unsigned int &n_nodes, int max_nodes)
     {
-        while (!(cur & FRT_CHILD_LEAF))
+        for (int it = 0; it < max_nodes && !(cur & FRT_CHILD_LEAF); ++it)
         {
-            const uint4 *n = sc.nodes8 + 6 * (size_t)cur;
+            const uint4 *n = sc.nodes8 + sc.node8_stride * (size_t)cur;
             if (COUNT) ++n_nodes;
             const uint4 hd = __ldg(n), qa = __ldg(n + 1), qb = __ldg(n + 2), qc = __ldg(n + 3);
             const uint4 c0 = __ldg(n + 4), c1 = __ldg(n + 5);
@@ -256,8 +278,8 @@ struct Walker
                     stk[sp++] = make_uint2(ref, key[j] & ~7u);
                     // the node will be wanted when this entry is popped: pull it towards L2 now (latency, not bandwidth,
                     // bounds a large incoherent scene)
-                    if (sc.prefetch && !(ref & FRT_CHILD_LEAF))
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(sc.nodes8 + 6 * (size_t)ref));
+                    if ((sc.prefetch & 1u) && j == 1 && !(ref & FRT_CHILD_LEAF))
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(sc.nodes8 + sc.node8_stride * (size_t)ref));
                 }
             if (key[0] != 0xFFFFFFFFu)
             {
@@ -269,9 +291,13 @@ struct Walker
         }
     }
 
-    __device__ __forceinline__ void round(const DevScene &sc, uint2 *stk, unsigned int &n_nodes, unsigned int &n_tris)
+    // max_nodes: inner nodes one round may visit before the caller looks at the warp again (large incoherent scenes:
+    // 1, so that idle lanes are refilled after every memory round trip; cache-resident scenes: unlimited)
+    __device__ __forceinline__ void round(const DevScene &sc, uint2 *stk, unsigned int &n_nodes, unsigned int &n_tris,
+                                          const int max_nodes = 0x7FFFFFFF)
     {
-        if (WIDE == 8) descend8(sc, stk, n_nodes); else descend4(sc, stk, n_nodes);
+        if (WIDE == 8) descend8(sc, stk, n_nodes, max_nodes); else descend4(sc, stk, n_nodes, max_nodes);
+        if (!(cur & FRT_CHILD_LEAF)) return; // still inside the tree: the round ends at the node budget
 
         // ---- part 2: one leaf
         if (cur != FRT_CHILD_EMPTY)
@@ -279,6 +305,14 @@ struct Walker
             const uint32_t first = cur & FRT_LEAF_FIRST_MASK;
             const uint32_t count = ((cur >> FRT_LEAF_COUNT_SHIFT) & 15u) + 1u;
             const bool is_sphere = cur & FRT_CHILD_SPHERE;
+            if ((sc.prefetch & 2u) && !is_sphere && count > 1u)
+            {
+                // the leaf's triangles are contiguous (48 B each) and tested one after the other: ask for the lines
+                // behind the first one now, so that the following tests do not each wait for HBM
+                const char *tp = reinterpret_cast<const char *>(sc.tris + 3 * (size_t)first);
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(tp + 128));
+                if (count > 5u) asm volatile("prefetch.global.L1 [%0];" ::"l"(tp + 256));
+            }
             for (uint32_t k = 0; k < count; ++k)
             {
                 const uint32_t prim = is_sphere ? ((first + k) | FRT_CHILD_SPHERE) : first + k;

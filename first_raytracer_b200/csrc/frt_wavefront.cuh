@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelA
             unsigned long long base = total;
             // frt_cancel (viewer::to_exit, viewer.cpp:101-104; path.cpp:127 leaves its row loop): polled once per
             // CTA iteration; a cancelled tile takes no more samples and drops the paths in flight
-            const bool cancelled = *a.cancel != 0;
+            const bool cancelled = *(const volatile unsigned int *)&a.ctr->cancel_epoch >= a.epoch; // device memory: an L2 hit
             sh.cancelled = cancelled;
             if (want && !sh.exhausted && !cancelled)
             {
