@@ -36,11 +36,12 @@ int frt_create(frt_ctx **out, const int *devices, int n)
     if (const char *s = getenv("FRT_WF_SLOTS")) c->wf_slots = (unsigned int)std::min(1568, std::max(32, atoi(s) / 32 * 32));
     if (const char *s = getenv("FRT_WF_CONFIG")) c->wf_config = std::min(n_wf_configs - 1, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_WF_SORT")) c->wf_sort = atoi(s) & 3;
+    if (const char *s = getenv("FRT_WF_MODE")) c->wf_mode = atoi(s) ? 1 : 0;
     if (const char *s = getenv("FRT_WF_REFILL")) c->wf_refill = std::min(31, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_WIDE8")) c->wide8 = atoi(s) ? 1 : 0;
     // ray-cast tuning knobs (measured defaults; the sweeps of scripts/soup_sweep.py set them)
-    if (const char *s = getenv("FRT_TRACE_OCC")) c->trace_occ[0] = std::min(2, std::max(0, atoi(s)));
-    if (const char *s = getenv("FRT_TRACE_OCC_ANY")) c->trace_occ[1] = std::min(2, std::max(0, atoi(s)));
+    if (const char *s = getenv("FRT_TRACE_OCC")) c->trace_occ[0] = std::min(3, std::max(0, atoi(s)));
+    if (const char *s = getenv("FRT_TRACE_OCC_ANY")) c->trace_occ[1] = std::min(3, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_TRACE_REFILL")) c->trace_refill[0] = std::min(31, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_TRACE_REFILL_ANY")) c->trace_refill[1] = std::min(31, std::max(-1, atoi(s)));
     if (const char *s = getenv("FRT_TRACE_STEP")) c->trace_step = std::max(0, atoi(s));
@@ -68,22 +69,24 @@ int frt_create(frt_ctx **out, const int *devices, int n)
         int per_sm = 0;
         for (int w8 = 0; w8 < 2; ++w8)
             for (int any = 0; any < 2; ++any)
-                for (int occ = 0; occ < 3; ++occ)
+                for (int occ = 0; occ < 4; ++occ)
                 {
                     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_kernels[w8][any][0][occ], 128, 0));
                     d.blocks_trace[w8][any][occ] = std::max(1, per_sm) * d.sms;
                 }
         const size_t wf_smem = (size_t)c->wf_slots * FRT_WF_SLOT_BYTES;
         const WfConfig &wc = wf_configs[c->wf_config];
-        CU(cudaFuncSetAttribute(wc.plain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
-        CU(cudaFuncSetAttribute(wc.counting, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wc.plain, wc.threads, wf_smem));
+        for (int mode = 0; mode < 2; ++mode)
+            for (int cnt = 0; cnt < 2; ++cnt)
+            {
+                CU(cudaFuncSetAttribute(wc.kernel[mode][cnt], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
+                CU(cudaFuncSetAttribute(wf_other.kernel[mode][cnt], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
+            }
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wc.kernel[c->wf_mode][0], wc.threads, wf_smem));
         if (per_sm < 1)
             return fail(nullptr, FRT_ERR_CUDA, "frt_create: k_wavefront does not fit an SM with %u slots per CTA", c->wf_slots);
         d.blocks_wavefront = per_sm * d.sms;
-        CU(cudaFuncSetAttribute(wf_other.plain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
-        CU(cudaFuncSetAttribute(wf_other.counting, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_other.plain, wf_other.threads, wf_smem));
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_other.kernel[c->wf_mode][0], wf_other.threads, wf_smem));
         d.blocks_wavefront_other = per_sm * d.sms; // 0: only the path integrator fits this FRT_WF_SLOTS
     }
     // peer access between every pair of the context's devices: the film reduce-scatter of frt_readback reads
@@ -254,16 +257,21 @@ int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *s)
     {
         CU(cudaSetDevice(d.ordinal));
         CU(cudaStreamSynchronize(d.stream));
-        if ((rc = upload_array(ctx, &d.d_nodes, s->nodes, s->n_nodes)) != FRT_OK) return rc;
-        if ((rc = upload_array(ctx, &d.d_tris, s->tris, 3 * (size_t)s->n_tris)) != FRT_OK) return rc;
-        if ((rc = upload_array(ctx, &d.d_normals, s->tri_normals, s->tri_normals ? 3 * (size_t)s->n_tris : 0)) != FRT_OK) return rc;
-        if ((rc = upload_array(ctx, &d.d_spheres, s->spheres, s->n_spheres)) != FRT_OK) return rc;
-        if ((rc = upload_array(ctx, &d.d_mats, s->materials, s->n_materials)) != FRT_OK) return rc;
-        if ((rc = upload_array(ctx, &d.d_lights, s->lights, s->n_lights)) != FRT_OK) return rc;
-        if ((rc = upload_array(ctx, &d.d_env, s->env_image, s->env_image ? 3 * (size_t)s->env_nx * s->env_ny : 0)) != FRT_OK) return rc;
-        if ((rc = upload_array(ctx, &d.d_textures, s->textures, s->n_textures)) != FRT_OK) return rc;
-        if ((rc = upload_array(ctx, &d.d_texels, s->tex_texels, 3 * (size_t)s->n_texels)) != FRT_OK) return rc;
-        if ((rc = upload_array(ctx, &d.d_tri_uv, s->tri_uv, (s->tri_uv && s->n_textures) ? 6 * (size_t)s->n_tris : 0)) != FRT_OK) return rc;
+        if ((rc = upload_array(ctx, d, &d.d_nodes, s->nodes, s->n_nodes)) != FRT_OK) return rc;
+        if ((rc = upload_array(ctx, d, &d.d_tris, s->tris, 3 * (size_t)s->n_tris)) != FRT_OK) return rc;
+        if ((rc = upload_array(ctx, d, &d.d_normals, s->tri_normals, s->tri_normals ? 3 * (size_t)s->n_tris : 0)) != FRT_OK) return rc;
+        if ((rc = upload_array(ctx, d, &d.d_spheres, s->spheres, s->n_spheres)) != FRT_OK) return rc;
+        if ((rc = upload_array(ctx, d, &d.d_mats, s->materials, s->n_materials)) != FRT_OK) return rc;
+        if ((rc = upload_array(ctx, d, &d.d_lights, s->lights, s->n_lights)) != FRT_OK) return rc;
+        if ((rc = upload_array(ctx, d, &d.d_env, s->env_image, s->env_image ? 3 * (size_t)s->env_nx * s->env_ny : 0)) != FRT_OK) return rc;
+        if ((rc = upload_array(ctx, d, &d.d_textures, s->textures, s->n_textures)) != FRT_OK) return rc;
+        if ((rc = upload_array(ctx, d, &d.d_texels, s->tex_texels, 3 * (size_t)s->n_texels)) != FRT_OK) return rc;
+        if ((rc = upload_array(ctx, d, &d.d_tri_uv, s->tri_uv, (s->tri_uv && s->n_textures) ? 6 * (size_t)s->n_tris : 0)) != FRT_OK) return rc;
+    }
+    for (Device &d : ctx->dev) // the caller's arrays may go away after the call
+    {
+        CU(cudaSetDevice(d.ordinal));
+        CU(cudaStreamSynchronize(d.stream));
     }
     // scene box (children of the root): the Morton keys of frt_trace_rays' sort are taken inside it
     for (int a = 0; a < 3; ++a) { ctx->bounds_lo[a] = 0.f; ctx->bounds_hi[a] = 0.f; }
@@ -307,7 +315,12 @@ int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *s)
             for (Device &d : ctx->dev)
             {
                 CU(cudaSetDevice(d.ordinal));
-                if ((rc = upload_array(ctx, &d.d_nodes8, words.data(), words.size())) != FRT_OK) return rc;
+                if ((rc = upload_array(ctx, d, &d.d_nodes8, words.data(), words.size())) != FRT_OK) return rc;
+            }
+            for (Device &d : ctx->dev) // `words` is a local
+            {
+                CU(cudaSetDevice(d.ordinal));
+                CU(cudaStreamSynchronize(d.stream));
             }
             ctx->have_wide8 = true;
             ctx->n_nodes8 = n8;

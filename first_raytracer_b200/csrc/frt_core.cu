@@ -7,12 +7,14 @@
 #include <cstdlib>
 #include <cmath>
 #include <cstring>
+#include <map>
 #include <memory>
 #include <string>
 #include <thread>
 #include <vector>
 #include "frt_shade.cuh"
 #include "frt_wavefront.cuh"
+#include "frt_wavefront_warp.cuh"
 #include "frt_wide8.cuh"
 #include "frt_sort.cuh"
 
@@ -39,11 +41,12 @@ struct Device
     void *d_rays = nullptr, *d_hits = nullptr, *d_sort = nullptr;
     size_t trace_cap = 0, sort_cap = 0;
     int sms = 0;
-    int blocks_trace[2][2][3] = {}; // resident CTAs of trace_kernels[wide8][any][.][occupancy]
+    int blocks_trace[2][2][4] = {}; // resident CTAs of trace_kernels[wide8][any][.][occupancy]
     int blocks_wavefront = 0, blocks_wavefront_other = 0;
     unsigned int wf_ctas_launched = 0;
     bool rendered = false;
     unsigned long long launches = 0;
+    std::map<void *, size_t> cap; // bytes allocated behind each scene-array pointer above (keyed by the member's address)
 };
 
 } // namespace
@@ -58,11 +61,13 @@ struct frt_ctx
     DevScene host_view{}; // counts + camera; pointers filled per device
     uint32_t nx = 0, ny = 0;
     unsigned int wf_slots = 1024; // slots per CTA (multiple of 32)
-    int wf_config = 4;            // index into wf_configs[]: 512 threads, one CTA per SM (measured best)
+    int wf_config = 1;            // index into wf_configs[]: 512 threads, one CTA per SM (measured best)
+    int wf_mode = 1;              // 0 = CTA-wide pipeline (k_wavefront), 1 = warp-autonomous (k_wavefront_warp)
     int wf_refill = 24;           // dynamic fetch threshold (lanes still traversing)
     int wf_sort = -1;             // bit 0: bin queued rays by where they start; bit 1: shade grouped by material;
                                   // -1 = bit 0 always, bit 1 when the scene has more than one BSDF type
-    int trace_occ[2] = {0, 2};    // ray casting: index into {4, 6, 8} CTAs per SM for closest / occlusion casts
+    int trace_occ[2] = {2, 2};    // ray casting: index into {4, 6, 8, 12} CTAs per SM for closest / occlusion casts (a large
+                                  // incoherent scene is latency-bound: 8 CTAs of 64 registers measured +25 % over 4 of 128)
     int trace_refill[2] = {24, -1}; // dynamic fetch threshold for closest / occlusion casts (-1: plain batches of 32)
     int trace_step = 0;           // inner nodes per traversal round (0 = run to the next leaf)
     int wide8 = -1;               // ray casting over the 8-wide compressed nodes: -1 = scenes of >= wide8_min_tris triangles
@@ -102,13 +107,28 @@ int fail(frt_ctx *ctx, int code, const char *fmt, ...)
             return fail(ctx, FRT_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
     } while (0)
 
+// Scene arrays keep their device allocation between uploads (renderer<gpu_path_integrator> uploads the scene every
+// frame: ten cudaFree + cudaMalloc pairs per device cost more than a 1080p x 128 spp share of an 8-GPU frame); the
+// copy is enqueued on the device's stream, frt_upload_scene synchronises every device once at the end.
 template <class T>
-int upload_array(frt_ctx *ctx, void **dst, const T *src, size_t n)
+int upload_array(frt_ctx *ctx, Device &d, void **dst, const T *src, size_t n)
 {
-    if (*dst) { cudaFree(*dst); *dst = nullptr; }
-    if (n == 0) return FRT_OK;
-    CU(cudaMalloc(dst, n * sizeof(T)));
-    CU(cudaMemcpy(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice));
+    const size_t bytes = n * sizeof(T);
+    size_t &cap = d.cap[(void *)dst];
+    if (n == 0)
+    {
+        if (*dst) { cudaFree(*dst); *dst = nullptr; }
+        cap = 0;
+        return FRT_OK;
+    }
+    if (!*dst || cap < bytes)
+    {
+        if (*dst) { cudaFree(*dst); *dst = nullptr; }
+        cap = 0;
+        CU(cudaMalloc(dst, bytes));
+        cap = bytes;
+    }
+    CU(cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, d.stream));
     return FRT_OK;
 }
 
@@ -230,7 +250,7 @@ __device__ __forceinline__ void frt_trace_count(Counters *ctr, unsigned int n_ra
 // global cursor with dynamic fetch (frt_persistent_trace).  Occlusion queries end early and carry little state; for
 // them plain batches of 32 rays measured faster, kept.  Register budget: closest hit 4 CTAs / SM (no spills);
 // occlusion queries 8 (64 registers).
-// OCC = CTAs of 128 threads per SM the register budget is cut for (4: 128 registers, 6: 85, 8: 64).
+// OCC = CTAs of 128 threads per SM the register budget is cut for (4: 128 registers, 6: 85, 8: 64, 12: 42).
 template <bool ANY, bool COUNT, int OCC>
 __global__ void __launch_bounds__(128, OCC) k_trace(DevScene sc, Counters *ctr, const float2 *rays, frt_hit *hits,
                                                           const unsigned int *order, unsigned int n, int refill_below)
@@ -248,7 +268,7 @@ __global__ void __launch_bounds__(128, OCC) k_trace(DevScene sc, Counters *ctr, 
             if (base + lane_id() >= n) continue;
             float3 o, d;
             io.load(base + lane_id(), o, d);
-            Walker<ANY, COUNT> w;
+            Walker<ANY, COUNT, 4, true> w;
             uint2 stk[FRT_STACK_SIZE];
             w.begin(sc, o, d);
             while (w.active) w.round(sc, stk, n_nodes, n_tris);
@@ -257,7 +277,7 @@ __global__ void __launch_bounds__(128, OCC) k_trace(DevScene sc, Counters *ctr, 
         }
     }
     else
-        frt_persistent_trace<ANY, COUNT>(sc, io, n, &ctr->trace_next, refill_below, n_rays, n_nodes, n_tris, sc.trace_step);
+        frt_persistent_trace<ANY, COUNT, TraceIo, 4, true>(sc, io, n, &ctr->trace_next, refill_below, n_rays, n_nodes, n_tris, sc.trace_step);
     frt_trace_count<ANY, COUNT>(ctr, n_rays, n_nodes, n_tris);
 }
 
@@ -274,31 +294,29 @@ __global__ void __launch_bounds__(128, OCC) k_trace8(DevScene sc, Counters *ctr,
 
 // The launch shapes of the ray-cast kernels compiled into the library: [wide8][any][count][occupancy 4 / 6 / 8]
 typedef void (*TraceKernel)(DevScene, Counters *, const float2 *, frt_hit *, const unsigned int *, unsigned int, int);
-#define TRACE_OCC(K, A, C) {K<A, C, 4>, K<A, C, 6>, K<A, C, 8>}
-const TraceKernel trace_kernels[2][2][2][3] = {{{TRACE_OCC(k_trace, false, false), TRACE_OCC(k_trace, false, true)},
+#define TRACE_OCC(K, A, C) {K<A, C, 4>, K<A, C, 6>, K<A, C, 8>, K<A, C, 12>}
+const TraceKernel trace_kernels[2][2][2][4] = {{{TRACE_OCC(k_trace, false, false), TRACE_OCC(k_trace, false, true)},
                                                 {TRACE_OCC(k_trace, true, false), TRACE_OCC(k_trace, true, true)}},
                                                {{TRACE_OCC(k_trace8, false, false), TRACE_OCC(k_trace8, false, true)},
                                                 {TRACE_OCC(k_trace8, true, false), TRACE_OCC(k_trace8, true, true)}}};
 
-// Launch shapes of k_wavefront compiled into the library (threads per CTA, CTAs per SM the register
-// budget is cut for); FRT_WF_CONFIG picks one, the default is the measured best.
+// Launch shapes of the wavefront kernels compiled into the library (threads per CTA, CTAs per SM the register budget is
+// cut for); FRT_WF_CONFIG picks one, the default is the measured best.  Each shape exists as the CTA-wide pipeline
+// (k_wavefront: one pool per CTA, stages separated by __syncthreads) and as the warp-autonomous one (k_wavefront_warp:
+// every warp runs the pipeline on its slice of the pool); FRT_WF_MODE picks (0 = CTA-wide, 1 = warp-autonomous).
+typedef void (*WfKernel)(const KernelArgs, const unsigned int, const int, const int);
 struct WfConfig
 {
     int threads, min_blocks;
-    void (*plain)(const KernelArgs, const unsigned int, const int, const int);
-    void (*counting)(const KernelArgs, const unsigned int, const int, const int);
+    WfKernel kernel[2][2]; // [mode][counting]
 };
-#define WF_CFG(T, B) {T, B, k_wavefront<false, T, B, false>, k_wavefront<true, T, B, false>}
-const WfConfig wf_configs[] = {WF_CFG(256, 2), WF_CFG(128, 4), WF_CFG(128, 5), WF_CFG(256, 3), WF_CFG(512, 1), WF_CFG(128, 3),
-                               WF_CFG(192, 3), WF_CFG(160, 4), WF_CFG(320, 2), WF_CFG(224, 3), WF_CFG(288, 2),
-                               WF_CFG(384, 1), WF_CFG(448, 1), WF_CFG(192, 2),
-                               WF_CFG(576, 1), WF_CFG(640, 1), WF_CFG(704, 1), WF_CFG(768, 1), WF_CFG(1024, 1), WF_CFG(320, 2) /* = 8 */,
-                               WF_CFG(384, 2)};
+#define WF_CFG(T, B, O) {T, B, {{k_wavefront<false, T, B, O>, k_wavefront<true, T, B, O>}, {k_wavefront_warp<false, T, B, O>, k_wavefront_warp<true, T, B, O>}}}
+const WfConfig wf_configs[] = {WF_CFG(256, 2, false), WF_CFG(512, 1, false), WF_CFG(384, 1, false), WF_CFG(320, 2, false), WF_CFG(640, 1, false)};
 const int n_wf_configs = (int)(sizeof wf_configs / sizeof wf_configs[0]);
 // The general kernel: the integrators next to `path` (ao, normals_renderer, ass_1_renderer) and `path` over textured
 // surfaces.  Its own instantiation, so that the path kernel of the untextured scenes carries none of that code
 // (measured: -11 % when it did), in one shape.
-const WfConfig wf_other = {512, 1, k_wavefront<false, 512, 1, true>, k_wavefront<true, 512, 1, true>};
+const WfConfig wf_other = WF_CFG(512, 1, true);
 
 // `any_tend` = upper end of occlusion queries: path.cpp:50 passes 1 - SHADOW_EPSILON (a float literal, util.h:11)
 DevScene device_view(const frt_ctx *ctx, const Device &d, double any_tend = 1.0 - (double)1e-3f)

@@ -209,8 +209,10 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
         if (resident < 1) return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: FRT_WF_SLOTS=%u leaves no room for this integrator's kernel", ctx->wf_slots);
         const unsigned int grid = (unsigned int)std::min<unsigned long long>((unsigned long long)resident, want);
         k_reset_tile<<<1, 1, 0, d.stream>>>(d.d_ctr, total);
-        (count ? wc.counting : wc.plain)<<<grid, wc.threads, smem, d.stream>>>(a, ctx->wf_slots, ctx->wf_refill,
-                                                                                 ctx->wf_sort >= 0 ? ctx->wf_sort : (ctx->multi_bsdf ? 3 : 1));
+        // the warp-autonomous pipeline needs at least 32 slots per warp of the CTA
+        const int mode = (ctx->wf_mode && ctx->wf_slots / (unsigned int)(wc.threads / 32) >= 32u) ? 1 : 0;
+        wc.kernel[mode][count ? 1 : 0]<<<grid, wc.threads, smem, d.stream>>>(a, ctx->wf_slots, ctx->wf_refill,
+                                                                               ctx->wf_sort >= 0 ? ctx->wf_sort : (ctx->multi_bsdf ? 3 : 1));
         CU(cudaGetLastError());
         CU(cudaEventRecord(d.ev_end, d.stream));
         d.launches += 2;

@@ -93,7 +93,9 @@ struct BestHit
 // to a leaf, test its primitives, pop the next postponed child), finish() gives the hit.  Splitting
 // the loop this way lets a persistent warp look at its lanes between rounds and hand finished
 // lanes a new ray (dynamic fetch) instead of idling until the slowest lane is done.
-template <bool ANY, bool COUNT, int WIDE = 4>
+// RT = the ray-cast entry's runtime knobs are compiled in (node budget per round, prefetches, the order occlusion
+// queries descend in: DevScene::trace_step / ::prefetch); the wavefront kernels instantiate RT = false and carry none.
+template <bool ANY, bool COUNT, int WIDE = 4, bool RT = false>
 struct Walker
 {
     float3 o, d;
@@ -139,7 +141,7 @@ struct Walker
     // ends the loop)
     __device__ __forceinline__ void descend4(const DevScene &sc, uint2 *stk, unsigned int &n_nodes, int max_nodes)
     {
-        for (int it = 0; it < max_nodes && !(cur & FRT_CHILD_LEAF); ++it)
+        for (int it = 0; (!RT || it < max_nodes) && !(cur & FRT_CHILD_LEAF); ++it)
         {
             // eight 128-bit loads, near/far planes picked by ray-direction sign
             const float4 *n = sc.nodes + 8 * (size_t)cur;
@@ -157,11 +159,11 @@ struct Walker
             const float tf1 = fminf(fminf(fx.y * idx - oox, fy.y * idy - ooy), fminf(fz.y * idz - ooz, tmax));
             const float tf2 = fminf(fminf(fx.z * idx - oox, fy.z * idy - ooy), fminf(fz.z * idz - ooz, tmax));
             const float tf3 = fminf(fminf(fx.w * idx - oox, fy.w * idy - ooy), fminf(fz.w * idz - ooz, tmax));
-            if (ANY)
+            if (ANY && !(RT && (sc.prefetch & 8u))) // bit 3: occlusion queries walk exactly like closest-hit queries (sorted)
             {
                 // an occlusion query looks at every child the segment enters unless an occluder turns up
                 // first, so the order is free: no sort, no entry distances on the stack
-                if (sc.prefetch & 4u)
+                if (RT && (sc.prefetch & 4u))
                 {
                     // nearest entered child first (an occluder close to the origin ends the query soonest: shadow rays
                     // leave a surface whose neighbourhood is where most occluders sit), the others postponed unordered
@@ -204,7 +206,7 @@ struct Walker
                 const uint32_t ref = frt_pick(ch, k1 & 3u);
                 stk[sp++] = make_uint2(ref, k1 & ~3u);
                 // the next-nearest child is the likeliest to be popped: pull it towards L2 while the nearest is walked
-                if ((sc.prefetch & 1u) && !(ref & FRT_CHILD_LEAF)) asm volatile("prefetch.global.L2 [%0];" ::"l"(sc.nodes + 8 * (size_t)ref));
+                if (RT && (sc.prefetch & 1u) && !(ref & FRT_CHILD_LEAF)) asm volatile("prefetch.global.L2 [%0];" ::"l"(sc.nodes + 8 * (size_t)ref));
             }
             cur = (k0 != 0xFFFFFFFFu) ? frt_pick(ch, k0 & 3u) : FRT_CHILD_EMPTY;
         }
@@ -217,7 +219,7 @@ struct Walker
     // triangle code, so results do not depend on which tree is walked.
     __device__ __forceinline__ void descend8(const DevScene &sc, uint2 *stk, unsigned int &n_nodes, int max_nodes)
     {
-        for (int it = 0; it < max_nodes && !(cur & FRT_CHILD_LEAF); ++it)
+        for (int it = 0; (!RT || it < max_nodes) && !(cur & FRT_CHILD_LEAF); ++it)
         {
             const uint4 *n = sc.nodes8 + sc.node8_stride * (size_t)cur;
             if (COUNT) ++n_nodes;
@@ -278,7 +280,7 @@ struct Walker
                     stk[sp++] = make_uint2(ref, key[j] & ~7u);
                     // the node will be wanted when this entry is popped: pull it towards L2 now (latency, not bandwidth,
                     // bounds a large incoherent scene)
-                    if ((sc.prefetch & 1u) && j == 1 && !(ref & FRT_CHILD_LEAF))
+                    if (RT && (sc.prefetch & 1u) && j == 1 && !(ref & FRT_CHILD_LEAF))
                         asm volatile("prefetch.global.L2 [%0];" ::"l"(sc.nodes8 + sc.node8_stride * (size_t)ref));
                 }
             if (key[0] != 0xFFFFFFFFu)
@@ -297,7 +299,7 @@ struct Walker
                                           const int max_nodes = 0x7FFFFFFF)
     {
         if (WIDE == 8) descend8(sc, stk, n_nodes, max_nodes); else descend4(sc, stk, n_nodes, max_nodes);
-        if (!(cur & FRT_CHILD_LEAF)) return; // still inside the tree: the round ends at the node budget
+        if (RT && !(cur & FRT_CHILD_LEAF)) return; // still inside the tree: the round ends at the node budget
 
         // ---- part 2: one leaf
         if (cur != FRT_CHILD_EMPTY)
@@ -305,7 +307,7 @@ struct Walker
             const uint32_t first = cur & FRT_LEAF_FIRST_MASK;
             const uint32_t count = ((cur >> FRT_LEAF_COUNT_SHIFT) & 15u) + 1u;
             const bool is_sphere = cur & FRT_CHILD_SPHERE;
-            if ((sc.prefetch & 2u) && !is_sphere && count > 1u)
+            if (RT && (sc.prefetch & 2u) && !is_sphere && count > 1u)
             {
                 // the leaf's triangles are contiguous (48 B each) and tested one after the other: ask for the lines
                 // behind the first one now, so that the following tests do not each wait for HBM
@@ -454,15 +456,4 @@ __device__ __forceinline__ void frt_resolve_hit(const DevScene &sc, const float3
     prim &= ~FRT_HIT_INEXACT;
     const ExactHit b = frt_tri_exact(sc.tris, prim, o.x, o.y, o.z, d.x, d.y, d.z, frt_tmin_exact(o));
     if (b.t >= 0.0) { t = (float)b.t; u = b.u; v = b.v; }
-}
-
-template <bool ANY, bool COUNT>
-__device__ __forceinline__ RayHit frt_traverse(const DevScene &sc, const float3 o, const float3 d, float /*unused*/,
-                                               unsigned int &n_nodes, unsigned int &n_tris)
-{
-    Walker<ANY, COUNT> w;
-    uint2 stk[FRT_STACK_SIZE];
-    w.begin(sc, o, d);
-    while (w.active) w.round(sc, stk, n_nodes, n_tris);
-    return w.finish(sc);
 }

@@ -2,7 +2,7 @@
   python scripts/prof_target.py soup [n_tri] [n_rays] | teapot [spp] | cornell [spp] | veach [spp]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np
+import numpy as np  # noqa: F401
 from first_raytracer_b200 import api
 what = sys.argv[1]
 if what == "soup":
