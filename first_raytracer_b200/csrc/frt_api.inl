@@ -36,7 +36,6 @@ int frt_create(frt_ctx **out, const int *devices, int n)
     if (const char *s = getenv("FRT_WF_SLOTS")) c->wf_slots = (unsigned int)std::min(1568, std::max(32, atoi(s) / 32 * 32));
     if (const char *s = getenv("FRT_WF_CONFIG")) c->wf_config = std::min(n_wf_configs - 1, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_WF_SORT")) c->wf_sort = atoi(s) & 3;
-    if (const char *s = getenv("FRT_WF_MODE")) c->wf_mode = atoi(s) ? 1 : 0;
     if (const char *s = getenv("FRT_WF_REFILL")) c->wf_refill = std::min(31, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_WIDE8")) c->wide8 = atoi(s) ? 1 : 0;
     // ray-cast tuning knobs (measured defaults; the sweeps of scripts/soup_sweep.py set them)
@@ -44,7 +43,7 @@ int frt_create(frt_ctx **out, const int *devices, int n)
     if (const char *s = getenv("FRT_TRACE_OCC_ANY")) c->trace_occ[1] = std::min(3, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_TRACE_REFILL")) c->trace_refill[0] = std::min(31, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_TRACE_REFILL_ANY")) c->trace_refill[1] = std::min(31, std::max(-1, atoi(s)));
-    if (const char *s = getenv("FRT_TRACE_STEP")) c->trace_step = std::max(0, atoi(s));
+
     if (const char *s = getenv("FRT_WIDE8_MIN_TRIS")) c->wide8_min_tris = (uint32_t)std::max(0ll, atoll(s));
     CU(cudaHostAlloc((void **)&c->h_cancel, sizeof(unsigned int), cudaHostAllocPortable));
     *c->h_cancel = 0;
@@ -76,17 +75,16 @@ int frt_create(frt_ctx **out, const int *devices, int n)
                 }
         const size_t wf_smem = (size_t)c->wf_slots * FRT_WF_SLOT_BYTES;
         const WfConfig &wc = wf_configs[c->wf_config];
-        for (int mode = 0; mode < 2; ++mode)
-            for (int cnt = 0; cnt < 2; ++cnt)
-            {
-                CU(cudaFuncSetAttribute(wc.kernel[mode][cnt], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
-                CU(cudaFuncSetAttribute(wf_other.kernel[mode][cnt], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
-            }
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wc.kernel[c->wf_mode][0], wc.threads, wf_smem));
+        for (int cnt = 0; cnt < 2; ++cnt)
+        {
+            CU(cudaFuncSetAttribute(wc.kernel[cnt], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
+            CU(cudaFuncSetAttribute(wf_other.kernel[cnt], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
+        }
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wc.kernel[0], wc.threads, wf_smem));
         if (per_sm < 1)
             return fail(nullptr, FRT_ERR_CUDA, "frt_create: k_wavefront does not fit an SM with %u slots per CTA", c->wf_slots);
         d.blocks_wavefront = per_sm * d.sms;
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_other.kernel[c->wf_mode][0], wf_other.threads, wf_smem));
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_other.kernel[0], wf_other.threads, wf_smem));
         d.blocks_wavefront_other = per_sm * d.sms; // 0: only the path integrator fits this FRT_WF_SLOTS
     }
     // peer access between every pair of the context's devices: the film reduce-scatter of frt_readback reads
@@ -329,7 +327,6 @@ int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *s)
     if (!ctx->have_wide8)
         for (Device &d : ctx->dev)
             if (d.d_nodes8) { cudaSetDevice(d.ordinal); cudaFree(d.d_nodes8); d.d_nodes8 = nullptr; }
-    v.prefetch = getenv("FRT_TUNE") ? (uint32_t)atoi(getenv("FRT_TUNE")) : 0u;
     uint32_t bsdf_types = 0;
     for (uint32_t i = 0; i < s->n_materials; ++i)
         if (s->materials[i].type != FRT_MAT_DIFFUSE_LIGHT) bsdf_types |= 1u << s->materials[i].type;

@@ -14,7 +14,6 @@
 #include <vector>
 #include "frt_shade.cuh"
 #include "frt_wavefront.cuh"
-#include "frt_wavefront_warp.cuh"
 #include "frt_wide8.cuh"
 #include "frt_sort.cuh"
 
@@ -60,16 +59,15 @@ struct frt_ctx
     bool peer_ok = true;
     DevScene host_view{}; // counts + camera; pointers filled per device
     uint32_t nx = 0, ny = 0;
-    unsigned int wf_slots = 1024; // slots per CTA (multiple of 32)
+    unsigned int wf_slots = 1280; // slots per CTA (multiple of 32): 185 KB of the SM's 228 KB; the rest stays L1 for the scene and the
+                                  // traversal stacks (1024 -> 1280: +2 % Cornell, +8 % veach_mi, -1 % teapot; 1568 leaves no L1: -25 %)
     int wf_config = 1;            // index into wf_configs[]: 512 threads, one CTA per SM (measured best)
-    int wf_mode = 1;              // 0 = CTA-wide pipeline (k_wavefront), 1 = warp-autonomous (k_wavefront_warp)
-    int wf_refill = 24;           // dynamic fetch threshold (lanes still traversing)
+    int wf_refill = 20;           // dynamic fetch threshold (lanes still traversing)
     int wf_sort = -1;             // bit 0: bin queued rays by where they start; bit 1: shade grouped by material;
                                   // -1 = bit 0 always, bit 1 when the scene has more than one BSDF type
     int trace_occ[2] = {2, 2};    // ray casting: index into {4, 6, 8, 12} CTAs per SM for closest / occlusion casts (a large
                                   // incoherent scene is latency-bound: 8 CTAs of 64 registers measured +25 % over 4 of 128)
     int trace_refill[2] = {24, -1}; // dynamic fetch threshold for closest / occlusion casts (-1: plain batches of 32)
-    int trace_step = 0;           // inner nodes per traversal round (0 = run to the next leaf)
     int wide8 = -1;               // ray casting over the 8-wide compressed nodes: -1 = scenes of >= wide8_min_tris triangles
     uint32_t wide8_min_tris = 1u << 16;
     bool have_wide8 = false;
@@ -251,14 +249,20 @@ __device__ __forceinline__ void frt_trace_count(Counters *ctr, unsigned int n_ra
 // them plain batches of 32 rays measured faster, kept.  Register budget: closest hit 4 CTAs / SM (no spills);
 // occlusion queries 8 (64 registers).
 // OCC = CTAs of 128 threads per SM the register budget is cut for (4: 128 registers, 6: 85, 8: 64, 12: 42).
-template <bool ANY, bool COUNT, int OCC>
-__global__ void __launch_bounds__(128, OCC) k_trace(DevScene sc, Counters *ctr, const float2 *rays, frt_hit *hits,
-                                                          const unsigned int *order, unsigned int n, int refill_below)
+// The first FRT_TRACE_SMEM_STACK stack entries of every thread live in shared memory (HybridStack).
+#define FRT_TRACE_SMEM_STACK 12
+template <bool ANY, bool COUNT, int OCC, int WIDE>
+__device__ __forceinline__ void frt_trace_body(const DevScene &sc, Counters *ctr, const float2 *rays, frt_hit *hits, const unsigned int *order,
+                                               const unsigned int n, const int refill_below)
 {
+    __shared__ uint2 shared_stack[FRT_TRACE_SMEM_STACK * 128];
+    uint2 overflow[(WIDE == 8 ? FRT_STACK8_SIZE : FRT_STACK_SIZE) - FRT_TRACE_SMEM_STACK];
+    HybridStack<FRT_TRACE_SMEM_STACK, 128> stk{shared_stack + threadIdx.x, overflow};
     unsigned int n_rays = 0, n_nodes = 0, n_tris = 0;
     TraceIo io{rays, hits, order, 0u};
     if (ANY && refill_below < 0)
     {
+        // plain batches of 32 rays: occlusion queries end early and carry little state
         while (true)
         {
             unsigned int base = 0;
@@ -268,8 +272,7 @@ __global__ void __launch_bounds__(128, OCC) k_trace(DevScene sc, Counters *ctr, 
             if (base + lane_id() >= n) continue;
             float3 o, d;
             io.load(base + lane_id(), o, d);
-            Walker<ANY, COUNT, 4, true> w;
-            uint2 stk[FRT_STACK_SIZE];
+            Walker<ANY, COUNT, WIDE, true> w;
             w.begin(sc, o, d);
             while (w.active) w.round(sc, stk, n_nodes, n_tris);
             io.store(sc, w);
@@ -277,8 +280,16 @@ __global__ void __launch_bounds__(128, OCC) k_trace(DevScene sc, Counters *ctr, 
         }
     }
     else
-        frt_persistent_trace<ANY, COUNT, TraceIo, 4, true>(sc, io, n, &ctr->trace_next, refill_below, n_rays, n_nodes, n_tris, sc.trace_step);
+        frt_persistent_trace<ANY, COUNT, TraceIo, HybridStack<FRT_TRACE_SMEM_STACK, 128>, WIDE, true>(
+            sc, io, stk, n, &ctr->trace_next, refill_below < 0 ? 0 : refill_below, n_rays, n_nodes, n_tris);
     frt_trace_count<ANY, COUNT>(ctr, n_rays, n_nodes, n_tris);
+}
+
+template <bool ANY, bool COUNT, int OCC>
+__global__ void __launch_bounds__(128, OCC) k_trace(DevScene sc, Counters *ctr, const float2 *rays, frt_hit *hits,
+                                                          const unsigned int *order, unsigned int n, int refill_below)
+{
+    frt_trace_body<ANY, COUNT, OCC, 4>(sc, ctr, rays, hits, order, n, refill_below);
 }
 
 // The same entry over the 8-wide compressed nodes (frt_wide8.cuh).
@@ -286,10 +297,7 @@ template <bool ANY, bool COUNT, int OCC>
 __global__ void __launch_bounds__(128, OCC) k_trace8(DevScene sc, Counters *ctr, const float2 *rays, frt_hit *hits,
                                                            const unsigned int *order, unsigned int n, int refill_below)
 {
-    unsigned int n_rays = 0, n_nodes = 0, n_tris = 0;
-    TraceIo io{rays, hits, order, 0u};
-    frt_persistent_trace8<ANY, COUNT>(sc, io, n, &ctr->trace_next, refill_below < 0 ? 0 : refill_below, n_rays, n_nodes, n_tris, sc.trace_step);
-    frt_trace_count<ANY, COUNT>(ctr, n_rays, n_nodes, n_tris);
+    frt_trace_body<ANY, COUNT, OCC, 8>(sc, ctr, rays, hits, order, n, refill_below);
 }
 
 // The launch shapes of the ray-cast kernels compiled into the library: [wide8][any][count][occupancy 4 / 6 / 8]
@@ -300,18 +308,20 @@ const TraceKernel trace_kernels[2][2][2][4] = {{{TRACE_OCC(k_trace, false, false
                                                {{TRACE_OCC(k_trace8, false, false), TRACE_OCC(k_trace8, false, true)},
                                                 {TRACE_OCC(k_trace8, true, false), TRACE_OCC(k_trace8, true, true)}}};
 
-// Launch shapes of the wavefront kernels compiled into the library (threads per CTA, CTAs per SM the register budget is
-// cut for); FRT_WF_CONFIG picks one, the default is the measured best.  Each shape exists as the CTA-wide pipeline
-// (k_wavefront: one pool per CTA, stages separated by __syncthreads) and as the warp-autonomous one (k_wavefront_warp:
-// every warp runs the pipeline on its slice of the pool); FRT_WF_MODE picks (0 = CTA-wide, 1 = warp-autonomous).
+// Launch shapes of k_wavefront compiled into the library (threads per CTA, CTAs per SM the register budget is cut
+// for); FRT_WF_CONFIG picks one, the default is the measured best (profiles/r01_sweep_launch_shapes.log, r02_wf_sweep*.log).
+// Measured and rejected in round 2 (profiles/r02_wf_sweep_warp_autonomous.log): a warp-autonomous pipeline — every warp
+// running generate / trace / shade on its own 64-slot slice, no CTA barrier — lost 40 % on Cornell and 65 % on
+// veach_mi (warps in different stages evict each other's code from the instruction caches, and 64 slots leave too few
+// paths per material to fill a warp), gained 5 % on the teapot.
 typedef void (*WfKernel)(const KernelArgs, const unsigned int, const int, const int);
 struct WfConfig
 {
     int threads, min_blocks;
-    WfKernel kernel[2][2]; // [mode][counting]
+    WfKernel kernel[2]; // [counting]
 };
-#define WF_CFG(T, B, O) {T, B, {{k_wavefront<false, T, B, O>, k_wavefront<true, T, B, O>}, {k_wavefront_warp<false, T, B, O>, k_wavefront_warp<true, T, B, O>}}}
-const WfConfig wf_configs[] = {WF_CFG(256, 2, false), WF_CFG(512, 1, false), WF_CFG(384, 1, false), WF_CFG(320, 2, false), WF_CFG(640, 1, false)};
+#define WF_CFG(T, B, O) {T, B, {k_wavefront<false, T, B, O>, k_wavefront<true, T, B, O>}}
+const WfConfig wf_configs[] = {WF_CFG(256, 2, false), WF_CFG(512, 1, false), WF_CFG(384, 1, false), WF_CFG(320, 2, false)};
 const int n_wf_configs = (int)(sizeof wf_configs / sizeof wf_configs[0]);
 // The general kernel: the integrators next to `path` (ao, normals_renderer, ass_1_renderer) and `path` over textured
 // surfaces.  Its own instantiation, so that the path kernel of the untextured scenes carries none of that code

@@ -15,11 +15,7 @@ struct DevScene
 {
     const float4 *nodes;       // 8 float4 per frt_bvh4_node
     const uint4 *nodes8;       // 6 uint4 per 8-wide compressed node (frt_wide8.cuh) or nullptr
-    uint32_t prefetch;         // ray casting: bit 0 = L2-prefetch the next-nearest child when it is pushed, bit 1 = L1-prefetch
-                               // the rest of a leaf's triangles when the leaf is entered, bit 2 = occlusion queries descend into the
-                               // nearest entered child first (FRT_TUNE)
     uint32_t node8_stride;     // uint4 per 8-wide node: 6 (96 B, packed) or 8 (128 B, one cache line each)
-    int trace_step;            // ray casting: inner nodes per round before the warp looks for idle lanes again
     const float4 *tris;        // 3 float4 per triangle
     const float4 *tri_normals; // 3 float4 per triangle or nullptr
     const float4 *spheres;     // 2 float4 per frt_sphere

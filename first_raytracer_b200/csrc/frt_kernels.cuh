@@ -68,15 +68,14 @@ __device__ __forceinline__ unsigned int warp_append(bool pred, unsigned int *cou
 // atomic per warp), so a warp is not held by its slowest ray.  (Letting lanes run several rounds between two
 // looks at the warp was measured: no gain.)  Io::load(item, o, d) fetches a ray,
 // Io::store(sc, walker) consumes the finished traversal; both run for the lanes of one refill together.
-template <bool ANY, bool COUNT, class Io, int WIDE = 4, bool RT = false>
-__device__ __forceinline__ void frt_persistent_trace(const DevScene &sc, Io &io, const unsigned int n_items, unsigned int *cursor,
+template <bool ANY, bool COUNT, class Io, class Stk, int WIDE = 4, bool RT = false>
+__device__ __forceinline__ void frt_persistent_trace(const DevScene &sc, Io &io, Stk &stk, const unsigned int n_items, unsigned int *cursor,
                                                      const int refill_below, unsigned int &n_rays, unsigned int &n_nodes,
-                                                     unsigned int &n_tris, const int max_nodes = 0x7FFFFFFF)
+                                                     unsigned int &n_tris)
 {
     if (n_items == 0) return;
     const unsigned int lane = lane_id();
     Walker<ANY, COUNT, WIDE, RT> w;
-    uint2 stk[WIDE == 8 ? FRT_STACK8_SIZE : FRT_STACK_SIZE];
     w.active = false;
     bool pending = false, more = true;
     while (true)
@@ -101,7 +100,7 @@ __device__ __forceinline__ void frt_persistent_trace(const DevScene &sc, Io &io,
         unsigned int act = __ballot_sync(0xFFFFFFFFu, w.active);
         while (act)
         {
-            if (w.active) w.round(sc, stk, n_nodes, n_tris, max_nodes);
+            if (w.active) w.round(sc, stk, n_nodes, n_tris);
             act = __ballot_sync(0xFFFFFFFFu, w.active);
             if (more && __popc(act) <= refill_below) break;
         }
@@ -112,14 +111,6 @@ __device__ __forceinline__ void frt_persistent_trace(const DevScene &sc, Io &io,
         }
         if (!more && act == 0) break;
     }
-}
-
-template <bool ANY, bool COUNT, class Io>
-__device__ __forceinline__ void frt_persistent_trace8(const DevScene &sc, Io &io, const unsigned int n_items, unsigned int *cursor,
-                                                      const int refill_below, unsigned int &n_rays, unsigned int &n_nodes,
-                                                      unsigned int &n_tris, const int max_nodes = 0x7FFFFFFF)
-{
-    frt_persistent_trace<ANY, COUNT, Io, 8, true>(sc, io, n_items, cursor, refill_below, n_rays, n_nodes, n_tris, max_nodes);
 }
 
 // Camera path number `idx` of the tile (sample idx / npix of pixel idx % npix) into slot `slot`.

@@ -209,9 +209,7 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
         if (resident < 1) return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: FRT_WF_SLOTS=%u leaves no room for this integrator's kernel", ctx->wf_slots);
         const unsigned int grid = (unsigned int)std::min<unsigned long long>((unsigned long long)resident, want);
         k_reset_tile<<<1, 1, 0, d.stream>>>(d.d_ctr, total);
-        // the warp-autonomous pipeline needs at least 32 slots per warp of the CTA
-        const int mode = (ctx->wf_mode && ctx->wf_slots / (unsigned int)(wc.threads / 32) >= 32u) ? 1 : 0;
-        wc.kernel[mode][count ? 1 : 0]<<<grid, wc.threads, smem, d.stream>>>(a, ctx->wf_slots, ctx->wf_refill,
+        wc.kernel[count ? 1 : 0]<<<grid, wc.threads, smem, d.stream>>>(a, ctx->wf_slots, ctx->wf_refill,
                                                                                ctx->wf_sort >= 0 ? ctx->wf_sort : (ctx->multi_bsdf ? 3 : 1));
         CU(cudaGetLastError());
         CU(cudaEventRecord(d.ev_end, d.stream));
@@ -372,8 +370,7 @@ int frt_trace_rays_device(frt_ctx *ctx, int dev, const void *d_rays, size_t n, v
     if (n == 0) { if (device_ms) *device_ms = 0; return FRT_OK; }
     Device &d = ctx->dev[dev];
     CU(cudaSetDevice(d.ordinal));
-    DevScene sc = device_view(ctx, d);
-    sc.trace_step = ctx->trace_step > 0 ? ctx->trace_step : 0x7FFFFFFF;
+    const DevScene sc = device_view(ctx, d);
     const bool count = ctx->flags & FRT_FLAG_COUNTERS, any_hit = mode & FRT_TRACE_ANY_HIT;
     const float2 *r = (const float2 *)d_rays;
     frt_hit *h = (frt_hit *)d_hits;

@@ -93,8 +93,39 @@ struct BestHit
 // to a leaf, test its primitives, pop the next postponed child), finish() gives the hit.  Splitting
 // the loop this way lets a persistent warp look at its lanes between rounds and hand finished
 // lanes a new ray (dynamic fetch) instead of idling until the slowest lane is done.
-// RT = the ray-cast entry's runtime knobs are compiled in (node budget per round, prefetches, the order occlusion
-// queries descend in: DevScene::trace_step / ::prefetch); the wavefront kernels instantiate RT = false and carry none.
+// The traversal's short stack of postponed children: x = child reference, y = bits of its entry distance (to drop it
+// at pop time once something closer was found).  LocalStack is a per-thread array in local memory: L1-resident for
+// the scenes that fit the caches (the wavefront kernels).  HybridStack keeps the first K entries of every thread in
+// SHARED memory (entry e of thread t at [e * threads + t]: conflict-free whatever the lanes' depths) and only deeper
+// ones in local memory: on a scene that streams gigabytes through L1 the local-memory stack lines are evicted
+// between push and pop (ncu, 10^7-triangle soup: 0.77 KB of DRAM WRITES per ray, and pops that wait for HBM).
+struct LocalStack
+{
+    uint2 *p;
+    __device__ __forceinline__ void push(int &sp, const uint2 v) { p[sp++] = v; }
+    __device__ __forceinline__ uint2 pop(int &sp) { return p[--sp]; }
+};
+template <int K, int THREADS>
+struct HybridStack
+{
+    uint2 *sm; // this thread's column of the CTA's shared stack area
+    uint2 *lm; // overflow (FRT_STACK_SIZE - K entries of local memory)
+    __device__ __forceinline__ void push(int &sp, const uint2 v)
+    {
+        if (sp < K) sm[sp * THREADS] = v; else lm[sp - K] = v;
+        ++sp;
+    }
+    __device__ __forceinline__ uint2 pop(int &sp)
+    {
+        --sp;
+        return sp < K ? sm[sp * THREADS] : lm[sp - K];
+    }
+};
+
+// RT = instantiated by the ray-cast entry (k_trace), where occlusion queries walk the children near-to-far exactly like
+// closest-hit queries (on the 10^7-triangle soup: 379 against 359 Mrays/s; the nearest entered leaf is the likeliest
+// to hold an occluder); the wavefront kernels (RT = false) keep the cheaper unordered occlusion walk, measured faster
+// on the scenes that fit the caches.
 template <bool ANY, bool COUNT, int WIDE = 4, bool RT = false>
 struct Walker
 {
@@ -139,9 +170,10 @@ struct Walker
 
     // ---- while-while, part 1 over the 4-wide nodes: descend through inner nodes (EMPTY carries the leaf bit and
     // ends the loop)
-    __device__ __forceinline__ void descend4(const DevScene &sc, uint2 *stk, unsigned int &n_nodes, int max_nodes)
+    template <class Stk>
+    __device__ __forceinline__ void descend4(const DevScene &sc, Stk &stk, unsigned int &n_nodes)
     {
-        for (int it = 0; (!RT || it < max_nodes) && !(cur & FRT_CHILD_LEAF); ++it)
+        while (!(cur & FRT_CHILD_LEAF))
         {
             // eight 128-bit loads, near/far planes picked by ray-direction sign
             const float4 *n = sc.nodes + 8 * (size_t)cur;
@@ -159,31 +191,15 @@ struct Walker
             const float tf1 = fminf(fminf(fx.y * idx - oox, fy.y * idy - ooy), fminf(fz.y * idz - ooz, tmax));
             const float tf2 = fminf(fminf(fx.z * idx - oox, fy.z * idy - ooy), fminf(fz.z * idz - ooz, tmax));
             const float tf3 = fminf(fminf(fx.w * idx - oox, fy.w * idy - ooy), fminf(fz.w * idz - ooz, tmax));
-            if (ANY && !(RT && (sc.prefetch & 8u))) // bit 3: occlusion queries walk exactly like closest-hit queries (sorted)
+            if (ANY && !RT)
             {
                 // an occlusion query looks at every child the segment enters unless an occluder turns up
                 // first, so the order is free: no sort, no entry distances on the stack
-                if (RT && (sc.prefetch & 4u))
-                {
-                    // nearest entered child first (an occluder close to the origin ends the query soonest: shadow rays
-                    // leave a surface whose neighbourhood is where most occluders sit), the others postponed unordered
-                    const uint32_t a0 = (tf0 >= tn0) ? ((__float_as_uint(tn0) & ~3u) | 0u) : 0xFFFFFFFFu;
-                    const uint32_t a1 = (tf1 >= tn1) ? ((__float_as_uint(tn1) & ~3u) | 1u) : 0xFFFFFFFFu;
-                    const uint32_t a2 = (tf2 >= tn2) ? ((__float_as_uint(tn2) & ~3u) | 2u) : 0xFFFFFFFFu;
-                    const uint32_t a3 = (tf3 >= tn3) ? ((__float_as_uint(tn3) & ~3u) | 3u) : 0xFFFFFFFFu;
-                    const uint32_t amin = min(min(a0, a1), min(a2, a3));
-                    if (a3 != 0xFFFFFFFFu && a3 != amin) stk[sp++] = make_uint2(ch.w, 0u);
-                    if (a2 != 0xFFFFFFFFu && a2 != amin) stk[sp++] = make_uint2(ch.z, 0u);
-                    if (a1 != 0xFFFFFFFFu && a1 != amin) stk[sp++] = make_uint2(ch.y, 0u);
-                    if (a0 != 0xFFFFFFFFu && a0 != amin) stk[sp++] = make_uint2(ch.x, 0u);
-                    cur = amin != 0xFFFFFFFFu ? frt_pick(ch, amin & 3u) : FRT_CHILD_EMPTY;
-                    continue;
-                }
                 uint32_t next = FRT_CHILD_EMPTY;
                 if (tf3 >= tn3) next = ch.w;
-                if (tf2 >= tn2) { if (next != FRT_CHILD_EMPTY) stk[sp++] = make_uint2(next, 0u); next = ch.z; }
-                if (tf1 >= tn1) { if (next != FRT_CHILD_EMPTY) stk[sp++] = make_uint2(next, 0u); next = ch.y; }
-                if (tf0 >= tn0) { if (next != FRT_CHILD_EMPTY) stk[sp++] = make_uint2(next, 0u); next = ch.x; }
+                if (tf2 >= tn2) { if (next != FRT_CHILD_EMPTY) stk.push(sp, make_uint2(next, 0u)); next = ch.z; }
+                if (tf1 >= tn1) { if (next != FRT_CHILD_EMPTY) stk.push(sp, make_uint2(next, 0u)); next = ch.y; }
+                if (tf0 >= tn0) { if (next != FRT_CHILD_EMPTY) stk.push(sp, make_uint2(next, 0u)); next = ch.x; }
                 cur = next;
                 continue;
             }
@@ -199,15 +215,9 @@ struct Walker
             a = min(k1, k3); b = max(k1, k3); k1 = a; k3 = b;
             a = min(k1, k2); b = max(k1, k2); k1 = a; k2 = b;
             // invalid keys sort last: push the far ones (farthest first), continue with the nearest
-            if (k3 != 0xFFFFFFFFu) stk[sp++] = make_uint2(frt_pick(ch, k3 & 3u), k3 & ~3u);
-            if (k2 != 0xFFFFFFFFu) stk[sp++] = make_uint2(frt_pick(ch, k2 & 3u), k2 & ~3u);
-            if (k1 != 0xFFFFFFFFu)
-            {
-                const uint32_t ref = frt_pick(ch, k1 & 3u);
-                stk[sp++] = make_uint2(ref, k1 & ~3u);
-                // the next-nearest child is the likeliest to be popped: pull it towards L2 while the nearest is walked
-                if (RT && (sc.prefetch & 1u) && !(ref & FRT_CHILD_LEAF)) asm volatile("prefetch.global.L2 [%0];" ::"l"(sc.nodes + 8 * (size_t)ref));
-            }
+            if (k3 != 0xFFFFFFFFu) stk.push(sp, make_uint2(frt_pick(ch, k3 & 3u), k3 & ~3u));
+            if (k2 != 0xFFFFFFFFu) stk.push(sp, make_uint2(frt_pick(ch, k2 & 3u), k2 & ~3u));
+            if (k1 != 0xFFFFFFFFu) stk.push(sp, make_uint2(frt_pick(ch, k1 & 3u), k1 & ~3u));
             cur = (k0 != 0xFFFFFFFFu) ? frt_pick(ch, k0 & 3u) : FRT_CHILD_EMPTY;
         }
     }
@@ -217,9 +227,10 @@ struct Walker
     // slab distance is q * (scale / d) + (origin / d - o / d): one FFMA per plane after three per node.  The
     // quantised boxes contain the float32 boxes of the 4-wide tree (floor / ceil), hits are decided by the same
     // triangle code, so results do not depend on which tree is walked.
-    __device__ __forceinline__ void descend8(const DevScene &sc, uint2 *stk, unsigned int &n_nodes, int max_nodes)
+    template <class Stk>
+    __device__ __forceinline__ void descend8(const DevScene &sc, Stk &stk, unsigned int &n_nodes)
     {
-        for (int it = 0; (!RT || it < max_nodes) && !(cur & FRT_CHILD_LEAF); ++it)
+        while (!(cur & FRT_CHILD_LEAF))
         {
             const uint4 *n = sc.nodes8 + sc.node8_stride * (size_t)cur;
             if (COUNT) ++n_nodes;
@@ -247,14 +258,14 @@ struct Walker
                 // an empty slot stores inverted planes (255 / 0) AND the EMPTY reference: never entered
                 key[k] = (tf >= tn && ref != FRT_CHILD_EMPTY) ? ((__float_as_uint(tn) & ~7u) | (uint32_t)k) : 0xFFFFFFFFu;
             }
-            if (ANY)
+            if (ANY && !RT)
             {
                 uint32_t next = FRT_CHILD_EMPTY;
 #pragma unroll
                 for (int k = 7; k >= 0; --k)
                     if (key[k] != 0xFFFFFFFFu)
                     {
-                        if (next != FRT_CHILD_EMPTY) stk[sp++] = make_uint2(next, 0u);
+                        if (next != FRT_CHILD_EMPTY) stk.push(sp, make_uint2(next, 0u));
                         next = k < 4 ? frt_pick(c0, k) : frt_pick(c1, k - 4);
                     }
                 cur = next;
@@ -277,11 +288,7 @@ struct Walker
                 {
                     const uint32_t slot = key[j] & 7u;
                     const uint32_t ref = slot < 4u ? frt_pick(c0, slot) : frt_pick(c1, slot - 4u);
-                    stk[sp++] = make_uint2(ref, key[j] & ~7u);
-                    // the node will be wanted when this entry is popped: pull it towards L2 now (latency, not bandwidth,
-                    // bounds a large incoherent scene)
-                    if (RT && (sc.prefetch & 1u) && j == 1 && !(ref & FRT_CHILD_LEAF))
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(sc.nodes8 + sc.node8_stride * (size_t)ref));
+                    stk.push(sp, make_uint2(ref, key[j] & ~7u));
                 }
             if (key[0] != 0xFFFFFFFFu)
             {
@@ -293,13 +300,10 @@ struct Walker
         }
     }
 
-    // max_nodes: inner nodes one round may visit before the caller looks at the warp again (large incoherent scenes:
-    // 1, so that idle lanes are refilled after every memory round trip; cache-resident scenes: unlimited)
-    __device__ __forceinline__ void round(const DevScene &sc, uint2 *stk, unsigned int &n_nodes, unsigned int &n_tris,
-                                          const int max_nodes = 0x7FFFFFFF)
+    template <class Stk>
+    __device__ __forceinline__ void round(const DevScene &sc, Stk &stk, unsigned int &n_nodes, unsigned int &n_tris)
     {
-        if (WIDE == 8) descend8(sc, stk, n_nodes, max_nodes); else descend4(sc, stk, n_nodes, max_nodes);
-        if (RT && !(cur & FRT_CHILD_LEAF)) return; // still inside the tree: the round ends at the node budget
+        if (WIDE == 8) descend8(sc, stk, n_nodes); else descend4(sc, stk, n_nodes);
 
         // ---- part 2: one leaf
         if (cur != FRT_CHILD_EMPTY)
@@ -307,14 +311,6 @@ struct Walker
             const uint32_t first = cur & FRT_LEAF_FIRST_MASK;
             const uint32_t count = ((cur >> FRT_LEAF_COUNT_SHIFT) & 15u) + 1u;
             const bool is_sphere = cur & FRT_CHILD_SPHERE;
-            if (RT && (sc.prefetch & 2u) && !is_sphere && count > 1u)
-            {
-                // the leaf's triangles are contiguous (48 B each) and tested one after the other: ask for the lines
-                // behind the first one now, so that the following tests do not each wait for HBM
-                const char *tp = reinterpret_cast<const char *>(sc.tris + 3 * (size_t)first);
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(tp + 128));
-                if (count > 5u) asm volatile("prefetch.global.L1 [%0];" ::"l"(tp + 256));
-            }
             for (uint32_t k = 0; k < count; ++k)
             {
                 const uint32_t prim = is_sphere ? ((first + k) | FRT_CHILD_SPHERE) : first + k;
@@ -412,7 +408,7 @@ struct Walker
         active = false;
         while (sp > 0)
         {
-            const uint2 e = stk[--sp];
+            const uint2 e = stk.pop(sp);
             if (__uint_as_float(e.y) <= tmax) { cur = e.x; active = true; break; }
         }
     }

@@ -27,6 +27,8 @@ struct WfShared
     unsigned int hist_mat[8];                                 // shade order: miss + the six material types
     unsigned long long base; // first sample index of this iteration's run
     unsigned int n_ext, n_free, n_shadow, n_new, cur_ext, cur_shadow, exhausted, cancelled;
+    unsigned int cancel_seen;  // frt_cancel's flag as the CTA's last warp read it during the previous shade stage
+    unsigned int shadow_first; // this iteration traces the shadow queue before the extension queue
 };
 
 __device__ __forceinline__ unsigned long long frt_globaltimer()
@@ -84,7 +86,9 @@ __device__ __forceinline__ void wf_trace_queue(const DevScene &sc, const PathPoo
                                                unsigned int &n_rays, unsigned int &n_nodes, unsigned int &n_tris)
 {
     WfQueueIo<ANY> io{lp, q, 0u};
-    frt_persistent_trace<ANY, COUNT>(sc, io, n_items, cursor, refill_below, n_rays, n_nodes, n_tris);
+    uint2 stack_mem[FRT_STACK_SIZE]; // local memory; L1-resident next to a scene that fits the caches
+    LocalStack stk{stack_mem};
+    frt_persistent_trace<ANY, COUNT>(sc, io, stk, n_items, cursor, refill_below, n_rays, n_nodes, n_tris);
 }
 
 // Statistics: one set of 64-bit atomics per warp; the per-thread counters restart from zero.
@@ -143,7 +147,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelA
     }
     if (tid == 0)
     {
-        sh.n_ext = 0; sh.n_free = P; sh.n_shadow = 0; sh.n_new = 0; sh.exhausted = 0;
+        sh.n_ext = 0; sh.n_free = P; sh.n_shadow = 0; sh.n_new = 0; sh.exhausted = 0; sh.cancel_seen = 0; sh.shadow_first = 0;
     }
     __syncthreads();
 
@@ -160,9 +164,13 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelA
             const unsigned int want = sh.n_free;
             unsigned long long base = total;
             // frt_cancel (viewer::to_exit, viewer.cpp:101-104; path.cpp:127 leaves its row loop): polled once per
-            // CTA iteration; a cancelled tile takes no more samples and drops the paths in flight
-            const bool cancelled = *(const volatile unsigned int *)&a.ctr->cancel_epoch >= a.epoch; // device memory: an L2 hit
+            // CTA iteration (by another warp, during the shade stage, so that nobody waits for the load here); a
+            // cancelled tile takes no more samples and drops the paths in flight
+            const bool cancelled = sh.cancel_seen != 0;
             sh.cancelled = cancelled;
+            // the two trace stages run back to back without a barrier, so only the second one's tail (its last rays,
+            // most lanes of the CTA idle) is exposed: put the stage that has been taking longer first
+            sh.shadow_first = t_con > t_ext ? 1u : 0u;
             if (want && !sh.exhausted && !cancelled)
             {
                 base = atomicAdd(&a.ctr->next_sample, (unsigned long long)want);
@@ -189,15 +197,30 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_wavefront(const KernelA
         if (tid == 0) { const unsigned long long t = frt_globaltimer(); t_gen += t - t0; t0 = t; }
 
         // ---- extend + connect -----------------------------------------------------------------
-        wf_trace_queue<false, COUNT>(a.sc, lp, ext_q, n_ext, &sh.cur_ext, refill_below, n_closest, n_nodes, n_tris);
-        if (tid == 0) { const unsigned long long t = frt_globaltimer(); t_ext += t - t0; t0 = t; }
-        wf_trace_queue<true, COUNT>(a.sc, lp, shadow_q, n_sh, &sh.cur_shadow, refill_below, n_shadow_rays, n_nodes, n_tris);
+        const bool shadow_first = sh.shadow_first != 0;
+#pragma unroll 1
+        for (int pass = 0; pass < 2; ++pass) // a loop, so that each trace loop is compiled into the kernel once
+        {
+            if ((pass == 0) == shadow_first)
+                wf_trace_queue<true, COUNT>(a.sc, lp, shadow_q, n_sh, &sh.cur_shadow, refill_below, n_shadow_rays, n_nodes, n_tris);
+            else
+                wf_trace_queue<false, COUNT>(a.sc, lp, ext_q, n_ext, &sh.cur_ext, refill_below, n_closest, n_nodes, n_tris);
+            if (pass == 0 && tid == 0)
+            {
+                const unsigned long long t = frt_globaltimer();
+                if (shadow_first) t_con += t - t0; else t_ext += t - t0;
+                t0 = t;
+            }
+        }
         __syncthreads();
         if (tid == 0)
         {
             sh.n_ext = 0; sh.n_free = 0; sh.n_shadow = 0;
-            const unsigned long long t = frt_globaltimer(); t_con += t - t0; t0 = t;
+            const unsigned long long t = frt_globaltimer();
+            if (shadow_first) t_ext += t - t0; else t_con += t - t0;
+            t0 = t;
         }
+        if (tid == THREADS - 32) sh.cancel_seen = *(const volatile unsigned int *)&a.ctr->cancel_epoch >= a.epoch; // device memory: an L2 hit
         __syncthreads();
 
         // ---- shade + queue compaction -----------------------------------------------------------
