@@ -426,7 +426,7 @@ def config_soup(rig: Rig, n_tri: int, n_rays: int, peaks):
                 rig.ctx.trace_device(rays.data_ptr(), n, hits2.data_ptr(), any_hit, sort=True)
             nodes = (c1["node_visits"] - c0["node_visits"]) / sub
             tris = (c1["tri_tests"] - c0["tri_tests"]) / sub
-            node_bytes = 96.0 if n_tri >= 65536 else 128.0
+            node_bytes = 96.0 if os.environ.get("FRT_WIDE8") == "1" else 128.0
             b_ray = node_bytes * nodes + 48.0 * tris + 24.0 + 16.0  # node + triangle fetches, ray in (24 B), hit out (16 B)
             gbs = n_rays * b_ray / (ms * 1e-3) / 1e9 / rig.world  # per GPU
             cast = {"query": label, "order": "morton (device sort inside)" if sort else "as given (incoherent)",

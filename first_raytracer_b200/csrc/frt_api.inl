@@ -44,7 +44,6 @@ int frt_create(frt_ctx **out, const int *devices, int n)
     if (const char *s = getenv("FRT_TRACE_REFILL")) c->trace_refill[0] = std::min(31, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_TRACE_REFILL_ANY")) c->trace_refill[1] = std::min(31, std::max(-1, atoi(s)));
 
-    if (const char *s = getenv("FRT_WIDE8_MIN_TRIS")) c->wide8_min_tris = (uint32_t)std::max(0ll, atoll(s));
     CU(cudaHostAlloc((void **)&c->h_cancel, sizeof(unsigned int), cudaHostAllocPortable));
     *c->h_cancel = 0;
     for (int i = 0; i < n; ++i)
@@ -288,7 +287,10 @@ int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *s)
     // large scenes: ray casting walks 8-wide compressed nodes derived from the 4-wide ones (frt_wide8.cuh)
     ctx->have_wide8 = false;
     ctx->n_nodes8 = 0;
-    const bool want8 = ctx->wide8 >= 0 ? ctx->wide8 != 0 : s->n_tris >= ctx->wide8_min_tris;
+    // Opt-in (FRT_WIDE8=1): on the 10^7-triangle soup the 8-wide walk fetches 25 % fewer nodes at 3/4 of the bytes each but
+    // measured 15 % slower than the 4-wide one (492 vs 589 Mrays/s closest hit; profiles/r02_soup_sweep.log) — the byte
+    // decode and the 8-key sort cost more issue slots than the shorter dependent chain saves.
+    const bool want8 = ctx->wide8 > 0;
     if (want8 && s->n_nodes)
     {
         std::vector<uint32_t> words;

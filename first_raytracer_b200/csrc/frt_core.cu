@@ -68,8 +68,7 @@ struct frt_ctx
     int trace_occ[2] = {2, 2};    // ray casting: index into {4, 6, 8, 12} CTAs per SM for closest / occlusion casts (a large
                                   // incoherent scene is latency-bound: 8 CTAs of 64 registers measured +25 % over 4 of 128)
     int trace_refill[2] = {24, -1}; // dynamic fetch threshold for closest / occlusion casts (-1: plain batches of 32)
-    int wide8 = -1;               // ray casting over the 8-wide compressed nodes: -1 = scenes of >= wide8_min_tris triangles
-    uint32_t wide8_min_tris = 1u << 16;
+    int wide8 = 0;                // ray casting over the 8-wide compressed nodes (FRT_WIDE8=1): off by default, measured slower
     bool have_wide8 = false;
     uint32_t n_nodes8 = 0;
     bool multi_bsdf = false;

@@ -264,8 +264,8 @@ FRT_API int frt_stream_handle(frt_ctx *ctx, int dev, void **stream);
  * calls).  Buffers from frt_host_alloc (or any pinned memory) are copied asynchronously at link speed; pageable ones
  * go through one host thread per device.  FRT_TRACE_SORT: the rays are first put in Morton order of (origin cell,
  * direction octant) by a device radix sort — only the order they are traced in changes, every hit lands at its ray's
- * index.  `device_ms` (may be NULL) = sort + kernel time, max over devices.  Scenes of >= 65 536 triangles are walked
- * over 8-wide compressed nodes derived at upload (same hits; FRT_WIDE8=0/1 forces the choice). */
+ * index.  `device_ms` (may be NULL) = sort + kernel time, max over devices.  With FRT_WIDE8=1 in the environment the
+ * casts walk 8-wide compressed nodes derived at upload (same hits; measured slower than the 4-wide walk, off by default). */
 #define FRT_TRACE_ANY_HIT 1
 #define FRT_TRACE_SORT 2
 FRT_API int frt_trace_rays(frt_ctx *ctx, const frt_ray *rays, size_t n, frt_hit *hits, int mode, double *device_ms);
