@@ -33,8 +33,11 @@ int frt_create(frt_ctx **out, const int *devices, int n)
     std::unique_ptr<frt_ctx, void (*)(frt_ctx *)> guard(new frt_ctx, frt_destroy);
     frt_ctx *c = guard.get();
     c->dev.resize(n);
-    if (const char *s = getenv("FRT_WF_SLOTS")) c->wf_slots = (unsigned int)std::min(1568, std::max(32, atoi(s) / 32 * 32));
-    if (const char *s = getenv("FRT_WF_CONFIG")) c->wf_config = std::min(n_wf_configs - 1, std::max(0, atoi(s)));
+    // FRT_WF_SLOTS / FRT_WF_CONFIG force ONE shape for every scene (the sweeps of scripts/wf_sweep.py)
+    if (const char *s = getenv("FRT_WF_SLOTS"))
+        c->wf_slots = c->wf_slots_of[0] = c->wf_slots_of[1] = (unsigned int)std::min(1568, std::max(32, atoi(s) / 32 * 32));
+    if (const char *s = getenv("FRT_WF_CONFIG")) c->wf_config[0] = c->wf_config[1] = std::min(n_wf_configs - 1, std::max(0, atoi(s)));
+    if (const char *s = getenv("FRT_WF_BIG_SCENE")) c->wf_big_scene_bytes = (size_t)std::max(0ll, atoll(s));
     if (const char *s = getenv("FRT_WF_SORT")) c->wf_sort = atoi(s) & 3;
     if (const char *s = getenv("FRT_WF_REFILL")) c->wf_refill = std::min(31, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_WIDE8")) c->wide8 = atoi(s) ? 1 : 0;
@@ -72,17 +75,23 @@ int frt_create(frt_ctx **out, const int *devices, int n)
                     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_kernels[w8][any][0][occ], 128, 0));
                     d.blocks_trace[w8][any][occ] = std::max(1, per_sm) * d.sms;
                 }
-        const size_t wf_smem = (size_t)c->wf_slots * FRT_WF_SLOT_BYTES;
-        const WfConfig &wc = wf_configs[c->wf_config];
-        for (int cnt = 0; cnt < 2; ++cnt)
+        for (int shape = 0; shape < 2; ++shape)
         {
-            CU(cudaFuncSetAttribute(wc.kernel[cnt], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
-            CU(cudaFuncSetAttribute(wf_other.kernel[cnt], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
+            const size_t smem = (size_t)c->wf_slots_of[shape] * FRT_WF_SLOT_BYTES;
+            const WfConfig &wc = wf_configs[c->wf_config[shape]];
+            // the attribute is per kernel: when both shapes use one kernel it must cover the larger pool
+            const size_t smem_max = c->wf_config[0] == c->wf_config[1]
+                                        ? (size_t)std::max(c->wf_slots_of[0], c->wf_slots_of[1]) * FRT_WF_SLOT_BYTES : smem;
+            for (int cnt = 0; cnt < 2; ++cnt)
+                CU(cudaFuncSetAttribute(wc.kernel[cnt], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
+            CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wc.kernel[0], wc.threads, smem));
+            if (per_sm < 1)
+                return fail(nullptr, FRT_ERR_CUDA, "frt_create: k_wavefront does not fit an SM with %u slots per CTA", c->wf_slots_of[shape]);
+            d.blocks_wavefront[shape] = per_sm * d.sms;
         }
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wc.kernel[0], wc.threads, wf_smem));
-        if (per_sm < 1)
-            return fail(nullptr, FRT_ERR_CUDA, "frt_create: k_wavefront does not fit an SM with %u slots per CTA", c->wf_slots);
-        d.blocks_wavefront = per_sm * d.sms;
+        const size_t wf_smem = (size_t)c->wf_slots * FRT_WF_SLOT_BYTES;
+        for (int cnt = 0; cnt < 2; ++cnt)
+            CU(cudaFuncSetAttribute(wf_other.kernel[cnt], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wf_smem));
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_other.kernel[0], wf_other.threads, wf_smem));
         d.blocks_wavefront_other = per_sm * d.sms; // 0: only the path integrator fits this FRT_WF_SLOTS
     }
@@ -333,6 +342,7 @@ int frt_upload_scene(frt_ctx *ctx, const frt_scene_desc *s)
     for (uint32_t i = 0; i < s->n_materials; ++i)
         if (s->materials[i].type != FRT_MAT_DIFFUSE_LIGHT) bsdf_types |= 1u << s->materials[i].type;
     ctx->multi_bsdf = (bsdf_types & (bsdf_types - 1)) != 0;
+    ctx->scene_bytes = (size_t)s->n_nodes * sizeof(frt_bvh4_node) + (size_t)s->n_tris * 48 + (size_t)s->n_spheres * sizeof(frt_sphere);
     ctx->have_scene = true;
     return FRT_OK;
 }

@@ -41,7 +41,7 @@ struct Device
     size_t trace_cap = 0, sort_cap = 0;
     int sms = 0;
     int blocks_trace[2][2][4] = {}; // resident CTAs of trace_kernels[wide8][any][.][occupancy]
-    int blocks_wavefront = 0, blocks_wavefront_other = 0;
+    int blocks_wavefront[2] = {0, 0}, blocks_wavefront_other = 0; // [0] small scene shape, [1] large scene shape
     unsigned int wf_ctas_launched = 0;
     bool rendered = false;
     unsigned long long launches = 0;
@@ -59,9 +59,16 @@ struct frt_ctx
     bool peer_ok = true;
     DevScene host_view{}; // counts + camera; pointers filled per device
     uint32_t nx = 0, ny = 0;
-    unsigned int wf_slots = 1280; // slots per CTA (multiple of 32): 185 KB of the SM's 228 KB; the rest stays L1 for the scene and the
+    unsigned int wf_slots = 1280; // general kernel (ao / normals / direct / textured): slots per CTA (multiple of 32): 185 KB of the SM's 228 KB; the rest stays L1 for the scene and the
                                   // traversal stacks (1024 -> 1280: +2 % Cornell, +8 % veach_mi, -1 % teapot; 1568 leaves no L1: -25 %)
-    int wf_config = 1;            // index into wf_configs[]: 512 threads, one CTA per SM (measured best)
+    // The path kernel's launch shape follows the size of the scene (profiles/r02_wf_sweep_pool_size.log): a scene that fits
+    // the SM's L1 beside the pool (Cornell, veach_mi: a few KB) runs fastest as ONE 512-thread CTA with the largest pool;
+    // a mesh scene (teapot: 0.2 MB of nodes and triangles) wants the L1 for the tree, and two 256-thread CTAs of 512
+    // slots each hide its node fetches better (+8 %).  Index 0 = small, 1 = large.
+    int wf_config[2] = {1, 0};                // index into wf_configs[]
+    unsigned int wf_slots_of[2] = {1280, 512}; // slots per CTA of the path kernel, per shape
+    size_t wf_big_scene_bytes = 128u << 10;   // nodes + triangles + spheres above this: the large-scene shape
+    size_t scene_bytes = 0;
     int wf_refill = 20;           // dynamic fetch threshold (lanes still traversing)
     int wf_sort = -1;             // bit 0: bin queued rays by where they start; bit 1: shade grouped by material;
                                   // -1 = bit 0 always, bit 1 when the scene has more than one BSDF type

@@ -199,17 +199,20 @@ int frt_render_tile(frt_ctx *ctx, const frt_tile *t)
         if (!d.rendered) CU(cudaEventRecord(d.ev_begin, d.stream));
         d.rendered = true;
         // the whole tile is one persistent launch: path state lives in the CTAs' shared memory
-        const size_t smem = (size_t)ctx->wf_slots * FRT_WF_SLOT_BYTES;
-        // no more CTAs than can be kept busy: one CTA-iteration consumes up to wf_slots samples
-        const unsigned long long want = (total + ctx->wf_slots - 1) / ctx->wf_slots;
         // the general kernel: the integrators next to `path`, and `path` itself over textured surfaces
         const bool other = t->integrator != FRT_INTEGRATOR_PATH || ctx->host_view.n_textures != 0;
-        const WfConfig &wc = other ? wf_other : wf_configs[ctx->wf_config];
-        const int resident = other ? d.blocks_wavefront_other : d.blocks_wavefront;
-        if (resident < 1) return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: FRT_WF_SLOTS=%u leaves no room for this integrator's kernel", ctx->wf_slots);
+        // the path kernel's launch shape follows the scene's size (frt_ctx::wf_config)
+        const int shape = ctx->scene_bytes > ctx->wf_big_scene_bytes ? 1 : 0;
+        const unsigned int slots = other ? ctx->wf_slots : ctx->wf_slots_of[shape];
+        const size_t smem = (size_t)slots * FRT_WF_SLOT_BYTES;
+        // no more CTAs than can be kept busy: one CTA-iteration consumes up to `slots` samples
+        const unsigned long long want = (total + slots - 1) / slots;
+        const WfConfig &wc = other ? wf_other : wf_configs[ctx->wf_config[shape]];
+        const int resident = other ? d.blocks_wavefront_other : d.blocks_wavefront[shape];
+        if (resident < 1) return fail(ctx, FRT_ERR_INVALID, "frt_render_tile: FRT_WF_SLOTS=%u leaves no room for this integrator's kernel", slots);
         const unsigned int grid = (unsigned int)std::min<unsigned long long>((unsigned long long)resident, want);
         k_reset_tile<<<1, 1, 0, d.stream>>>(d.d_ctr, total);
-        wc.kernel[count ? 1 : 0]<<<grid, wc.threads, smem, d.stream>>>(a, ctx->wf_slots, ctx->wf_refill,
+        wc.kernel[count ? 1 : 0]<<<grid, wc.threads, smem, d.stream>>>(a, slots, ctx->wf_refill,
                                                                                ctx->wf_sort >= 0 ? ctx->wf_sort : (ctx->multi_bsdf ? 3 : 1));
         CU(cudaGetLastError());
         CU(cudaEventRecord(d.ev_end, d.stream));

@@ -5,11 +5,11 @@ capture given, the kernel's DRAM bytes, L2 bytes, issue-slot utilisation, active
 
 A `.ncu-rep` is read through `ncu -i --page raw --csv`; a `.csv` is the --metrics log of scripts/gpu_traffic.sh (its DRAM
 bytes and duration override the rep's: that pass profiles the very launch the bench times)."""
-import csv, io, json, subprocess, sys
+import csv, io, json, os, subprocess, sys
 from pathlib import Path
 
 REPO = Path(__file__).resolve().parent.parent
-OUT = REPO / "profiles" / "r02_ncu_metrics.json"
+OUT = Path(os.environ.get("NCU_METRICS_OUT") or REPO / "profiles" / "r02_ncu_metrics.json")  # the GPU box writes into gpurun_out/
 
 
 def from_rep(path):
@@ -35,6 +35,13 @@ def from_rep(path):
            "warps_active_pct": val("sm__warps_active.avg.pct_of_peak_sustained_active"), "registers": val("launch__registers_per_thread"),
            "l1_hit_pct": val("l1tex__t_sector_hit_rate.pct"), "l2_hit_pct": val("lts__t_sector_hit_rate.pct"),
            "dram_throughput_pct": val("dram__throughput.avg.pct_of_peak_sustained_elapsed")}
+    if out["lts_bytes"] is None:  # --set full on this ncu carries sectors / the L2->crossbar rate, not lts__t_bytes
+        if val("lts__t_sectors.sum") is not None:
+            out["lts_bytes"], out["lts_bytes_from"] = 32.0 * val("lts__t_sectors.sum"), "lts__t_sectors.sum x 32 B"
+        elif val("derived__lts__lts2xbar_bytes.sum.per_second", scale_unit=False) is not None and out["duration_s"]:
+            u = units[idx["derived__lts__lts2xbar_bytes.sum.per_second"]]
+            rate = val("derived__lts__lts2xbar_bytes.sum.per_second", scale_unit=False) * {"Gbyte/s": 1e9, "Tbyte/s": 1e12, "Mbyte/s": 1e6, "Kbyte/s": 1e3}.get(u, 1.0)
+            out["lts_bytes"], out["lts_bytes_from"] = rate * out["duration_s"], "derived__lts__lts2xbar_bytes.sum.per_second x duration (L2 -> SM only)"
     clk = val("smsp__cycles_elapsed.avg.per_second", scale_unit=False)
     if clk is not None:
         u = units[idx["smsp__cycles_elapsed.avg.per_second"]]
