@@ -20,6 +20,7 @@ FRTH_CANCELLED = 1
 FRT_FLAG_COUNTERS = 1
 FRT_TRACE_ANY_HIT = 1
 FRT_TRACE_SORT = 2
+TRACE_NOALLOC_MAX_RAYS = 1 << 20  # FRT_TRACE_NOALLOC_MAX_RAYS
 
 # every exported symbol of include/frt.h and include/frt_host.h (tests check the libraries export them)
 FRT_SYMBOLS = [
@@ -27,6 +28,7 @@ FRT_SYMBOLS = [
     "frt_upload_scene", "frt_render_tile", "frt_clear_film", "frt_readback", "frt_film_device_ptr",
     "frt_trace_rays", "frt_trace_rays_device", "frt_stream_handle", "frt_get_counters", "frt_restore_film",
     "frt_readback_film", "frt_cancel", "frt_poll", "frt_host_alloc", "frt_host_free", "frt_build_wide8",
+    "frt_trace_rays_device_noalloc",
 ]
 FRTH_SYMBOLS = [
     "frth_last_error", "frth_scene_create", "frth_scene_create_soup", "frth_scene_destroy",
@@ -137,6 +139,7 @@ def load_libs():
             "frt_stream_handle": (i32, [vp, i32, C.POINTER(vp)]),
             "frt_trace_rays": (i32, [vp, vp, sz, vp, i32, C.POINTER(dbl)]),
             "frt_trace_rays_device": (i32, [vp, i32, vp, sz, vp, i32, C.POINTER(dbl)]),
+            "frt_trace_rays_device_noalloc": (i32, [vp, i32, vp, sz, vp, i32, C.POINTER(dbl)]),
             "frt_readback_film": (i32, [vp, u64, vp, vp, vp, C.POINTER(frt_stats)]),
             "frt_cancel": (i32, [vp]),
             "frt_poll": (i32, [vp, C.POINTER(i32)]),
@@ -370,6 +373,13 @@ class Context:
         ms = C.c_double()
         mode = (FRT_TRACE_ANY_HIT if any_hit else 0) | (FRT_TRACE_SORT if sort else 0)
         self._check(self._frt.frt_trace_rays_device(self.handle, dev, d_rays_ptr, n, d_hits_ptr, mode, C.byref(ms)), "frt_trace_rays_device")
+        return ms.value
+
+    def trace_device_noalloc(self, d_rays_ptr: int, n: int, d_hits_ptr: int, any_hit: bool = False, dev: int = 0) -> float:
+        """frt_trace_rays_device_noalloc: the Morton-ordered cast over the library's static scratch (n <= TRACE_NOALLOC_MAX_RAYS)."""
+        ms = C.c_double()
+        self._check(self._frt.frt_trace_rays_device_noalloc(self.handle, dev, d_rays_ptr, n, d_hits_ptr,
+                                                            FRT_TRACE_ANY_HIT if any_hit else 0, C.byref(ms)), "frt_trace_rays_device_noalloc")
         return ms.value
 
     def readback_film(self, ns: int):

@@ -67,6 +67,8 @@ int frt_create(frt_ctx **out, const int *devices, int n)
         CU(cudaMemset(d.d_ctr, 0, sizeof(Counters)));
         CU(cudaMallocHost((void **)&d.h_ctr, sizeof(Counters)));
         memset(d.h_ctr, 0, sizeof(Counters));
+        // frt_trace_rays_device_noalloc: where the static scratch lives on THIS device
+        CU(cudaGetSymbolAddress((void **)&d.d_noalloc_scratch, g_noalloc_sort_scratch));
         int per_sm = 0;
         for (int w8 = 0; w8 < 2; ++w8)
             for (int any = 0; any < 2; ++any)

@@ -17,6 +17,13 @@
 #include "frt_wide8.cuh"
 #include "frt_sort.cuh"
 
+// Scratch of frt_trace_rays_device_noalloc (include/frt.h): the sort's keys, ray indices and histograms for up to
+// FRT_TRACE_NOALLOC_MAX_RAYS rays, part of the library's device image so that the call allocates nothing.  In host code
+// this NAME is only a stand-in for the symbol: frt_create asks every device for its address (cudaGetSymbolAddress,
+// with that device current) and the launches get that pointer.
+#define FRT_NOALLOC_SCRATCH_WORDS (4u * FRT_TRACE_NOALLOC_MAX_RAYS + 256u * FRT_SORT_MAX_BLOCKS)
+static __device__ __align__(256) uint32_t g_noalloc_sort_scratch[FRT_NOALLOC_SCRATCH_WORDS];
+
 namespace {
 
 thread_local std::string g_create_error;
@@ -38,6 +45,7 @@ struct Device
     size_t film_floats = 0;
     // ray casting: device buffers kept between calls (grow-only), sort scratch
     void *d_rays = nullptr, *d_hits = nullptr, *d_sort = nullptr;
+    uint32_t *d_noalloc_scratch = nullptr; // this device's address of g_noalloc_sort_scratch (never freed: not an allocation)
     size_t trace_cap = 0, sort_cap = 0;
     int sms = 0;
     int blocks_trace[2][2][4] = {}; // resident CTAs of trace_kernels[wide8][any][.][occupancy]

@@ -410,6 +410,46 @@ int frt_trace_rays_device(frt_ctx *ctx, int dev, const void *d_rays, size_t n, v
     return FRT_OK;
 }
 
+// The Morton-ordered cast with the sort's scratch in g_noalloc_sort_scratch: nothing here (or below it) allocates —
+// stream-ordered memset, event records and kernel launches only.  A separate body on purpose: frt_trace_rays_device
+// stays as it is.
+int frt_trace_rays_device_noalloc(frt_ctx *ctx, int dev, const void *d_rays, size_t n, void *d_hits, int mode, double *device_ms)
+{
+    if (!ctx || dev < 0 || dev >= (int)ctx->dev.size()) return FRT_ERR_INVALID;
+    if (!ctx->have_scene) return fail(ctx, FRT_ERR_STATE, "frt_trace_rays_device_noalloc: no scene uploaded");
+    if (mode & ~(FRT_TRACE_ANY_HIT | FRT_TRACE_SORT)) return fail(ctx, FRT_ERR_INVALID, "frt_trace_rays_device_noalloc: unknown mode bits %d", mode);
+    if (n > FRT_TRACE_NOALLOC_MAX_RAYS)
+        return fail(ctx, FRT_ERR_INVALID, "frt_trace_rays_device_noalloc: %zu rays exceed the static scratch (FRT_TRACE_NOALLOC_MAX_RAYS = %u); "
+                                          "split the batch or use frt_trace_rays_device", n, (unsigned int)FRT_TRACE_NOALLOC_MAX_RAYS);
+    if (n && (!d_rays || !d_hits)) return fail(ctx, FRT_ERR_INVALID, "frt_trace_rays_device_noalloc: NULL buffer");
+    if (n == 0) { if (device_ms) *device_ms = 0; return FRT_OK; }
+    Device &d = ctx->dev[dev];
+    if (!d.d_noalloc_scratch) return fail(ctx, FRT_ERR_STATE, "frt_trace_rays_device_noalloc: the scratch symbol was not resolved on device %d", d.ordinal);
+    CU(cudaSetDevice(d.ordinal));
+    const DevScene sc = device_view(ctx, d);
+    const bool count = ctx->flags & FRT_FLAG_COUNTERS, any_hit = mode & FRT_TRACE_ANY_HIT;
+    const uint32_t *order = nullptr;
+    // the one word that must start at zero: the persistent kernel's work cursor.  Keys, indices and histograms are
+    // written in full by each pass before they are read, so the previous call's contents do not matter.
+    CU(cudaMemsetAsync(&d.d_ctr->trace_next, 0, sizeof(unsigned int), d.stream));
+    CU(cudaEventRecord(d.ev_t0, d.stream));
+    CU(frt_sort_rays((const float2 *)d_rays, (unsigned int)n, ctx->bounds_lo, ctx->bounds_hi, d.d_noalloc_scratch, &order, d.stream, &d.launches));
+    const int a = any_hit ? 1 : 0, w8 = ctx->have_wide8 ? 1 : 0, occ = ctx->trace_occ[a];
+    trace_kernels[w8][a][count ? 1 : 0][occ]<<<d.blocks_trace[w8][a][occ], 128, 0, d.stream>>>(sc, d.d_ctr, (const float2 *)d_rays, (frt_hit *)d_hits, order,
+                                                                                         (unsigned int)n, ctx->trace_refill[a]);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(d.ev_t1, d.stream));
+    d.launches += 1;
+    if (device_ms)
+    {
+        CU(cudaEventSynchronize(d.ev_t1));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, d.ev_t0, d.ev_t1));
+        *device_ms = ms;
+    }
+    return FRT_OK;
+}
+
 int frt_trace_rays(frt_ctx *ctx, const frt_ray *rays, size_t n, frt_hit *hits, int mode, double *device_ms)
 {
     if (!ctx || (n && (!rays || !hits))) return FRT_ERR_INVALID;

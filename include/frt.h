@@ -275,6 +275,22 @@ FRT_API int frt_trace_rays(frt_ctx *ctx, const frt_ray *rays, size_t n, frt_hit 
 FRT_API int frt_trace_rays_device(frt_ctx *ctx, int dev, const void *d_rays, size_t n, void *d_hits, int mode,
                           double *device_ms);
 
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * frt_trace_rays_device with FRT_TRACE_SORT (implied here: the Morton-ordered cast is the kernel sequence that needs
+ * scratch — keys, ray indices and radix histograms), but the scratch is a fixed array in the library's device image
+ * instead of a grow-only cudaMalloc: the call allocates NOTHING (no cudaMalloc / cudaFree / allocating library
+ * routine); the caller passes device-resident rays and hits of device `dev` as before.  Same hits as
+ * frt_trace_rays_device, bit for bit.
+ *   - n > FRT_TRACE_NOALLOC_MAX_RAYS is rejected with FRT_ERR_INVALID and a message in frt_last_error.
+ *   - The array (17 MiB) is held by every GPU that loads libfrt.so until the process exits.
+ *   - Every call on a GPU shares the one array, which keeps the previous call's contents (each pass overwrites what
+ *     it reads; the work cursor is cleared per call).  Calls that OVERLAP on the same GPU — two contexts, two host
+ *     threads, or one ordinal listed twice in a context — race on it: serialise them. */
+#define FRT_TRACE_NOALLOC_MAX_RAYS (1u << 20)
+FRT_API int frt_trace_rays_device_noalloc(frt_ctx *ctx, int dev, const void *d_rays, size_t n, void *d_hits, int mode,
+                                          double *device_ms);
+
 /* Pinned host memory for ray / hit / film buffers (cudaHostAlloc, portable); NULL on failure. */
 FRT_API void *frt_host_alloc(size_t bytes);
 FRT_API void frt_host_free(void *p);
