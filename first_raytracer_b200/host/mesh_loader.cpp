@@ -1,14 +1,30 @@
 // OBJ / MTL import for the host layer.  Same interface as the reference's mesh_loader
 // (mesh_loader.h:18-22) and create_triangle_mesh factories (triangle.h:189-190, triangle.cpp:9-60)
-// but self-contained: the reference delegates parsing to Assimp 5.0.1, which is not part of this
-// product.  What is kept from the reference is what decides pixel values:
-//   * one triangle_mesh per (group, material) in first-appearance order, polygons fan-triangulated
-//   * MTL → material mapping of mesh_loader.cpp:59-112 (Ke → diffuse_light; Ks & d<1 →
-//     dielectric; Ks → modified_phong; else lambertian; colours through FromSrgb except Ke)
-//   * angle-weighted vertex normals when the file has none (mesh_loader.cpp:114-155)
+// but self-contained: the reference delegates parsing to its vendored Assimp 5.0.1
+// (mesh_loader.cpp:9: TargetRealtime_Fast without GenNormals, plus GenSmoothNormals), which is not
+// part of this product.  What decides pixel values is restated here and checked against the
+// reference's own loader (oracle/_ref/frt_ref_assimp, tests/test_host.py):
+//   * numbers are read the way Assimp's fast_atoreal_move<float> reads them (fast_atof.h:232-338):
+//     float(integer part) + float(double(up to 15 fraction digits) * 10^-k) — not the correctly
+//     rounded float, so vertices can differ from strtof by one ulp
+//   * one triangle_mesh per (group, material) in first-appearance order; quads are split from
+//     their concave corner if they have one, else from corner 0 (TriangulateProcess.cpp:227-277);
+//     larger polygons are fanned (Assimp ear-clips them: none in the shipped scenes)
+//   * a file without normals gets Assimp's GenSmoothNormals (GenVertexNormalsProcess.cpp:115-236
+//     with the default 175 degree limit): unweighted mean of the unit facet normals of every
+//     corner within 1e-4 of the mesh's box diagonal, in float.  The angle-weighted normals of
+//     mesh_loader.cpp:114-155 never run in the reference: Assimp has already made normals
+//   * MTL -> material mapping of mesh_loader.cpp:59-112 (Ke -> diffuse_light; Ks & d<1 ->
+//     dielectric; Ks -> modified_phong; else lambertian; colours through FromSrgb except Ke).
+//     The reference reads opacity / ior / shininess into `double`s, which aiMaterial::Get refuses
+//     (4-byte properties), so for Ks != 0 it branches on uninitialised stack; the mapping here is
+//     the one the code spells out
 //   * emissive triangles are appended to `lights` in creation order (triangle.cpp:15-20)
 #include "mesh_loader.h"
+#include <algorithm>
 #include <array>
+#include <cmath>
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -25,6 +41,62 @@ struct mtl_record
     float Ns = 0.f, Ni = 1.f, d = 1.f;
 };
 
+// fast_atof.h:232-338 for Real = float (the sign, digits, fraction and exponent forms the shipped files use)
+float assimp_atof(const char *c, const char **end = nullptr)
+{
+    static const double neg_pow10[16] = {0.0, 0.1, 0.01, 0.001, 0.0001, 0.00001, 0.000001, 0.0000001, 0.00000001, 0.000000001,
+                                         0.0000000001, 0.00000000001, 0.000000000001, 0.0000000000001, 0.00000000000001,
+                                         0.000000000000001};
+    float f = 0.f;
+    const bool neg = *c == '-';
+    if (neg || *c == '+') ++c;
+    auto digits = [&c](unsigned int limit, unsigned int *count) {
+        uint64_t v = 0;
+        unsigned int n = 0;
+        while (*c >= '0' && *c <= '9')
+        {
+            v = v * 10u + (uint64_t)(*c - '0');
+            ++c;
+            if (++n == limit) { while (*c >= '0' && *c <= '9') ++c; break; }
+        }
+        if (count) *count = n;
+        return v;
+    };
+    if (*c != '.') f = (float)digits(0, nullptr);
+    if (*c == '.' && c[1] >= '0' && c[1] <= '9')
+    {
+        ++c;
+        unsigned int n = 0;
+        double frac = (double)digits(15, &n);
+        frac *= neg_pow10[n];
+        f += (float)frac;
+    }
+    else if (*c == '.') ++c;
+    if (*c == 'e' || *c == 'E')
+    {
+        ++c;
+        const bool eneg = *c == '-';
+        if (eneg || *c == '+') ++c;
+        float e = (float)digits(0, nullptr);
+        if (eneg) e = -e;
+        f *= std::pow(10.0f, e);
+    }
+    if (end) *end = c;
+    return neg ? -f : f;
+}
+
+// the next `n` blank-separated numbers of a line (missing ones stay as they are)
+void read_floats(std::istringstream &ls, float *dst, int n)
+{
+    std::string tok;
+    for (int i = 0; i < n && (ls >> tok); ++i)
+    {
+        const char *c = tok.c_str();
+        const char *d = *c == '-' || *c == '+' ? c + 1 : c;
+        if ((*d >= '0' && *d <= '9') || (*d == '.' && d[1] >= '0' && d[1] <= '9')) dst[i] = assimp_atof(c);
+    }
+}
+
 void parse_mtl(const std::string &path, std::map<std::string, mtl_record> &out)
 {
     std::ifstream in(path);
@@ -39,10 +111,10 @@ void parse_mtl(const std::string &path, std::map<std::string, mtl_record> &out)
         if (current.empty()) continue;
         mtl_record &r = out[current];
         float *dst3 = key == "Kd" ? r.Kd : key == "Ks" ? r.Ks : key == "Ke" ? r.Ke : nullptr;
-        if (dst3) ls >> dst3[0] >> dst3[1] >> dst3[2];
-        else if (key == "Ns") ls >> r.Ns;
-        else if (key == "Ni") ls >> r.Ni;
-        else if (key == "d") ls >> r.d;
+        if (dst3) read_floats(ls, dst3, 3);
+        else if (key == "Ns") read_floats(ls, &r.Ns, 1);
+        else if (key == "Ni") read_floats(ls, &r.Ni, 1);
+        else if (key == "d") read_floats(ls, &r.d, 1);
     }
 }
 
@@ -76,44 +148,94 @@ struct mesh_builder
     std::vector<Vector3f> pos, nrm;
     std::vector<Vector2f> tex;
     std::vector<int> idx;
+    // Assimp's view of the mesh for smooth_normals: one vertex per polygon corner in file order (`corner_vertex` = its
+    // index into pos), and for every triangle corner the polygon corner it came from
+    std::vector<int> corner_vertex, tri_corner;
     bool all_normals = true;
 };
 
 int resolve(int i, size_t count) { return i < 0 ? (int)count + i + 1 : i; }
 
-// util.h:14-19
-double unit_angle(const Vector3f &u, const Vector3f &v)
+struct f3
 {
-    if (dot(u, v) < 0) return M_PI - 2 * std::asin(0.5 * (v + u).length());
-    return 2 * std::asin(0.5 * (v - u).length());
+    float x, y, z;
+};
+inline f3 sub(const f3 &a, const f3 &b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline float dot3(const f3 &a, const f3 &b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline f3 cross3(const f3 &a, const f3 &b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+inline float length3(const f3 &a) { return std::sqrt(dot3(a, a)); }
+inline f3 scaled(const f3 &a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+inline f3 as_f3(const Vector3f &v) { return {(float)v[0], (float)v[1], (float)v[2]}; }
+
+// TriangulateProcess.cpp:232-254: the corner a quad is fanned from — its concave corner (the two angles between the
+// edges and the diagonal add up to more than pi, in float), else corner 0
+int quad_fan_start(const f3 q[4])
+{
+    for (int i = 0; i < 4; ++i)
+    {
+        const f3 &v = q[i];
+        f3 left = sub(q[(i + 3) % 4], v), diag = sub(q[(i + 2) % 4], v), right = sub(q[(i + 1) % 4], v);
+        left = scaled(left, 1.0f / length3(left));
+        diag = scaled(diag, 1.0f / length3(diag));
+        right = scaled(right, 1.0f / length3(right));
+        const float angle = std::acos(dot3(left, diag)) + std::acos(dot3(right, diag));
+        if (angle > 3.1415926538f) return i;
+    }
+    return 0;
 }
 
-void facet_normals(mesh_builder &m)
+// GenVertexNormalsProcess.cpp:115-236 (no angle limit).  Assimp's mesh has one vertex per POLYGON corner; triangulation
+// (which runs first) leaves them shared between a quad's two triangles.  Every triangle writes its unit facet normal to
+// its three vertices, so a vertex ends up with the normal of the LAST triangle that uses it; then vertices closer than
+// 1e-4 x the mesh's box diagonal (ProcessHelper.cpp:147-155) to the first vertex not yet visited form a group and
+// share the normalised sum of their normals.  Float throughout, like aiVector3D; the sum itself is taken in double
+// (Assimp adds in the order of its unstable spatial sort, so the last bit is not defined by the source).
+void smooth_normals(mesh_builder &m)
 {
-    const int nt = (int)m.idx.size() / 3;
-    std::fill(m.nrm.begin(), m.nrm.end(), Vector3f(0, 0, 0));
+    const int nt = (int)m.idx.size() / 3, nc = (int)m.corner_vertex.size();
+    std::vector<f3> pos(nc);
+    for (int c = 0; c < nc; ++c) pos[c] = as_f3(m.pos[m.corner_vertex[c]]);
+    std::vector<f3> facet(nc, f3{0.f, 0.f, 0.f});
     for (int f = 0; f < nt; ++f)
     {
-        const int *V = &m.idx[3 * f];
-        Vector3f fn(0, 0, 0);
-        for (int c = 0; c < 3; ++c)
-        {
-            const Vector3f &a = m.pos[V[c]], &b = m.pos[V[(c + 1) % 3]], &d = m.pos[V[(c + 2) % 3]];
-            const Vector3f ab = b - a, ad = d - a;
-            if (c == 0)
-            {
-                fn = cross(ab, ad);
-                const double len = fn.length();
-                if (len == 0) break;
-                fn /= len;
-            }
-            m.nrm[V[c]] += fn * unit_angle(unit_vector(ab), unit_vector(ad));
-        }
+        const f3 &a = pos[m.tri_corner[3 * f]], &b = pos[m.tri_corner[3 * f + 1]], &c = pos[m.tri_corner[3 * f + 2]];
+        f3 n = cross3(sub(b, a), sub(c, a));
+        const float len = length3(n);
+        if (len > 0.f) n = scaled(n, 1.0f / len);
+        for (int k = 0; k < 3; ++k) facet[m.tri_corner[3 * f + k]] = n;
     }
-    for (Vector3f &n : m.nrm)
+    f3 lo{1e10f, 1e10f, 1e10f}, hi{-1e10f, -1e10f, -1e10f};
+    for (const f3 &p : pos)
     {
-        const double len = n.length();
-        if (len != 0) n /= len; else n = Vector3f(1, 0, 0);
+        lo = {std::min(lo.x, p.x), std::min(lo.y, p.y), std::min(lo.z, p.z)};
+        hi = {std::max(hi.x, p.x), std::max(hi.y, p.y), std::max(hi.z, p.z)};
+    }
+    const float eps = length3(sub(hi, lo)) * 1e-4f, eps2 = eps * eps;
+    // vertices ordered along x: the candidates of a vertex are a window of this order
+    std::vector<int> order(nc), rank(nc);
+    for (int c = 0; c < nc; ++c) order[c] = c;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return pos[a].x < pos[b].x; });
+    for (int r = 0; r < nc; ++r) rank[order[r]] = r;
+    std::vector<char> had(nc, 0);
+    std::vector<int> found;
+    for (int c = 0; c < nc; ++c)
+    {
+        if (had[c]) continue;
+        const f3 &p = pos[c];
+        found.clear();
+        int r0 = rank[c];
+        while (r0 > 0 && p.x - pos[order[r0 - 1]].x <= eps) --r0;
+        for (int r = r0; r < nc && pos[order[r]].x - p.x <= eps; ++r)
+        {
+            const f3 d = sub(pos[order[r]], p);
+            if (dot3(d, d) < eps2) found.push_back(order[r]);
+        }
+        double sx = 0, sy = 0, sz = 0;
+        for (int k : found) { sx += facet[k].x; sy += facet[k].y; sz += facet[k].z; }
+        f3 n{(float)sx, (float)sy, (float)sz};
+        const float len = length3(n);
+        if (len > 0.f) n = scaled(n, 1.0f / len);
+        for (int k : found) { m.nrm[m.corner_vertex[k]] = Vector3f(n.x, n.y, n.z); had[k] = 1; }
     }
 }
 
@@ -139,9 +261,9 @@ std::vector<std::shared_ptr<triangle_mesh>> mesh_loader::load_obj(std::string fi
         if (c != std::string::npos) line.erase(c);
         std::istringstream ls(line);
         if (!(ls >> key)) continue;
-        if (key == "v") { std::array<float, 3> p{}; ls >> p[0] >> p[1] >> p[2]; P.push_back(p); }
-        else if (key == "vn") { std::array<float, 3> p{}; ls >> p[0] >> p[1] >> p[2]; N.push_back(p); }
-        else if (key == "vt") { std::array<float, 2> p{}; ls >> p[0] >> p[1]; T.push_back(p); }
+        if (key == "v") { std::array<float, 3> p{}; read_floats(ls, p.data(), 3); P.push_back(p); }
+        else if (key == "vn") { std::array<float, 3> p{}; read_floats(ls, p.data(), 3); N.push_back(p); }
+        else if (key == "vt") { std::array<float, 2> p{}; read_floats(ls, p.data(), 2); T.push_back(p); }
         else if (key == "g" || key == "o") { group = "default"; ls >> group; }
         else if (key == "usemtl") { mtl.clear(); ls >> mtl; }
         else if (key == "mtllib") { std::string f; ls >> f; parse_mtl(dir + f, library); }
@@ -158,6 +280,7 @@ std::vector<std::shared_ptr<triangle_mesh>> mesh_loader::load_obj(std::string fi
             }
             mesh_builder &m = builders[found->second];
             std::vector<int> poly;
+            const int corner0 = (int)m.corner_vertex.size();
             std::string tok;
             while (ls >> tok)
             {
@@ -185,12 +308,22 @@ std::vector<std::shared_ptr<triangle_mesh>> mesh_loader::load_obj(std::string fi
                     else { m.nrm.emplace_back(0.0, 0.0, 0.0); m.all_normals = false; }
                 }
                 poly.push_back(it->second);
+                m.corner_vertex.push_back(it->second);
+            }
+            size_t first = 0;
+            if (poly.size() == 4)
+            {
+                const f3 q[4] = {as_f3(m.pos[poly[0]]), as_f3(m.pos[poly[1]]), as_f3(m.pos[poly[2]]), as_f3(m.pos[poly[3]])};
+                first = (size_t)quad_fan_start(q);
             }
             for (size_t i = 1; i + 1 < poly.size(); ++i)
             {
-                m.idx.push_back(poly[0]);
-                m.idx.push_back(poly[i]);
-                m.idx.push_back(poly[i + 1]);
+                m.idx.push_back(poly[first]);
+                m.idx.push_back(poly[(first + i) % poly.size()]);
+                m.idx.push_back(poly[(first + i + 1) % poly.size()]);
+                m.tri_corner.push_back(corner0 + (int)first);
+                m.tri_corner.push_back(corner0 + (int)((first + i) % poly.size()));
+                m.tri_corner.push_back(corner0 + (int)((first + i + 1) % poly.size()));
             }
         }
     }
@@ -198,16 +331,16 @@ std::vector<std::shared_ptr<triangle_mesh>> mesh_loader::load_obj(std::string fi
     std::vector<std::shared_ptr<triangle_mesh>> meshes;
     for (mesh_builder &m : builders)
     {
-        if (!m.all_normals) facet_normals(m);
+        if (!m.all_normals) smooth_normals(m);
+        // no `usemtl` at all: Assimp's "DefaultMaterial" -> the placeholder of mesh_loader.cpp:105-109.  A name the
+        // library does not hold: Assimp makes a default material (Kd 0.6) under that name (ObjFileParser.cpp:570-576)
         const mtl_record *rec = nullptr;
+        static const mtl_record unlisted;
         if (!m.mtl.empty())
         {
             auto it = library.find(m.mtl);
-            if (it != library.end())
-            {
-                rec = &it->second;
-                std::printf("Loading %s\n", m.mtl.c_str()); // mesh_loader.cpp:66
-            }
+            rec = it != library.end() ? &it->second : &unlisted;
+            std::printf("Loading %s\n", m.mtl.c_str()); // mesh_loader.cpp:66
         }
         const int nv = (int)m.pos.size(), nt = (int)m.idx.size() / 3;
         Vector3f *v = new Vector3f[nv];
@@ -216,9 +349,10 @@ std::vector<std::shared_ptr<triangle_mesh>> mesh_loader::load_obj(std::string fi
         std::copy(m.pos.begin(), m.pos.end(), v);
         std::copy(m.nrm.begin(), m.nrm.end(), n);
         std::copy(m.tex.begin(), m.tex.end(), t);
-        // `name` carries the OBJ group so scene builders can address sub-meshes (veach_mis plates)
+        // `name` is the MATERIAL's name, as in the reference (mesh_loader.cpp:62,158); "unknown" without one (:108).
+        // In CornellBox-Original.obj the boxes' faces come before their `g` lines, so the group would name them wrongly
         meshes.push_back(std::make_shared<triangle_mesh>(nt, nv, v, m.idx.data(), n, t, make_material(rec),
-                                                         use_geometry_normals, m.group, true));
+                                                         use_geometry_normals, rec ? m.mtl : std::string("unknown"), true));
     }
     return meshes;
 }

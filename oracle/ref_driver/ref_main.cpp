@@ -8,10 +8,10 @@
 // microfacet, camera — is the reference's own object code.
 //
 // What is NOT the reference here (documented deviations):
-//  * mesh_loader.cpp / triangle.cpp need Assimp (cmake + generated config.h): not built.  The
-//    OBJ/MTL reader below feeds the reference's own triangle_mesh / triangle classes and
-//    restates the MTL→material mapping of mesh_loader.cpp:59-112 and its fallback vertex
-//    normals (mesh_loader.cpp:114-155).
+//  * OBJ files go through the reference's own mesh_loader.cpp + its vendored Assimp 5.0.1; the one
+//    override (materials with Ks != 0, where the reference reads uninitialised doubles) is
+//    explained above read_obj.  triangle.cpp's create_triangle_mesh is restated in push_triangles
+//    (it is six lines around the loader call).
 //  * path::Render only covers rows 101..209 (path.cpp:120); the row loop below covers the
 //    whole frame like ao.h:17 does, on the reference's own tf::Taskflow.
 //  * veach_mis(): plates become rough_conductor (alphas from veach_mi/mi.xml), root becomes
@@ -40,6 +40,9 @@
 #include "assignment_1.hpp"
 #include "debug_renderer.h"
 
+#include "mesh_loader.h"
+#include <assimp/fast_atof.h>
+
 #ifdef FRT_DROPIN
 // The drop-in build: the product's integrator and flattener compiled against the REFERENCE's own headers
 // (Scene.h, triangle.h, material.h, texture.h, integrator.h ...), the way a maintainer of the reference would add
@@ -51,13 +54,26 @@
 static std::string g_assets = "assets";
 
 // ------------------------------------------------------------------------------------------
-// OBJ / MTL reader (driver-side stand-in for Assimp; see header comment)
+// OBJ import: the reference's own mesh_loader::load_obj (mesh_loader.cpp:5-162) over its vendored Assimp 5.0.1
+// (oracle/Makefile target `assimp`: plain g++ over the sources where they lie).
+//
+// One override.  For a material with Ks != 0, mesh_loader.cpp:81-96 reads AI_MATKEY_OPACITY / REFRACTI / SHININESS
+// into `double`s; aiMaterial::Get<double> refuses a 4-byte property and leaves them uninitialised, so the reference
+// picks dielectric or modified_phong (and its ior / exponent) from whatever the stack holds — undefined behaviour, not
+// an algorithm.  Those materials are rebuilt here the way the code spells the mapping out (d < 1 -> dielectric(Ni),
+// else modified_phong(Kd, Ks, Ns)), from the MTL numbers read with Assimp's own fast_atof.
 // ------------------------------------------------------------------------------------------
 struct mtl_entry
 {
     float Kd[3] = {0.6f, 0.6f, 0.6f}, Ks[3] = {0, 0, 0}, Ke[3] = {0, 0, 0};
     float Ns = 0.f, Ni = 1.f, d = 1.f;
 };
+
+static void mtl_numbers(std::istringstream &ss, float *dst, int n)
+{
+    std::string tok;
+    for (int i = 0; i < n && (ss >> tok); ++i) dst[i] = Assimp::fast_atof(tok.c_str());
+}
 
 static std::map<std::string, mtl_entry> read_mtl(const std::string &path)
 {
@@ -74,169 +90,51 @@ static std::map<std::string, mtl_entry> read_mtl(const std::string &path)
         if (key == "newmtl") { ss >> cur; out[cur] = mtl_entry(); continue; }
         if (cur.empty()) continue;
         mtl_entry &m = out[cur];
-        if (key == "Kd") ss >> m.Kd[0] >> m.Kd[1] >> m.Kd[2];
-        else if (key == "Ks") ss >> m.Ks[0] >> m.Ks[1] >> m.Ks[2];
-        else if (key == "Ke") ss >> m.Ke[0] >> m.Ke[1] >> m.Ke[2];
-        else if (key == "Ns") ss >> m.Ns;
-        else if (key == "Ni") ss >> m.Ni;
-        else if (key == "d") ss >> m.d;
+        if (key == "Kd") mtl_numbers(ss, m.Kd, 3);
+        else if (key == "Ks") mtl_numbers(ss, m.Ks, 3);
+        else if (key == "Ke") mtl_numbers(ss, m.Ke, 3);
+        else if (key == "Ns") mtl_numbers(ss, &m.Ns, 1);
+        else if (key == "Ni") mtl_numbers(ss, &m.Ni, 1);
+        else if (key == "d") mtl_numbers(ss, &m.d, 1);
     }
     return out;
 }
-
-// mesh_loader.cpp:59-112
-static std::unique_ptr<material> material_from_mtl(const mtl_entry *m)
-{
-    if (!m)
-        return std::make_unique<lambertian>(new constant_texture(Vector3f(0.5, 0.5, 0.5)));
-    if (m->Ke[0] != 0 || m->Ke[1] != 0 || m->Ke[2] != 0)
-        return std::make_unique<diffuse_light>(new constant_texture(Vector3f(m->Ke[0], m->Ke[1], m->Ke[2])));
-    if (m->Ks[0] != 0 || m->Ks[1] != 0 || m->Ks[2] != 0)
-    {
-        const Vector3f ks(FromSrgb(m->Ks[0]), FromSrgb(m->Ks[1]), FromSrgb(m->Ks[2]));
-        if (double(m->d) < 1.0)
-            return std::make_unique<dielectric>(double(m->Ni), new constant_texture(ks),
-                                                new constant_texture(Vector3f(1.0, 1.0, 1.0)));
-        const Vector3f kd(FromSrgb(m->Kd[0]), FromSrgb(m->Kd[1]), FromSrgb(m->Kd[2]));
-        return std::make_unique<modified_phong>(new constant_texture(kd), new constant_texture(ks), double(m->Ns));
-    }
-    return std::make_unique<lambertian>(
-        new constant_texture(Vector3f(FromSrgb(m->Kd[0]), FromSrgb(m->Kd[1]), FromSrgb(m->Kd[2]))));
-}
-
-struct raw_mesh
-{
-    std::string group, mtl;
-    std::map<std::array<int, 3>, int> remap;
-    std::vector<Vector3f> v, n;
-    std::vector<Vector2f> t;
-    std::vector<int> idx;
-    bool has_normals = true;
-};
 
 static std::vector<std::shared_ptr<triangle_mesh>> read_obj(const std::string &file, bool use_geometry_normals)
 {
+    std::vector<std::shared_ptr<triangle_mesh>> meshes = mesh_loader::load_obj(file, use_geometry_normals);
     std::ifstream is(file);
-    if (!is.is_open()) throw std::runtime_error("cannot open " + file);
     const std::string dir = file.substr(0, file.find_last_of('/') + 1);
-    std::vector<std::array<float, 3>> P, N;
-    std::vector<std::array<float, 2>> T;
     std::map<std::string, mtl_entry> mtls;
-    std::vector<raw_mesh> meshes;
-    std::map<std::pair<std::string, std::string>, int> mesh_of;
-    std::string group = "default", mtl = "";
     std::string line;
     while (std::getline(is, line))
     {
-        const size_t hash = line.find('#');
-        if (hash != std::string::npos) line.resize(hash);
         std::istringstream ss(line);
-        std::string key;
-        if (!(ss >> key)) continue;
-        if (key == "v") { std::array<float, 3> p; ss >> p[0] >> p[1] >> p[2]; P.push_back(p); }
-        else if (key == "vn") { std::array<float, 3> p; ss >> p[0] >> p[1] >> p[2]; N.push_back(p); }
-        else if (key == "vt") { std::array<float, 2> p; ss >> p[0] >> p[1]; T.push_back(p); }
-        else if (key == "g" || key == "o") { group = "default"; ss >> group; }
-        else if (key == "usemtl") { mtl = ""; ss >> mtl; }
-        else if (key == "mtllib") { std::string f; ss >> f; auto m = read_mtl(dir + f); mtls.insert(m.begin(), m.end()); }
-        else if (key == "f")
+        std::string key, f;
+        if ((ss >> key) && key == "mtllib" && (ss >> f))
         {
-            auto mk = std::make_pair(group, mtl);
-            auto it = mesh_of.find(mk);
-            if (it == mesh_of.end())
-            {
-                it = mesh_of.emplace(mk, (int)meshes.size()).first;
-                meshes.emplace_back();
-                meshes.back().group = group;
-                meshes.back().mtl = mtl;
-            }
-            raw_mesh &m = meshes[it->second];
-            std::vector<int> corner;
-            std::string tok;
-            while (ss >> tok)
-            {
-                int vi = 0, ti = 0, ni = 0;
-                const size_t s1 = tok.find('/');
-                vi = std::atoi(tok.substr(0, s1).c_str());
-                if (s1 != std::string::npos)
-                {
-                    const size_t s2 = tok.find('/', s1 + 1);
-                    const std::string a = tok.substr(s1 + 1, s2 == std::string::npos ? std::string::npos : s2 - s1 - 1);
-                    if (!a.empty()) ti = std::atoi(a.c_str());
-                    if (s2 != std::string::npos) ni = std::atoi(tok.substr(s2 + 1).c_str());
-                }
-                if (vi < 0) vi = (int)P.size() + vi + 1;
-                if (ti < 0) ti = (int)T.size() + ti + 1;
-                if (ni < 0) ni = (int)N.size() + ni + 1;
-                std::array<int, 3> k = {vi, ti, ni};
-                auto f = m.remap.find(k);
-                if (f == m.remap.end())
-                {
-                    f = m.remap.emplace(k, (int)m.v.size()).first;
-                    m.v.push_back(Vector3f(P[vi - 1][0], P[vi - 1][1], P[vi - 1][2]));
-                    m.t.push_back(ti ? Vector2f(T[ti - 1][0], T[ti - 1][1]) : Vector2f(0, 0));
-                    if (ni) m.n.push_back(Vector3f(N[ni - 1][0], N[ni - 1][1], N[ni - 1][2]));
-                    else { m.n.push_back(Vector3f(0, 0, 0)); m.has_normals = false; }
-                }
-                corner.push_back(f->second);
-            }
-            for (size_t k = 1; k + 1 < corner.size(); ++k)
-            {
-                m.idx.push_back(corner[0]);
-                m.idx.push_back(corner[k]);
-                m.idx.push_back(corner[k + 1]);
-            }
+            auto m = read_mtl(dir + f);
+            mtls.insert(m.begin(), m.end());
         }
     }
-
-    std::vector<std::shared_ptr<triangle_mesh>> out;
-    for (raw_mesh &m : meshes)
+    for (auto &mesh : meshes) // mesh->name is the material's name (mesh_loader.cpp:62,158)
     {
-        const int nv = (int)m.v.size(), nt = (int)m.idx.size() / 3;
-        Vector3f *vertices = new Vector3f[nv];
-        Vector3f *normals = new Vector3f[nv];
-        Vector2f *uv = new Vector2f[nv];
-        for (int i = 0; i < nv; ++i) { vertices[i] = m.v[i]; normals[i] = m.n[i]; uv[i] = m.t[i]; }
-        if (!m.has_normals)
+        auto f = mtls.find(mesh->name);
+        if (f == mtls.end()) continue;
+        const mtl_entry &m = f->second;
+        const bool emissive = m.Ke[0] != 0 || m.Ke[1] != 0 || m.Ke[2] != 0;
+        const bool specular = m.Ks[0] != 0 || m.Ks[1] != 0 || m.Ks[2] != 0;
+        if (emissive || !specular) continue;
+        const Vector3f ks(FromSrgb(m.Ks[0]), FromSrgb(m.Ks[1]), FromSrgb(m.Ks[2]));
+        if (double(m.d) < 1.0)
+            mesh->mat = std::make_unique<dielectric>(double(m.Ni), new constant_texture(ks), new constant_texture(Vector3f(1.0, 1.0, 1.0)));
+        else
         {
-            // mesh_loader.cpp:114-155 (angle-weighted facet normals)
-            for (int i = 0; i < nv; ++i) normals[i] = Vector3f(0, 0, 0);
-            for (int j = 0; j < nt; ++j)
-            {
-                Vector3f n(0.0, 0.0, 0.0);
-                const int *V = &m.idx[3 * j];
-                for (int i = 0; i < 3; ++i)
-                {
-                    const Vector3f &v0 = vertices[V[i]];
-                    const Vector3f &v1 = vertices[V[(i + 1) % 3]];
-                    const Vector3f &v2 = vertices[V[(i + 2) % 3]];
-                    const Vector3f e1 = v1 - v0, e2 = v2 - v0;
-                    if (i == 0)
-                    {
-                        n = cross(e1, e2);
-                        const double length = n.length();
-                        if (length == 0) break;
-                        n /= length;
-                    }
-                    const double angle = unit_angle(unit_vector(e1), unit_vector(e2));
-                    normals[V[i]] += n * angle;
-                }
-            }
-            for (int i = 0; i < nv; ++i)
-            {
-                const double length = normals[i].length();
-                if (length != 0) normals[i] /= length; else normals[i] = Vector3f(1, 0, 0);
-            }
+            const Vector3f kd(FromSrgb(m.Kd[0]), FromSrgb(m.Kd[1]), FromSrgb(m.Kd[2]));
+            mesh->mat = std::make_unique<modified_phong>(new constant_texture(kd), new constant_texture(ks), double(m.Ns));
         }
-        const mtl_entry *me = nullptr;
-        auto f = mtls.find(m.mtl);
-        if (!m.mtl.empty() && f != mtls.end()) me = &f->second;
-        out.push_back(std::make_shared<triangle_mesh>(nt, nv, vertices, m.idx.data(), normals, uv,
-                                                      material_from_mtl(me), use_geometry_normals,
-                                                      me ? m.mtl : std::string("unknown"), true));
-        out.back()->name = m.group; // group name is what the scene builders key on
     }
-    return out;
+    return meshes;
 }
 
 // triangle.cpp:9-26 without the Assimp call
