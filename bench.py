@@ -211,6 +211,15 @@ class Rig:
         _, st = self.ctx.readback(want_image=False)
         return e0.elapsed_time(e1), st
 
+    def per_rank(self, x: float) -> list:
+        """x of every rank, in rank order (diagnostics: which rank sets the max)."""
+        if self.world == 1:
+            return [x]
+        t = self.torch.zeros(self.world, dtype=self.torch.float64, device=self.dev)
+        t[self.rank] = x
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return [float(v) for v in t.tolist()]
+
     def max_over_ranks(self, x: float) -> float:
         if self.world == 1:
             return x
@@ -414,6 +423,7 @@ def config_soup(rig: Rig, n_tri: int, n_rays: int, peaks):
         for sort in (False, True):
             rig.barrier()
             ms = min(rig.ctx.trace_device(rays.data_ptr(), n, hits2.data_ptr() if sort else hits.data_ptr(), any_hit, sort=sort) for _ in range(3))
+            ms_ranks = rig.per_rank(ms)
             ms = rig.max_over_ranks(ms)
             # node / triangle fetches per ray from a counting build of the same kernel on a prefix
             rig.ctx.set_flags(api.FRT_FLAG_COUNTERS)
@@ -430,7 +440,7 @@ def config_soup(rig: Rig, n_tri: int, n_rays: int, peaks):
             b_ray = node_bytes * nodes + 48.0 * tris + 24.0 + 16.0  # node + triangle fetches, ray in (24 B), hit out (16 B)
             gbs = n_rays * b_ray / (ms * 1e-3) / 1e9 / rig.world  # per GPU
             cast = {"query": label, "order": "morton (device sort inside)" if sort else "as given (incoherent)",
-                    "value": n_rays / ms / 1e3, "unit": "Mrays/s", "ms": ms, "nodes_per_ray": nodes, "tris_per_ray": tris,
+                    "value": n_rays / ms / 1e3, "unit": "Mrays/s", "ms": ms, "ms_per_rank": ms_ranks, "nodes_per_ray": nodes, "tris_per_ray": tris,
                     "bytes_per_ray": b_ray, "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
                                                          "per": "GPU"}}
             if sort:
@@ -453,6 +463,7 @@ def config_soup(rig: Rig, n_tri: int, n_rays: int, peaks):
                   "h2d_bytes": m * 24, "d2h_bytes": m * 16, "call": "frt_trace_rays, pinned host rays in / hits out, closest hit, unsorted"}
     pr.close(); ph.close()
     res["clocks"] = sampler.finish()
+    res["sm_mhz_per_rank"] = rig.per_rank(res["clocks"].get("sm_mhz") or 0.0)
     scene.close()
     return res
 

@@ -45,6 +45,7 @@ int frt_create(frt_ctx **out, const int *devices, int n)
     if (const char *s = getenv("FRT_TRACE_OCC")) c->trace_occ[0] = std::min(3, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_TRACE_OCC_ANY")) c->trace_occ[1] = std::min(3, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_TRACE_REFILL")) c->trace_refill[0] = std::min(31, std::max(0, atoi(s)));
+    if (const char *s = getenv("FRT_TRACE_CHUNK")) c->trace_chunk = (size_t)std::max(1024ll, atoll(s));
     if (const char *s = getenv("FRT_TRACE_REFILL_ANY")) c->trace_refill[1] = std::min(31, std::max(-1, atoi(s)));
 
     CU(cudaHostAlloc((void **)&c->h_cancel, sizeof(unsigned int), cudaHostAllocPortable));
@@ -62,6 +63,8 @@ int frt_create(frt_ctx **out, const int *devices, int n)
         d.sms = prop.multiProcessorCount;
         CU(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
         CU(cudaStreamCreateWithFlags(&d.side_stream, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&d.in_stream, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&d.out_stream, cudaStreamNonBlocking));
         for (cudaEvent_t *ev : {&d.ev_begin, &d.ev_end, &d.ev_sum, &d.ev_t0, &d.ev_t1}) CU(cudaEventCreate(ev));
         CU(cudaMalloc((void **)&d.d_ctr, sizeof(Counters)));
         CU(cudaMemset(d.d_ctr, 0, sizeof(Counters)));
@@ -130,6 +133,9 @@ void frt_destroy(frt_ctx *ctx)
         for (cudaEvent_t ev : {d.ev_begin, d.ev_end, d.ev_sum, d.ev_t0, d.ev_t1}) if (ev) cudaEventDestroy(ev);
         if (d.stream) cudaStreamDestroy(d.stream);
         if (d.side_stream) cudaStreamDestroy(d.side_stream);
+        if (d.in_stream) cudaStreamDestroy(d.in_stream);
+        if (d.out_stream) cudaStreamDestroy(d.out_stream);
+        for (cudaEvent_t ev : d.chunk_ev) cudaEventDestroy(ev);
     }
     if (!ctx->dev.empty()) cudaSetDevice(ctx->dev[0].ordinal);
     if (ctx->d_ldr) cudaFree(ctx->d_ldr);

@@ -33,6 +33,8 @@ struct Device
     int ordinal = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t side_stream = nullptr; // frt_cancel's 4-byte copy: runs beside the persistent kernel
+    cudaStream_t in_stream = nullptr, out_stream = nullptr; // frt_trace_rays: chunked copies in / out beside the casts
+    std::vector<cudaEvent_t> chunk_ev;                      // three per chunk (grown on demand)
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_sum = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
     // scene
     void *d_nodes = nullptr, *d_tris = nullptr, *d_normals = nullptr, *d_spheres = nullptr, *d_mats = nullptr,
@@ -83,6 +85,7 @@ struct frt_ctx
     int trace_occ[2] = {2, 2};    // ray casting: index into {4, 6, 8, 12} CTAs per SM for closest / occlusion casts (a large
                                   // incoherent scene is latency-bound: 8 CTAs of 64 registers measured +25 % over 4 of 128)
     int trace_refill[2] = {24, -1}; // dynamic fetch threshold for closest / occlusion casts (-1: plain batches of 32)
+    size_t trace_chunk = 1u << 21; // frt_trace_rays with pinned buffers: rays per pipelined chunk (FRT_TRACE_CHUNK)
     int wide8 = 0;                // ray casting over the 8-wide compressed nodes (FRT_WIDE8=1): off by default, measured slower
     bool have_wide8 = false;
     uint32_t n_nodes8 = 0;

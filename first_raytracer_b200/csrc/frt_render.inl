@@ -462,9 +462,9 @@ int frt_trace_rays(frt_ctx *ctx, const frt_ray *rays, size_t n, frt_hit *hits, i
     // buffers (frt_host_alloc, cudaHostAlloc, cudaHostRegister) are copied asynchronously straight from / to the
     // caller; pageable ones are staged by the runtime inside cudaMemcpyAsync, which blocks the issuing thread, so
     // each device then gets its own host thread.
-    struct Part { size_t b, e; int rc; };
+    struct Part { size_t b, e; int rc; size_t chunks; };
     std::vector<Part> parts(nd);
-    for (int i = 0; i < nd; ++i) { parts[i].b = n * i / nd; parts[i].e = n * (i + 1) / nd; parts[i].rc = FRT_OK; }
+    for (int i = 0; i < nd; ++i) { parts[i].b = n * i / nd; parts[i].e = n * (i + 1) / nd; parts[i].rc = FRT_OK; parts[i].chunks = 0; }
     for (int i = 0; i < nd; ++i)
     {
         Device &d = ctx->dev[i];
@@ -493,8 +493,46 @@ int frt_trace_rays(frt_ctx *ctx, const frt_ray *rays, size_t n, frt_hit *hits, i
         if (cudaMemcpyAsync(hits + b, d.d_hits, m * sizeof(frt_hit), cudaMemcpyDeviceToHost, d.stream) != cudaSuccess) parts[i].rc = FRT_ERR_CUDA;
         if (!pinned && cudaStreamSynchronize(d.stream) != cudaSuccess) parts[i].rc = FRT_ERR_CUDA;
     };
-    if (pinned || nd == 1)
-        for (int i = 0; i < nd; ++i) enqueue(i);
+    // Pinned buffers: a device's share moves in chunks on three streams, so that the copy in of chunk k+1 and the copy
+    // out of chunk k-1 run under the cast of chunk k (PCIe both ways beside the kernel); only the first copy in and the
+    // last copy out stay exposed.  Three events per chunk: rays arrived, cast begun, cast ended (the last two give the
+    // chunk's device time).  FRT_TRACE_SORT orders every chunk by itself.
+    const size_t chunk = ctx->trace_chunk;
+    auto pipeline = [&](int i) {
+        Device &d = ctx->dev[i];
+        const size_t b = parts[i].b, m = parts[i].e - b;
+        if (m == 0) return;
+        const size_t nc = (m + chunk - 1) / chunk;
+        bool ok = cudaSetDevice(d.ordinal) == cudaSuccess;
+        while (ok && d.chunk_ev.size() < 3 * nc)
+        {
+            cudaEvent_t ev = nullptr;
+            ok = cudaEventCreate(&ev) == cudaSuccess;
+            if (ok) d.chunk_ev.push_back(ev);
+        }
+        // the copy streams must not start before earlier work on the main stream (a previous call's casts) is done
+        ok = ok && cudaEventRecord(d.ev_t0, d.stream) == cudaSuccess && cudaStreamWaitEvent(d.in_stream, d.ev_t0, 0) == cudaSuccess;
+        for (size_t c = 0; ok && c < nc; ++c)
+        {
+            const size_t o = c * chunk, k = std::min(chunk, m - o);
+            cudaEvent_t arrived = d.chunk_ev[3 * c], begun = d.chunk_ev[3 * c + 1], ended = d.chunk_ev[3 * c + 2];
+            ok = cudaMemcpyAsync((frt_ray *)d.d_rays + o, rays + b + o, k * sizeof(frt_ray), cudaMemcpyHostToDevice, d.in_stream) == cudaSuccess &&
+                 cudaEventRecord(arrived, d.in_stream) == cudaSuccess && cudaStreamWaitEvent(d.stream, arrived, 0) == cudaSuccess &&
+                 cudaEventRecord(begun, d.stream) == cudaSuccess;
+            if (!ok) break;
+            parts[i].rc = frt_trace_rays_device(ctx, i, (frt_ray *)d.d_rays + o, k, (frt_hit *)d.d_hits + o, mode, nullptr);
+            if (parts[i].rc != FRT_OK) return;
+            ok = cudaSetDevice(d.ordinal) == cudaSuccess && cudaEventRecord(ended, d.stream) == cudaSuccess &&
+                 cudaStreamWaitEvent(d.out_stream, ended, 0) == cudaSuccess &&
+                 cudaMemcpyAsync(hits + b + o, (frt_hit *)d.d_hits + o, k * sizeof(frt_hit), cudaMemcpyDeviceToHost, d.out_stream) == cudaSuccess;
+        }
+        if (!ok) parts[i].rc = FRT_ERR_CUDA;
+        parts[i].chunks = nc;
+    };
+    if (pinned)
+        for (int i = 0; i < nd; ++i) pipeline(i);
+    else if (nd == 1)
+        enqueue(0);
     else
     {
         std::vector<std::thread> workers;
@@ -510,9 +548,24 @@ int frt_trace_rays(frt_ctx *ctx, const frt_ray *rays, size_t n, frt_hit *hits, i
         if (parts[i].rc != FRT_OK) return parts[i].rc == FRT_ERR_CUDA ? fail(ctx, FRT_ERR_CUDA, "frt_trace_rays: device %d: %s", i, cudaGetErrorString(cudaGetLastError())) : parts[i].rc;
         CU(cudaSetDevice(d.ordinal));
         CU(cudaStreamSynchronize(d.stream));
-        float ms = 0.f;
-        CU(cudaEventElapsedTime(&ms, d.ev_t0, d.ev_t1));
-        worst = std::max<double>(worst, ms);
+        double total = 0;
+        if (parts[i].chunks)
+        {
+            CU(cudaStreamSynchronize(d.out_stream));
+            for (size_t c = 0; c < parts[i].chunks; ++c)
+            {
+                float ms = 0.f;
+                CU(cudaEventElapsedTime(&ms, d.chunk_ev[3 * c + 1], d.chunk_ev[3 * c + 2]));
+                total += ms;
+            }
+        }
+        else
+        {
+            float ms = 0.f;
+            CU(cudaEventElapsedTime(&ms, d.ev_t0, d.ev_t1));
+            total = ms;
+        }
+        worst = std::max(worst, total);
     }
     if (device_ms) *device_ms = worst;
     return FRT_OK;
