@@ -338,7 +338,8 @@ struct WfConfig
     WfKernel kernel[2]; // [counting]
 };
 #define WF_CFG(T, B, O) {T, B, {k_wavefront<false, T, B, O>, k_wavefront<true, T, B, O>}}
-const WfConfig wf_configs[] = {WF_CFG(256, 2, false), WF_CFG(512, 1, false), WF_CFG(384, 1, false), WF_CFG(320, 2, false)};
+const WfConfig wf_configs[] = {WF_CFG(256, 2, false), WF_CFG(512, 1, false), WF_CFG(384, 1, false), WF_CFG(320, 2, false),
+                                WF_CFG(128, 4, false)};
 const int n_wf_configs = (int)(sizeof wf_configs / sizeof wf_configs[0]);
 // The general kernel: the integrators next to `path` (ao, normals_renderer, ass_1_renderer) and `path` over textured
 // surfaces.  Its own instantiation, so that the path kernel of the untextured scenes carries none of that code
