@@ -332,7 +332,7 @@ def roofline_pass(rig: Rig, spp_range, peaks, clocks):
 # ---------------------------------------------------------------------------------------------
 # BASELINE.json's other configs, measured in the same process (the `configs` block)
 # ---------------------------------------------------------------------------------------------
-def config_render(rig: Rig, name, nx, ny, spp, steps=3, fixture=None, fixture_block=1, leaf=2):
+def config_render(rig: Rig, name, nx, ny, spp, steps=3, fixture=None, fixture_block=1, leaf=0):
     """A render config on all ranks (spp range split, one NCCL reduce inside the step): Msamples/s from the max over
     ranks of the summed device step times; parity bit = mean radiance within 0.5 % of the as-shipped mt19937
     reference's (tests/golden/stat_*.npz, scripts/make_golden_stat.py) — rank 0 holds the reduced film."""

@@ -73,10 +73,12 @@ struct frt_ctx
                                   // traversal stacks (1024 -> 1280: +2 % Cornell, +8 % veach_mi, -1 % teapot; 1568 leaves no L1: -25 %)
     // The path kernel's launch shape follows the size of the scene (profiles/r02_wf_sweep_pool_size.log): a scene that fits
     // the SM's L1 beside the pool (Cornell, veach_mi: a few KB) runs fastest as ONE 512-thread CTA with the largest pool;
-    // a mesh scene (teapot: 0.2 MB of nodes and triangles) wants the L1 for the tree, and two 256-thread CTAs of 512
-    // slots each hide its node fetches better (+8 %).  Index 0 = small, 1 = large.
-    int wf_config[2] = {1, 0};                // index into wf_configs[]
-    unsigned int wf_slots_of[2] = {1280, 512}; // slots per CTA of the path kernel, per shape
+    // a mesh scene (teapot: 0.2 MB of nodes and triangles) wants the L1 for the tree, and several small CTAs hide its
+    // node fetches and each other's stage tails better: two 256-thread CTAs of 512 slots +8 %, four 128-thread CTAs of
+    // 256 slots another +5 % (profiles/r02_wf_sweep_128x4.log; the same shape costs Cornell 23 % and veach 43 %: their
+    // shade stage needs many paths per CTA to fill warps per material).  Index 0 = small, 1 = large.
+    int wf_config[2] = {1, 4};                // index into wf_configs[]
+    unsigned int wf_slots_of[2] = {1280, 256}; // slots per CTA of the path kernel, per shape
     size_t wf_big_scene_bytes = 128u << 10;   // nodes + triangles + spheres above this: the large-scene shape
     size_t scene_bytes = 0;
     int wf_refill = 20;           // dynamic fetch threshold (lanes still traversing)

@@ -66,9 +66,12 @@ class frt_flattener
 {
 public:
     // prim_ids: creation-order id per primitive (what the parity tests compare); when empty the
-    // ids follow the depth-first leaf order of the tree.  max_leaf: triangles per leaf (1..16).
-    frt_flattener(const std::unordered_map<const hitable *, int> *prim_ids = nullptr, int max_leaf = 4)
-        : ids_(prim_ids), max_leaf_(max_leaf < 1 ? 1 : (max_leaf > 16 ? 16 : max_leaf)) {}
+    // ids follow the depth-first leaf order of the tree.  max_leaf: triangles per leaf (1..16); 0 = by scene size —
+    // 2 for the reference's small scenes, 4 from 4096 primitives on (measured on B200, profiles/r02_wf_sweep_leaf.log:
+    // Cornell 1015 / 1195 / 1044 / 975 Msamples/s at 1 / 2 / 4 / 8 per leaf, the 15 704-triangle mesh scene
+    // 985 / 1071 / 1158 / 1091).
+    frt_flattener(const std::unordered_map<const hitable *, int> *prim_ids = nullptr, int max_leaf = 0)
+        : ids_(prim_ids), asked_leaf_(max_leaf < 1 ? 0 : (max_leaf > 16 ? 16 : max_leaf)), max_leaf_(asked_leaf_) {}
 
     frt_flat_scene flatten(const Scene *scene)
     {
@@ -84,6 +87,7 @@ public:
                 m = std::fmax(m, std::fmax(std::fabs(bn_[root].box.min[a]), std::fabs(bn_[root].box.max[a])));
             for (int a = 0; a < 3; ++a) m = std::fmax(m, std::fabs(scene->cam.origin[a]));
             pad_ = 4e-7 * m;
+            max_leaf_ = asked_leaf_ ? asked_leaf_ : (bn_[root].count >= 4096 ? 4 : 2);
             if (bn_[root].prim) { int r2 = (int)bn_.size(); bnode top; top.box = bn_[root].box; top.left = root; top.count = bn_[root].count; top.all_tris = bn_[root].all_tris; bn_.push_back(top); root = r2; }
             emit_wide(root, 1);
         }
@@ -436,7 +440,7 @@ private:
     }
 
     const std::unordered_map<const hitable *, int> *ids_;
-    int max_leaf_;
+    int asked_leaf_, max_leaf_;
     int next_id_ = 0;
     double pad_ = 0;
     std::vector<bnode> bn_;

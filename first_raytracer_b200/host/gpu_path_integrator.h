@@ -27,7 +27,7 @@ struct gpu_path_integrator
     int n_gpus = 1;
     uint32_t seed = 1;
     uint32_t max_depth = 34;
-    int max_leaf = 2; // triangles per wide-BVH leaf (measured best on B200 for the reference scenes)
+    int max_leaf = 0; // triangles per wide-BVH leaf; 0 = chosen by scene size (flatten.h: 2, or 4 for mesh scenes)
     uint32_t flags = 0;
     uint32_t integrator = FRT_INTEGRATOR_PATH; // which Li the tile runs; see gpu_ao_integrator / gpu_normals_integrator
     // resume: film sums of samples [0, spp_begin) from an earlier run; the render continues at

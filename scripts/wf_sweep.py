@@ -7,7 +7,7 @@ if len(sys.argv) > 1 and sys.argv[1] == "--child":
     from first_raytracer_b200 import api
     name, spp = sys.argv[2].split(":"); spp = int(spp)
     nx, ny = 1920, 1080
-    scene = api.HostScene(name, nx / ny, 2)
+    scene = api.HostScene(name, nx / ny, int(os.environ.get('SWEEP_LEAF', '2')))
     ctx = api.Context(devices=[0]); ctx.upload(scene)
     best = None
     for _ in range(3):
