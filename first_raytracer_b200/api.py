@@ -33,7 +33,7 @@ FRT_SYMBOLS = [
 FRTH_SYMBOLS = [
     "frth_last_error", "frth_scene_create", "frth_scene_create_soup", "frth_scene_destroy",
     "frth_scene_desc", "frth_scene_info", "frth_soup_triangles", "frth_camera_rays", "frth_render",
-    "frth_bvh4_build", "frth_cancel", "frth_last_ldr",
+    "frth_bvh4_build", "frth_cancel", "frth_last_ldr", "frth_write_png",
 ]
 
 
@@ -160,6 +160,7 @@ def load_libs():
             "frth_bvh4_build": (i32, [vp, sz, i32, dbl, C.POINTER(vp)]),
             "frth_cancel": (i32, []),
             "frth_last_ldr": (i32, [vp, sz]),
+            "frth_write_png": (i32, [C.c_char_p, vp, i32, i32]),
         },
     }
     for lib, table in sig.items():
@@ -266,6 +267,15 @@ class HostScene:
         if self._frth.frth_last_ldr(_ptr(out), out.size) != FRT_OK:
             raise FrtError("frth_last_ldr: no film of that size")
         return out
+
+
+def write_png(path: str, ldr: np.ndarray):
+    """frth_write_png: an 8-bit RGB film [ny, nx, 3] with row 0 = bottom (HostScene.last_ldr) as a PNG file."""
+    _, frth = load_libs()
+    ldr = np.ascontiguousarray(ldr, dtype=np.uint8)
+    assert ldr.ndim == 3 and ldr.shape[2] == 3
+    if frth.frth_write_png(str(path).encode(), _ptr(ldr), ldr.shape[1], ldr.shape[0]) != FRT_OK:
+        raise FrtError(f"frth_write_png: {frth.frth_last_error().decode()}")
 
 
 def soup_triangles(n: int, seed: int = 0x5EED0001, edge: float = 0.004) -> np.ndarray:

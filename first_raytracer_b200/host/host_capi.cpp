@@ -11,6 +11,7 @@
 #include "fast_bvh.h"
 #include "gpu_path_integrator.h"
 #include "integrator.h"
+#include "png_writer.h"
 #include "scenes.h"
 
 struct frth_scene
@@ -210,6 +211,14 @@ int frth_last_ldr(unsigned char *out, size_t n_bytes)
     std::lock_guard<std::mutex> lock(g_film_mutex);
     if (!g_film_cache || !out || n_bytes != (size_t)g_film_cache->nx * g_film_cache->ny * 3) return FRT_ERR_STATE;
     std::memcpy(out, g_film_cache->out_image.get(), n_bytes);
+    return FRT_OK;
+}
+
+// Host utility: an 8-bit RGB film (row 0 = bottom, what frth_last_ldr returns) as a PNG file
+int frth_write_png(const char *path, const unsigned char *rgb, int nx, int ny)
+{
+    if (!path || !rgb || nx <= 0 || ny <= 0) return FRT_ERR_INVALID;
+    if (!frt_png::write_rgb8(path, rgb, nx, ny)) { g_error = std::string("cannot write ") + path; return FRT_ERR_INVALID; }
     return FRT_OK;
 }
 

@@ -1,6 +1,6 @@
 // frt_main — the reference's main() (main.cpp:483-525) with the GPU integrator selectable:
 //   frt_main [--ns N] [--scene cornell|veach|teapot|soup:N] [--res WxH] [--integrator gpu_path]
-//            [--gpus N] [--seed S] [--out NAME] [--checkpoint FILE] [--resume FILE]
+//            [--gpus N] [--seed S] [--out NAME] [--png FILE] [--checkpoint FILE] [--resume FILE]
 // --checkpoint writes the film sums after the render; --resume starts from such a file and renders only the samples
 // it does not hold yet (same seed, same resolution), so an interrupted --ns 512 job can be finished as --ns 1024.
 // Defaults follow the reference: 512x512, ns = 100 (main.cpp:485-487).  The only integrator in
@@ -15,6 +15,7 @@
 #include <string>
 #include "gpu_path_integrator.h"
 #include "integrator.h"
+#include "png_writer.h"
 #include "scenes.h"
 
 namespace
@@ -64,7 +65,7 @@ int main(int argc, const char **argv)
     int nx = 512, ny = 512;
     uint_fast64_t ns = 100;
     constexpr int comp = 3;
-    std::string scene_name = "cornell", integrator_name = "gpu_path", out = "out_test", checkpoint, resume;
+    std::string scene_name = "cornell", integrator_name = "gpu_path", out = "out_test", checkpoint, resume, png;
     int gpus = 1;
     uint32_t seed = 1;
     for (int i = 1; i < argc; ++i)
@@ -78,6 +79,7 @@ int main(int argc, const char **argv)
         else if (a == "--seed") seed = (uint32_t)std::atoll(next());
         else if (a == "--out") out = next();
         else if (a == "--checkpoint") checkpoint = next();
+        else if (a == "--png") png = next();
         else if (a == "--resume") resume = next();
         else if (a == "--res") { const char *r = next(); if (std::sscanf(r, "%dx%d", &nx, &ny) != 2) { std::cerr << "bad --res\n"; return 2; } }
         else { std::cerr << "unknown argument " << a << "\n"; return 2; }
@@ -122,6 +124,8 @@ int main(int argc, const char **argv)
                   << " shadow rays in " << st.render_ms << " ms device time = "
                   << (st.closest_rays + st.shadow_rays) / (st.render_ms * 1e3) << " Mrays/s" << std::endl;
         if (!checkpoint.empty()) write_checkpoint(checkpoint, nx, ny, (uint32_t)ns, render.seed, li, render.max_depth, scene_name, final_sums);
+        // what the reference's window shows (viewer::out_image, viewer.cpp:117-125), as a file
+        if (!png.empty() && !frt_png::write_rgb8(png, film_viewer.out_image.get(), nx, ny)) throw std::runtime_error("cannot write " + png);
         film_viewer.save_and_destroy(out + "_" + std::to_string(render_time) + "s");
         gpu_path_integrator::release_cached_context();
     }

@@ -53,6 +53,11 @@ FRT_API int frth_cancel(void);
 /* viewer::out_image of the last frth_render: the 8-bit tone-mapped film (viewer.cpp:117-125), nx*ny*3 bytes. */
 FRT_API int frth_last_ldr(unsigned char *out, size_t n_bytes);
 
+/* The window of the reference (viewer.cpp:18-107 shows viewer::out_image through GL) does not exist on a headless
+ * box: the 8-bit tone-mapped film goes to a PNG file instead (8-bit RGB, rows flipped so that row 0 = bottom ends up
+ * at the bottom of the picture; image.cpp:30 flips on write too).  `frt_main --png FILE` calls it after the render. */
+FRT_API int frth_write_png(const char *path, const unsigned char *rgb, int nx, int ny);
+
 #ifdef __cplusplus
 }
 #endif

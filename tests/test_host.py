@@ -388,3 +388,29 @@ def test_wide8_nodes_contain_the_wide4_tree(built, name, aspect, soup):
     assert max(n_children) <= 8 and (len(n4) < 100 or np.mean(n_children) > 4.5)
     print(f"{name or 'soup'}: {len(n4)} 4-wide nodes ({128 * len(n4)} B) -> {len(words)} 8-wide nodes ({96 * len(words)} B), "
           f"depth {depth}, mean children {np.mean(n_children):.2f}")
+
+
+def test_png_writer_round_trip(built, tmp_path):
+    """frth_write_png (the headless stand-in for the reference's GL window): a valid PNG — signature, chunk CRCs, zlib
+    stream with its Adler-32 — that decodes to the film with the rows flipped (row 0 of the film is the bottom row)."""
+    import struct
+    import zlib
+    rng = np.random.default_rng(3)
+    for ny, nx in ((1, 1), (7, 5), (300, 401)):  # the last one spans several 65535-byte stored blocks
+        film = rng.integers(0, 256, (ny, nx, 3), dtype=np.uint8)
+        path = tmp_path / f"film_{nx}x{ny}.png"
+        api.write_png(path, film)
+        raw = path.read_bytes()
+        assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+        pos, chunks = 8, []
+        while pos < len(raw):
+            n, tag = struct.unpack(">I4s", raw[pos:pos + 8])
+            body = raw[pos + 8:pos + 8 + n]
+            assert struct.unpack(">I", raw[pos + 8 + n:pos + 12 + n])[0] == zlib.crc32(tag + body)
+            chunks.append((tag, body))
+            pos += 12 + n
+        assert [t for t, _ in chunks] == [b"IHDR", b"IDAT", b"IEND"]
+        assert struct.unpack(">IIBBBBB", chunks[0][1]) == (nx, ny, 8, 2, 0, 0, 0)
+        rows = np.frombuffer(zlib.decompress(chunks[1][1]), np.uint8).reshape(ny, 1 + 3 * nx)
+        assert (rows[:, 0] == 0).all()
+        assert np.array_equal(rows[:, 1:].reshape(ny, nx, 3), film[::-1])
