@@ -23,7 +23,7 @@ if what == "soup":
     print(f"soup {n_tri} tris, {n} rays: {n / ms / 1e3:.0f} Mrays/s")
 else:
     spp = int(sys.argv[2]) if len(sys.argv) > 2 else 8
-    scene = api.HostScene(what, 16 / 9, 2)
+    scene = api.HostScene(what, 16 / 9, 0)  # leaf size by scene size, as the bench
     ctx = api.Context(devices=[0]); ctx.upload(scene)
     for _ in range(2):
         ctx.clear_film(); ctx.render_tile(1920, 1080, 0, spp, seed=1)
