@@ -395,7 +395,7 @@ def config_soup(rig: Rig, n_tri: int, n_rays: int, peaks):
     torch, api = rig.torch, rig.api
     t0 = time.time()
     tri = api.soup_triangles(n_tri)
-    scene = api.HostScene(soup=tri, fast_bvh=True, max_leaf=int(os.environ.get("SOUP_LEAF", "4")))
+    scene = api.HostScene(soup=tri, fast_bvh=True, max_leaf=int(os.environ.get("SOUP_LEAF", "3")))
     build_s = time.time() - t0
     del tri
     t0 = time.time()

@@ -261,8 +261,9 @@ FRT_API int frt_stream_handle(frt_ctx *ctx, int dev, void **stream);
  * world->hit(r, EPSILON, 1 - SHADOW_EPSILON, rec) (FRT_TRACE_ANY_HIT, path.cpp:50; only prim_id >= 0 / -1 is
  * meaningful) return for each ray.  Host buffers; the rays are block-partitioned over the context's devices, which
  * copy, trace and copy back AT THE SAME TIME (per-device streams and ctx-owned device buffers that persist between
- * calls).  Buffers from frt_host_alloc (or any pinned memory) are copied asynchronously at link speed; pageable ones
- * go through one host thread per device.  FRT_TRACE_SORT: the rays are first put in Morton order of (origin cell,
+ * calls).  Buffers from frt_host_alloc (or any pinned memory) move in chunks of 2^21 rays on separate copy streams, so
+ * that the copy in of chunk k+1 and the copy out of chunk k-1 run under the cast of chunk k; pageable ones go through
+ * one host thread per device.  FRT_TRACE_SORT: the rays are first put in Morton order of (origin cell,
  * direction octant) by a device radix sort — only the order they are traced in changes, every hit lands at its ray's
  * index.  `device_ms` (may be NULL) = sort + kernel time, max over devices.  With FRT_WIDE8=1 in the environment the
  * casts walk 8-wide compressed nodes derived at upload (same hits; measured slower than the 4-wide walk, off by default). */

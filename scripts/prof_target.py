@@ -9,7 +9,7 @@ if what == "soup":
     import torch
     n_tri = int(float(sys.argv[2])) if len(sys.argv) > 2 else 10_000_000
     n = int(sys.argv[3]) if len(sys.argv) > 3 else 1 << 22
-    scene = api.HostScene(soup=api.soup_triangles(n_tri), fast_bvh=True, max_leaf=int(os.environ.get("SOUP_LEAF", "4")))
+    scene = api.HostScene(soup=api.soup_triangles(n_tri), fast_bvh=True, max_leaf=int(os.environ.get("SOUP_LEAF", "3")))
     ctx = api.Context(devices=[0]); ctx.upload(scene)
     dev = torch.device("cuda", 0)
     g = torch.Generator(device=dev); g.manual_seed(0x5EED0002)
