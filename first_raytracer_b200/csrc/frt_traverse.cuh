@@ -174,7 +174,11 @@ struct Walker
         sx = idx < 0.0f ? 1 : 0; sy = idy < 0.0f ? 1 : 0; sz = idz < 0.0f ? 1 : 0;
         sp = 0;
         cur = 0;
-        active = sc.n_nodes != 0;
+        // A NaN in the ray misses everything in the reference too (every comparison of aabb.h:24-28 and
+        // triangle.h:80-89 is false: no box is rejected, no triangle accepted) — after visiting the whole tree.
+        // The same answer without the walk.
+        const float s = o.x + o.y + o.z + d.x + d.y + d.z;
+        active = sc.n_nodes != 0 && s == s;
     }
 
     // ---- while-while, part 1 over the 4-wide nodes: descend through inner nodes (EMPTY carries the leaf bit and

@@ -287,14 +287,17 @@ def test_trace_edge_cases(built):
     ctx.upload(scene)
     hits, _ = ctx.trace(np.zeros(0, dtype=api.RAY_DTYPE))  # empty batch
     assert hits.shape == (0,)
-    # outside pointing away; zero-length direction; straight at the back wall; axis-parallel downwards
-    rays = np.zeros(4, dtype=api.RAY_DTYPE)
-    rays["o"] = [[0, 1, 10], [0, 1, 0.5], [0, 1.5, 3], [0.3, 0.7, 0.2]]
-    rays["d"] = [[0, 0, 1], [0, 0, 0], [0, 0, -1], [0, -1, 0]]
+    # outside pointing away; zero-length direction; straight at the back wall; axis-parallel downwards; a NaN in the
+    # direction / in the origin (every comparison of aabb.h and triangle.h is false: a miss)
+    rays = np.zeros(6, dtype=api.RAY_DTYPE)
+    rays["o"] = [[0, 1, 10], [0, 1, 0.5], [0, 1.5, 3], [0.3, 0.7, 0.2], [0, 1, 3], [np.nan, 1, 3]]
+    rays["d"] = [[0, 0, 1], [0, 0, 0], [0, 0, -1], [0, -1, 0], [0, np.nan, -1], [0, 0, -1]]
     hits, _ = ctx.trace(rays)
     want = oracle_c.Oracle(scene).trace(rays)
     assert (hits["prim_id"] == want["prim"]).all()
-    assert hits["prim_id"][0] == -1 and hits["prim_id"][1] == -1
+    assert hits["prim_id"][0] == -1 and hits["prim_id"][1] == -1 and hits["prim_id"][4] == -1 and hits["prim_id"][5] == -1
+    occ, _ = ctx.trace(rays, any_hit=True)
+    assert occ["prim_id"][4] == -1 and occ["prim_id"][5] == -1
     assert hits["prim_id"][2] >= 0 and abs(hits["t"][2] - 4.04) < 1e-4  # back wall z = -1.04
     # ragged sizes around the 32-ray warp batches
     for n in (1, 31, 33, 1000):
