@@ -241,6 +241,40 @@ def test_pinned_buffers_and_empty_or_ragged_batches(built):
     pr.close(); ph.close()
 
 
+def test_pipelined_chunks_give_the_hits_of_one_copy(built, monkeypatch):
+    """frt_trace_rays moves a pinned batch in chunks on three streams (copy in / cast / copy out overlapped).  With a
+    small chunk (FRT_TRACE_CHUNK) one call makes many chunks, the last one ragged, on two device records and with the
+    Morton sort inside every chunk: every hit must land at its ray's index, equal to the single-copy pageable path."""
+    scene = api.HostScene("teapot", 16 / 9, 2)
+    rays = _rays_for(scene, 200_001, seed=5)
+    info = scene.info
+    segs = refutil.segment_rays(150_007, info["bounds_lo"], info["bounds_hi"], seed=6)
+    monkeypatch.setenv("FRT_TRACE_CHUNK", "1000000000")
+    ctx = api.Context(devices=[0]); ctx.upload(scene)
+    want, _ = ctx.trace(rays)              # pageable: one copy, one cast
+    want_occ, _ = ctx.trace(segs, any_hit=True)
+    ctx.close()
+    monkeypatch.setenv("FRT_TRACE_CHUNK", "30000")
+    for devices in ([0], [0, 0]):
+        ctx = api.Context(devices=devices); ctx.upload(scene)
+        pr, ph = api.Pinned(rays.shape[0], api.RAY_DTYPE), api.Pinned(rays.shape[0], api.HIT_DTYPE)
+        pr.array[:] = rays
+        for sort in (False, True):
+            ph.array["prim_id"] = -5
+            got, ms = ctx.trace(pr.array, hits=ph.array, sort=sort)
+            assert np.array_equal(got["prim_id"], want["prim_id"]) and np.array_equal(got["t"], want["t"]), (devices, sort)
+            assert ms > 0
+        got = None
+        pr.close(); ph.close()
+        ps, po = api.Pinned(segs.shape[0], api.RAY_DTYPE), api.Pinned(segs.shape[0], api.HIT_DTYPE)
+        ps.array[:] = segs
+        occ, _ = ctx.trace(ps.array, any_hit=True, hits=po.array)
+        assert np.array_equal(occ["prim_id"] >= 0, want_occ["prim_id"] >= 0)
+        occ = None
+        ps.close(); po.close()
+        ctx.close()
+
+
 def test_ten_million_triangle_soup_parity(built):
     """SURVEY §8d config 5 at its FULL size: the 10^7-triangle soup (0.9 GB, the only workload that lives in HBM, walked
     over the 8-wide nodes), its 2^20-ray parity prefix and 2^20 shadow segments against the C oracle's own BVH walk
