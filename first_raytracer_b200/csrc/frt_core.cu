@@ -270,7 +270,9 @@ __device__ __forceinline__ void frt_trace_count(Counters *ctr, unsigned int n_ra
 // occlusion queries 8 (64 registers).
 // OCC = CTAs of 128 threads per SM the register budget is cut for (4: 128 registers, 6: 85, 8: 64, 12: 42).
 // The first FRT_TRACE_SMEM_STACK stack entries of every thread live in shared memory (HybridStack).
+#ifndef FRT_TRACE_SMEM_STACK
 #define FRT_TRACE_SMEM_STACK 12
+#endif
 template <bool ANY, bool COUNT, int OCC, int WIDE>
 __device__ __forceinline__ void frt_trace_body(const DevScene &sc, Counters *ctr, const float2 *rays, frt_hit *hits, const unsigned int *order,
                                                const unsigned int n, const int refill_below)
