@@ -132,6 +132,32 @@ Scene *teapot_scene(const double &aspect, frt_scene_ids *ids)
     return finish(list, cam, Vector3f(0.05, 0.06, 0.08), lights, ids);
 }
 
+// furnace_test_scene (main.cpp:177-221): the teapot through create_triangle_mesh(file, toWorld = identity, bsdf, lights)
+// with a dielectric(1.5) on every mesh, NO lights (pick_sample gives -1 and path.cpp:40 skips next-event estimation),
+// camera main.cpp:207-212.  Its environment is data/ennis.hdr, which the reference repository does not ship:
+// "furnace+hdr" uses the shipped data/test.hdr (the file main.cpp:170 loads).
+Scene *furnace_test_scene(const double &aspect, frt_scene_ids *ids)
+{
+    std::vector<hitable *> list, lights;
+    Matrix4x4 I;
+    I.set_identity();
+    auto meshes = mesh_loader::load_obj(asset("cube/teapot.obj"), false);
+    Matrix4x4 inv;
+    if (!I.invert(inv)) throw std::runtime_error("Cannot compute inverse. Matrix isn't singular.");
+    for (auto &m : meshes)
+    {
+        m->mat.reset(new dielectric(1.5, new constant_texture(Vector3f(1.0, 1.0, 1.0)), new constant_texture(Vector3f(1.0, 1.0, 1.0))));
+        for (int j = 0; j < m->nVertices; ++j)
+        {
+            m->vertices[j] = I * m->vertices[j];
+            m->normals[j] = inv.normal_transform(m->normals[j]);
+        }
+        add_mesh(m, list, lights);
+    }
+    camera cam(Vector3f(0, 125, 175.0), Vector3f(0, 50, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.0, 300.0);
+    return finish(list, cam, Vector3f(0.0, 0.0, 0.0), lights, ids);
+}
+
 // A reduced random_scene (main.cpp:55-113): the 1000-radius ground sphere under a checker_texture, the sphere light,
 // small spheres of the three materials random_scene draws (lambertian / metal / dielectric) on a fixed grid, plus
 // checker_texture (texture.h:30-49) and image_texture (texture.h:51-112) on spheres (get_sphere_uv hitable.h:15-21)
@@ -256,6 +282,7 @@ Scene *make_scene(const std::string &name, double aspect, frt_scene_ids *ids)
     if (name == "veach_beckmann") return veach_mis(aspect, ids, "beckmann");
     if (name == "textured") return textured_scene(aspect, ids);
     if (name == "teapot") return teapot_scene(aspect, ids);
+    if (name == "furnace" || name == "furnace_test_scene") return furnace_test_scene(aspect, ids);
     if (name.rfind("soup:", 0) == 0)
     {
         const size_t n = (size_t)std::atoll(name.c_str() + 5);

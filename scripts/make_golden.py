@@ -113,7 +113,9 @@ ROUND2_RENDER = [("veach_beckmann", 48, 32, 4, "path"), ("veach_beckmann", 192, 
                  ("cornell_lens", 32, 32, 2, "path"), ("cornell_lens", 96, 96, 8, "path"),
                  ("textured", 48, 32, 2, "path"), ("textured", 192, 128, 8, "path"), ("textured+hdr", 48, 32, 2, "path"),
                  ("textured", 96, 64, 2, "direct"), ("textured", 96, 64, 1, "normals"),
-                 ("veach_beckmann+sky", 48, 32, 2, "ao")]
+                 ("veach_beckmann+sky", 48, 32, 2, "ao"),
+                 # furnace_test_scene (main.cpp:177-221): dielectric teapot, NO lights, image environment
+                 ("furnace+hdr", 48, 27, 2, "path"), ("furnace+hdr", 160, 90, 4, "path")]
 
 
 def main():

@@ -47,7 +47,9 @@ OTHER_INTEGRATOR_CASES = [("teapot", 48, 27, 2, "ao"), ("cornell_glossy+sky", 32
                           ("teapot+hdr", 48, 27, 2, "path"), ("veach+hdr", 48, 32, 2, "path"),
                           ("teapot+hdr", 160, 90, 4, "path"),
                           ("textured", 96, 64, 2, "direct"), ("textured", 96, 64, 1, "normals"),
-                          ("veach_beckmann+sky", 48, 32, 2, "ao")]
+                          ("veach_beckmann+sky", 48, 32, 2, "ao"),
+                          # furnace_test_scene (main.cpp:177-221): dielectric mesh, no lights (NEE skipped, path.cpp:40)
+                          ("furnace+hdr", 48, 27, 2, "path")]
 
 
 @pytest.mark.parametrize("name,nx,ny,spp,integrator", OTHER_INTEGRATOR_CASES)
