@@ -63,8 +63,10 @@ Scene *cornell_box_obj(const double &aspect, const char *variant, frt_scene_ids 
     std::vector<hitable *> list, lights;
     const bool own_file = variant && (std::string(variant) == "Glossy" || std::string(variant) == "Sphere");
     const std::string file = std::string("CornellBox/CornellBox-") + (own_file ? variant : "Original") + ".obj";
-    // Use geometry normals (main.cpp:229)
-    auto meshes = mesh_loader::load_obj(asset(file), true);
+    // Use geometry normals (main.cpp:229); "Ao" = cornell_box_ao (main.cpp:254-280): the same file with its (generated,
+    // smooth) vertex normals and a white environment
+    const std::string var = variant ? variant : "Original";
+    auto meshes = mesh_loader::load_obj(asset(file), var != "Ao");
     // CornellBox-Glossy.mtl as shipped has no `light` entry, so that scene renders black; give the
     // `light` group the emitter of CornellBox-Original.mtl:81-88 (the oracle driver does the same).
     for (auto &m : meshes)
@@ -72,14 +74,13 @@ Scene *cornell_box_obj(const double &aspect, const char *variant, frt_scene_ids 
             m->mat.reset(new diffuse_light(new constant_texture(Vector3f(17, 12, 4))));
     // "Metal": CornellBox-Original with the tall box as a `metal` mirror (material.h:111-130; as shipped only
     // random_scene uses that class); "Lens": CornellBox-Original through a thin lens (camera.h:10-35)
-    const std::string var = variant ? variant : "Original";
     if (var == "Metal")
         for (auto &m : meshes)
             if (m->name == "tallBox") m->mat.reset(new metal(Vector3f(0.8, 0.7, 0.6)));
     for (auto &m : meshes) add_mesh(m, list, lights);
     camera cam = var == "Lens" ? camera(Vector3f(0, 1, 3.9f), Vector3f(0, 1, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.2, 4.0)
                                : camera(Vector3f(0, 1, 3.9f), Vector3f(0, 1, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.0, 10.0);
-    return finish(list, cam, Vector3f(0.0, 0.0, 0.0), lights, ids);
+    return finish(list, cam, var == "Ao" ? Vector3f(1.0, 1.0, 1.0) : Vector3f(0.0, 0.0, 0.0), lights, ids);
 }
 
 Scene *veach_mis(const double &aspect, frt_scene_ids *ids, const char *distribution)
@@ -278,6 +279,7 @@ Scene *make_scene(const std::string &name, double aspect, frt_scene_ids *ids)
     if (name == "cornell_sphere") return cornell_box_obj(aspect, "Sphere", ids);
     if (name == "cornell_metal") return cornell_box_obj(aspect, "Metal", ids);
     if (name == "cornell_lens") return cornell_box_obj(aspect, "Lens", ids);
+    if (name == "cornell_ao" || name == "cornell_box_ao") return cornell_box_obj(aspect, "Ao", ids);
     if (name == "veach" || name == "veach_mis") return veach_mis(aspect, ids, "ggx");
     if (name == "veach_beckmann") return veach_mis(aspect, ids, "beckmann");
     if (name == "textured") return textured_scene(aspect, ids);

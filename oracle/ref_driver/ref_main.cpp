@@ -189,7 +189,8 @@ static built_scene &build_scene(const std::string &full_name, double aspect)
     camera cam;
     Vector3f env(0, 0, 0);
 
-    if (name == "cornell" || name == "cornell_glossy" || name == "cornell_sphere" || name == "cornell_metal" || name == "cornell_lens")
+    if (name == "cornell" || name == "cornell_glossy" || name == "cornell_sphere" || name == "cornell_metal" || name == "cornell_lens" ||
+        name == "cornell_ao")
     {
         // main.cpp:222-252 (cornell_box_obj)
         // cornell_metal: the tall box becomes a `metal` mirror (material.h:111-130, only random_scene uses it as shipped)
@@ -197,7 +198,10 @@ static built_scene &build_scene(const std::string &full_name, double aspect)
         const char *file = name == "cornell_glossy" ? "/CornellBox/CornellBox-Glossy.obj"
                          : name == "cornell_sphere" ? "/CornellBox/CornellBox-Sphere.obj"
                                                     : "/CornellBox/CornellBox-Original.obj";
-        b.meshes = read_obj(g_assets + file, true);
+        // cornell_ao  : cornell_box_ao, main.cpp:254-280 — the same file WITHOUT use_geometry_normals, so shading uses the
+        //                vertex normals Assimp's GenSmoothNormals makes (box corners get rounded), white environment
+        b.meshes = read_obj(g_assets + file, name != "cornell_ao");
+        if (name == "cornell_ao") env = Vector3f(1.0, 1.0, 1.0);
         // CornellBox-Glossy.mtl has no `light` entry (the shipped scene is black): same emitter as Original
         for (auto &m : b.meshes)
             if (m->name == "light" && !dynamic_cast<diffuse_light *>(m->mat.get()))

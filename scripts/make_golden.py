@@ -115,7 +115,10 @@ ROUND2_RENDER = [("veach_beckmann", 48, 32, 4, "path"), ("veach_beckmann", 192, 
                  ("textured", 96, 64, 2, "direct"), ("textured", 96, 64, 1, "normals"),
                  ("veach_beckmann+sky", 48, 32, 2, "ao"),
                  # furnace_test_scene (main.cpp:177-221): dielectric teapot, NO lights, image environment
-                 ("furnace+hdr", 48, 27, 2, "path"), ("furnace+hdr", 160, 90, 4, "path")]
+                 ("furnace+hdr", 48, 27, 2, "path"), ("furnace+hdr", 160, 90, 4, "path"),
+                 # cornell_box_ao (main.cpp:254-280): Cornell with Assimp's smooth vertex normals, white environment
+                 ("cornell_ao", 32, 32, 2, "ao"), ("cornell_ao", 96, 96, 8, "ao"), ("cornell_ao", 32, 32, 2, "path"),
+                 ("cornell_ao", 32, 32, 1, "normals")]
 
 
 def main():

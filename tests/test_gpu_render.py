@@ -109,7 +109,10 @@ def test_same_random_numbers_as_golden(built, name, nx, ny, spp):
                                                        ("textured", 96, 64, 2, "direct"), ("textured", 96, 64, 1, "normals"),
                                                        ("veach_beckmann+sky", 48, 32, 2, "ao"), ("textured+hdr", 48, 32, 2, "path"),
                                                        # furnace_test_scene (main.cpp:177-221): dielectric mesh, NO lights
-                                                       ("furnace+hdr", 48, 27, 2, "path"), ("furnace+hdr", 160, 90, 4, "path")])
+                                                       ("furnace+hdr", 48, 27, 2, "path"), ("furnace+hdr", 160, 90, 4, "path"),
+                                                       # cornell_box_ao (main.cpp:254-280): smooth generated normals, white environment
+                                                       ("cornell_ao", 32, 32, 2, "ao"), ("cornell_ao", 96, 96, 8, "ao"),
+                                                       ("cornell_ao", 32, 32, 2, "path"), ("cornell_ao", 32, 32, 1, "normals")])
 def test_other_integrators_match_golden(built, name, nx, ny, spp, integrator):
     """gpu_ao_integrator / gpu_normals_integrator / gpu_ass_1_integrator (same trace kernels, another shade stage) and the environment
     term of the path integrator against fixtures rendered by the compiled reference's ao::Li /

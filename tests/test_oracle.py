@@ -49,7 +49,9 @@ OTHER_INTEGRATOR_CASES = [("teapot", 48, 27, 2, "ao"), ("cornell_glossy+sky", 32
                           ("textured", 96, 64, 2, "direct"), ("textured", 96, 64, 1, "normals"),
                           ("veach_beckmann+sky", 48, 32, 2, "ao"),
                           # furnace_test_scene (main.cpp:177-221): dielectric mesh, no lights (NEE skipped, path.cpp:40)
-                          ("furnace+hdr", 48, 27, 2, "path")]
+                          ("furnace+hdr", 48, 27, 2, "path"),
+                          # cornell_box_ao (main.cpp:254-280): smooth generated normals on the Cornell box, white environment
+                          ("cornell_ao", 32, 32, 2, "ao"), ("cornell_ao", 32, 32, 2, "path"), ("cornell_ao", 32, 32, 1, "normals")]
 
 
 @pytest.mark.parametrize("name,nx,ny,spp,integrator", OTHER_INTEGRATOR_CASES)
