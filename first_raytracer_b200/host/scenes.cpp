@@ -4,6 +4,7 @@
 // fix: veach plates are rough_conductor with the alphas of veach_mi/mi.xml and the root is a
 // parallel_bvh_node; the unshipped Mitsuba matpreview mesh is replaced by cube/teapot.obj.
 #include "scenes.h"
+#include <random>
 #include <cstdlib>
 #include <stdexcept>
 #include "mesh_loader.h"
@@ -205,6 +206,49 @@ Scene *textured_scene(const double &aspect, frt_scene_ids *ids)
     return finish(list, cam, Vector3f(0.15, 0.18, 0.24), lights, ids);
 }
 
+// random_scene, main.cpp:55-113, as written: 22 x 22 cells, one 0.2-radius sphere per cell unless it would touch the
+// spot at (4, 0.2, 0); lambertian / metal / dielectric by a uniform draw; the checkered 1000-radius ground sphere,
+// the sphere light, the thin-lens camera (aperture 0.1).  The reference seeds its sampler with time(0)
+// (sampler.h:14), so every run of it places other spheres: this is the instance of std::mt19937(1), with the
+// draws taken one per statement (the reference leaves their order to the compiler: constructor arguments).
+// Centres are rounded to float32 (the C ABI carries spheres as float32).  Its environment, data/grace.hdr, is not
+// in the repository: "random_scene+hdr" uses the shipped data/test.hdr.
+Scene *random_scene(const double &aspect, frt_scene_ids *ids)
+{
+    std::vector<hitable *> list, lights;
+    std::mt19937 engine(1);
+    auto get1d = [&engine]() { return std::uniform_real_distribution<>(0.0, 1.0)(engine); };
+    texture *checker = new checker_texture(new constant_texture(Vector3f(0.2f, 0.3f, 0.1f)),
+                                           new constant_texture(Vector3f(0.99f, 0.99f, 0.99f)), 1, 1);
+    list.push_back(new sphere(Vector3f(0, -1000, 0), 1000, new lambertian(checker)));
+    list.push_back(new sphere(Vector3f(0, 1.5, 0), 1.5, new diffuse_light(new constant_texture(Vector3f(10, 10, 10)))));
+    lights.push_back(new sphere(Vector3f(0, 1.5, 0), 1.5, new diffuse_light(new constant_texture(Vector3f(10, 10, 10)))));
+    for (int a = -11; a < 11; a++)
+        for (int c = -11; c < 11; c++)
+        {
+            const double choose_mat = get1d();
+            const double ux = get1d();
+            const double uz = get1d();
+            const Vector3f center((float)(a + 0.9f * ux), 0.2f, (float)(c + 0.9f * uz));
+            if (!((center - Vector3f(4, 0.2f, 0)).length() > 0.9f)) continue;
+            if (choose_mat < 0.5)
+            {
+                const double r0 = get1d(), r1 = get1d(), g0 = get1d(), g1 = get1d(), b0 = get1d(), b1 = get1d();
+                list.push_back(new sphere(center, 0.2f, new lambertian(new constant_texture(Vector3f(r0 * r1, g0 * g1, b0 * b1)))));
+            }
+            else if (choose_mat < 0.75)
+            {
+                const double r = get1d(), g = get1d(), bl = get1d();
+                list.push_back(new sphere(center, 0.2f, new metal(Vector3f(0.5 * (1 + r), 0.5 * (1 + g), 0.5 * (1 + bl)))));
+            }
+            else
+                list.push_back(new sphere(center, 0.2f, new dielectric(1.5, new constant_texture(Vector3f(1.0, 1.0, 1.0)),
+                                                                       new constant_texture(Vector3f(1.0, 1.0, 1.0)))));
+        }
+    camera cam(Vector3f(-15, 2, 1), Vector3f(0, 0, 0), Vector3f(0, 1, 0), 40.0, aspect, 0.1f, 10.0);
+    return finish(list, cam, Vector3f(0.0, 0.0, 0.0), lights, ids);
+}
+
 // splitmix64 stream, centre ~ U[0,1)^3, two edges ~ U[-l,l]^3
 static inline uint64_t splitmix64(uint64_t &s)
 {
@@ -283,6 +327,7 @@ Scene *make_scene(const std::string &name, double aspect, frt_scene_ids *ids)
     if (name == "veach" || name == "veach_mis") return veach_mis(aspect, ids, "ggx");
     if (name == "veach_beckmann") return veach_mis(aspect, ids, "beckmann");
     if (name == "textured") return textured_scene(aspect, ids);
+    if (name == "random_scene") return random_scene(aspect, ids);
     if (name == "teapot") return teapot_scene(aspect, ids);
     if (name == "furnace" || name == "furnace_test_scene") return furnace_test_scene(aspect, ids);
     if (name.rfind("soup:", 0) == 0)

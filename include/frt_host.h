@@ -22,7 +22,7 @@ typedef struct frth_info {
 
 FRT_API const char *frth_last_error(void);
 /* name: cornell | cornell_ao | cornell_glossy | cornell_sphere | cornell_metal | cornell_lens | veach | veach_beckmann | teapot |
- * furnace | textured | soup:<N>, optionally followed by +sky or +hdr (environment); assets are read
+ * furnace | textured | random_scene | soup:<N>, optionally followed by +sky or +hdr (environment); assets are read
  * from $FRT_ASSETS (default ./assets).  max_leaf = triangles per wide-BVH leaf (1..16; 0 = chosen by scene size). */
 FRT_API int frth_scene_create(const char *name, double aspect, int max_leaf, frth_scene **out);
 /* Triangle soup given as n*9 floats (v0,v1,v2). */

@@ -107,7 +107,7 @@ OTHER_INTEGRATOR_CASES = [("teapot", 48, 27, 2, "ao"), ("cornell_glossy+sky", 32
 # Round 2: the branches no shipped scene reaches — Beckmann rough_conductor (pdf.h:280-403), `metal`
 # (material.h:111-130), the thin-lens camera (camera.h:10-35, util.h:21-41) — and surface textures (texture.h:30-112)
 # on the reduced random_scene of ref_main.cpp "textured" (ao is left out there: constant_pdf::generate throws, pdf.h:197).
-ROUND2_TRACE = [("textured", 1.5)]
+ROUND2_TRACE = [("textured", 1.5), ("random_scene", 1.5)]
 ROUND2_RENDER = [("veach_beckmann", 48, 32, 4, "path"), ("veach_beckmann", 192, 128, 16, "path"),
                  ("cornell_metal", 32, 32, 2, "path"), ("cornell_metal", 96, 96, 8, "path"),
                  ("cornell_lens", 32, 32, 2, "path"), ("cornell_lens", 96, 96, 8, "path"),
@@ -118,7 +118,10 @@ ROUND2_RENDER = [("veach_beckmann", 48, 32, 4, "path"), ("veach_beckmann", 192, 
                  ("furnace+hdr", 48, 27, 2, "path"), ("furnace+hdr", 160, 90, 4, "path"),
                  # cornell_box_ao (main.cpp:254-280): Cornell with Assimp's smooth vertex normals, white environment
                  ("cornell_ao", 32, 32, 2, "ao"), ("cornell_ao", 96, 96, 8, "ao"), ("cornell_ao", 32, 32, 2, "path"),
-                 ("cornell_ao", 32, 32, 1, "normals")]
+                 ("cornell_ao", 32, 32, 1, "normals"),
+                 # random_scene (main.cpp:55-113), the std::mt19937(1) instance: 485 spheres, thin lens
+                 ("random_scene", 48, 32, 2, "path"), ("random_scene", 192, 128, 8, "path"), ("random_scene+hdr", 48, 32, 2, "path"),
+                 ("random_scene", 96, 64, 1, "normals")]
 
 
 def main():

@@ -46,7 +46,7 @@ def _whole_image_mean_bar(gpu, ref, close, label):
                                             # round 2: Beckmann plates (pdf.h:280-403), a metal box (material.h:111-130), the thin
                                             # lens (camera.h:30-35), textured surfaces (texture.h:30-112)
                                             ("veach_beckmann", 192, 128, 16), ("cornell_metal", 96, 96, 8),
-                                            ("cornell_lens", 96, 96, 8), ("textured", 192, 128, 8)])
+                                            ("cornell_lens", 96, 96, 8), ("textured", 192, 128, 8), ("random_scene", 192, 128, 8)])
 def test_same_random_numbers_as_reference(built, name, nx, ny, spp):
     if not refutil.have_ref():
         pytest.skip("oracle/_ref not built")
@@ -73,7 +73,8 @@ def test_same_random_numbers_as_reference(built, name, nx, ny, spp):
                                             ("veach_beckmann", 192, 128, 16), ("veach_beckmann", 48, 32, 4),
                                             ("cornell_metal", 96, 96, 8), ("cornell_metal", 32, 32, 2),
                                             ("cornell_lens", 96, 96, 8), ("cornell_lens", 32, 32, 2),
-                                            ("textured", 192, 128, 8), ("textured", 48, 32, 2)])
+                                            ("textured", 192, 128, 8), ("textured", 48, 32, 2),
+                                            ("random_scene", 192, 128, 8), ("random_scene", 48, 32, 2)])
 def test_same_random_numbers_as_golden(built, name, nx, ny, spp):
     """Same check against the committed fixtures (generated from the compiled reference by
     scripts/make_golden.py), so it also runs where oracle/_ref is absent."""
@@ -112,7 +113,10 @@ def test_same_random_numbers_as_golden(built, name, nx, ny, spp):
                                                        ("furnace+hdr", 48, 27, 2, "path"), ("furnace+hdr", 160, 90, 4, "path"),
                                                        # cornell_box_ao (main.cpp:254-280): smooth generated normals, white environment
                                                        ("cornell_ao", 32, 32, 2, "ao"), ("cornell_ao", 96, 96, 8, "ao"),
-                                                       ("cornell_ao", 32, 32, 2, "path"), ("cornell_ao", 32, 32, 1, "normals")])
+                                                       ("cornell_ao", 32, 32, 2, "path"), ("cornell_ao", 32, 32, 1, "normals"),
+                                                       # random_scene (main.cpp:55-113): 485 spheres, thin lens
+                                                       ("random_scene", 48, 32, 2, "path"), ("random_scene+hdr", 48, 32, 2, "path"),
+                                                       ("random_scene", 96, 64, 1, "normals")])
 def test_other_integrators_match_golden(built, name, nx, ny, spp, integrator):
     """gpu_ao_integrator / gpu_normals_integrator / gpu_ass_1_integrator (same trace kernels, another shade stage) and the environment
     term of the path integrator against fixtures rendered by the compiled reference's ao::Li /

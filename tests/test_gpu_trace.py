@@ -20,7 +20,7 @@ from first_raytracer_b200 import api
 
 pytestmark = pytest.mark.gpu
 
-SCENES = [("cornell", 1.0), ("veach", 1.5), ("teapot", 16 / 9), ("cornell_sphere", 1.0)]
+SCENES = [("cornell", 1.0), ("veach", 1.5), ("teapot", 16 / 9), ("cornell_sphere", 1.0), ("random_scene", 1.5)]
 
 
 def _rays_for(scene: api.HostScene, n_random: int, seed: int):
