@@ -45,6 +45,11 @@ int frt_create(frt_ctx **out, const int *devices, int n)
     if (const char *s = getenv("FRT_TRACE_OCC")) c->trace_occ[0] = std::min(3, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_TRACE_OCC_ANY")) c->trace_occ[1] = std::min(3, std::max(0, atoi(s)));
     if (const char *s = getenv("FRT_TRACE_REFILL")) c->trace_refill[0] = std::min(31, std::max(0, atoi(s)));
+    if (const char *s = getenv("FRT_SORT_BITS"))
+    {
+        int o = 9, dd = 1;
+        if ((sscanf(s, "%d,%d", &o, &dd) == 2 || sscanf(s, "%d:%d", &o, &dd) == 2) && o >= 1 && o <= 9 && dd >= 1 && dd <= 9 && 3 * (o + dd) <= 32) { c->sort_bits[0] = o; c->sort_bits[1] = dd; }
+    }
     if (const char *s = getenv("FRT_TRACE_CHUNK")) c->trace_chunk = (size_t)std::max(1024ll, atoll(s));
     if (const char *s = getenv("FRT_TRACE_REFILL_ANY")) c->trace_refill[1] = std::min(31, std::max(-1, atoi(s)));
 

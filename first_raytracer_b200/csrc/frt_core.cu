@@ -88,6 +88,7 @@ struct frt_ctx
                                   // incoherent scene is latency-bound: 8 CTAs of 64 registers measured +25 % over 4 of 128)
     int trace_refill[2] = {20, 20}; // dynamic fetch threshold for closest / occlusion casts (-1: plain batches of 32); re-measured once no
                                     // pathological ray hid the differences (profiles/r02_soup_sweep_clean.log): occlusion casts +35 % over -1
+    int sort_bits[2] = {9, 1};     // FRT_TRACE_SORT key: bits per axis of the origin cell / of the direction (FRT_SORT_BITS=o,d)
     size_t trace_chunk = 1u << 21; // frt_trace_rays with pinned buffers: rays per pipelined chunk (FRT_TRACE_CHUNK)
     int wide8 = 0;                // ray casting over the 8-wide compressed nodes (FRT_WIDE8=1): off by default, measured slower
     bool have_wide8 = false;

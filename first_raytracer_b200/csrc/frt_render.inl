@@ -391,7 +391,7 @@ int frt_trace_rays_device(frt_ctx *ctx, int dev, const void *d_rays, size_t n, v
     }
     CU(cudaEventRecord(d.ev_t0, d.stream));
     if (mode & FRT_TRACE_SORT) // the ordering is part of the call and of its device time
-        CU(frt_sort_rays(r, (unsigned int)n, ctx->bounds_lo, ctx->bounds_hi, (uint32_t *)d.d_sort, &order, d.stream, &d.launches));
+        CU(frt_sort_rays(r, (unsigned int)n, ctx->bounds_lo, ctx->bounds_hi, (uint32_t *)d.d_sort, &order, d.stream, &d.launches, ctx->sort_bits[0], ctx->sort_bits[1]));
     {
         const int a = any_hit ? 1 : 0, w8 = ctx->have_wide8 ? 1 : 0, occ = ctx->trace_occ[a];
         trace_kernels[w8][a][count ? 1 : 0][occ]<<<d.blocks_trace[w8][a][occ], 128, 0, d.stream>>>(sc, d.d_ctr, r, h, order, (unsigned int)n,
@@ -433,7 +433,7 @@ int frt_trace_rays_device_noalloc(frt_ctx *ctx, int dev, const void *d_rays, siz
     // written in full by each pass before they are read, so the previous call's contents do not matter.
     CU(cudaMemsetAsync(&d.d_ctr->trace_next, 0, sizeof(unsigned int), d.stream));
     CU(cudaEventRecord(d.ev_t0, d.stream));
-    CU(frt_sort_rays((const float2 *)d_rays, (unsigned int)n, ctx->bounds_lo, ctx->bounds_hi, d.d_noalloc_scratch, &order, d.stream, &d.launches));
+    CU(frt_sort_rays((const float2 *)d_rays, (unsigned int)n, ctx->bounds_lo, ctx->bounds_hi, d.d_noalloc_scratch, &order, d.stream, &d.launches, ctx->sort_bits[0], ctx->sort_bits[1]));
     const int a = any_hit ? 1 : 0, w8 = ctx->have_wide8 ? 1 : 0, occ = ctx->trace_occ[a];
     trace_kernels[w8][a][count ? 1 : 0][occ]<<<d.blocks_trace[w8][a][occ], 128, 0, d.stream>>>(sc, d.d_ctr, (const float2 *)d_rays, (frt_hit *)d_hits, order,
                                                                                          (unsigned int)n, ctx->trace_refill[a]);

@@ -20,16 +20,23 @@ __device__ __forceinline__ uint32_t frt_spread3(uint32_t v) // 9 bits -> every t
     return v;
 }
 
-__global__ void k_morton_keys(const float2 *rays, unsigned int n, float3 lo, float3 inv_ext, uint32_t *keys, uint32_t *idx)
+// Key layout: `ob` bits per axis of the origin's cell (Morton-interleaved, high part) and `db` bits per axis of the unit
+// direction (Morton-interleaved, low part); 3 * (ob + db) <= 32.  db = 1 is the direction octant.
+__global__ void k_morton_keys(const float2 *rays, unsigned int n, float3 lo, float3 inv_ext, uint32_t *keys, uint32_t *idx, int ob, int db)
 {
+    const float oscale = (float)(1u << ob), dscale = (float)(1u << db);
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
     {
         const float2 r0 = __ldg(rays + 3 * (size_t)i), r1 = __ldg(rays + 3 * (size_t)i + 1), r2 = __ldg(rays + 3 * (size_t)i + 2);
         const float fx = fminf(fmaxf((r0.x - lo.x) * inv_ext.x, 0.0f), 0.999999f), fy = fminf(fmaxf((r0.y - lo.y) * inv_ext.y, 0.0f), 0.999999f),
                     fz = fminf(fmaxf((r1.x - lo.z) * inv_ext.z, 0.0f), 0.999999f);
-        const uint32_t m = frt_spread3((uint32_t)(fx * 512.0f)) | (frt_spread3((uint32_t)(fy * 512.0f)) << 1) | (frt_spread3((uint32_t)(fz * 512.0f)) << 2);
-        const uint32_t oct = (r1.y < 0.0f ? 1u : 0u) | (r2.x < 0.0f ? 2u : 0u) | (r2.y < 0.0f ? 4u : 0u);
-        keys[i] = (m << 3) | oct;
+        const uint32_t m = frt_spread3((uint32_t)(fx * oscale)) | (frt_spread3((uint32_t)(fy * oscale)) << 1) | (frt_spread3((uint32_t)(fz * oscale)) << 2);
+        // direction components scaled by the largest one: [-1, 1] -> [0, 1); db = 1 gives the sign bits (octant)
+        const float dm = fmaxf(fmaxf(fabsf(r1.y), fabsf(r2.x)), fmaxf(fabsf(r2.y), 1e-30f));
+        const float gx = fminf(fmaxf(0.5f + 0.5f * r1.y / dm, 0.0f), 0.999999f), gy = fminf(fmaxf(0.5f + 0.5f * r2.x / dm, 0.0f), 0.999999f),
+                    gz = fminf(fmaxf(0.5f + 0.5f * r2.y / dm, 0.0f), 0.999999f);
+        const uint32_t dcode = frt_spread3((uint32_t)(gx * dscale)) | (frt_spread3((uint32_t)(gy * dscale)) << 1) | (frt_spread3((uint32_t)(gz * dscale)) << 2);
+        keys[i] = (m << (3 * db)) | dcode;
         idx[i] = i;
     }
 }
@@ -111,7 +118,8 @@ inline size_t frt_sort_scratch_words(size_t n) { return 4 * n + 256 * (size_t)FR
 
 // Leaves the sorted ray indices in *order_out (inside scratch).  4 passes; all launches on `stream`.
 inline cudaError_t frt_sort_rays(const float2 *rays, unsigned int n, const float lo[3], const float hi[3], uint32_t *scratch,
-                                 const uint32_t **order_out, cudaStream_t stream, unsigned long long *launches)
+                                 const uint32_t **order_out, cudaStream_t stream, unsigned long long *launches, int origin_bits = 9,
+                                 int dir_bits = 1)
 {
     uint32_t *keys[2] = {scratch, scratch + 2 * (size_t)n}, *idx[2] = {scratch + n, scratch + 3 * (size_t)n};
     unsigned int *hist = scratch + 4 * (size_t)n;
@@ -119,7 +127,7 @@ inline cudaError_t frt_sort_rays(const float2 *rays, unsigned int n, const float
     const float3 inv = make_float3(hi[0] > lo[0] ? 1.0f / (hi[0] - lo[0]) : 0.0f, hi[1] > lo[1] ? 1.0f / (hi[1] - lo[1]) : 0.0f,
                                    hi[2] > lo[2] ? 1.0f / (hi[2] - lo[2]) : 0.0f);
     const unsigned int kb = (unsigned int)((n + 255u) / 256u);
-    k_morton_keys<<<kb < 4096u ? kb : 4096u, 256, 0, stream>>>(rays, n, l, inv, keys[0], idx[0]);
+    k_morton_keys<<<kb < 4096u ? kb : 4096u, 256, 0, stream>>>(rays, n, l, inv, keys[0], idx[0], origin_bits, dir_bits);
     unsigned int n_blocks = (n + 4095u) / 4096u;
     if (n_blocks > FRT_SORT_MAX_BLOCKS) n_blocks = FRT_SORT_MAX_BLOCKS;
     unsigned int per_block = (n + n_blocks - 1u) / n_blocks;
