@@ -453,10 +453,12 @@ def test_checkpoint_and_resume(built, tmp_path):
 def test_frt_main_checkpoint_resume(built, tmp_path):
     """frt_main --checkpoint / --resume: finishing a 3-spp job as an 8-spp job gives the 8-spp film."""
     import subprocess
+    import os
     exe = str(api.PKG_DIR / "frt_main")
+    env = dict(os.environ, FRT_ASSETS=str(refutil.ASSETS))  # the test may be the first one of the process
     def run(*args):
         r = subprocess.run([exe, "--scene", "cornell", "--res", "48x32", "--seed", "5", *args], cwd=tmp_path,
-                           capture_output=True, text=True, timeout=300)
+                           capture_output=True, text=True, timeout=300, env=env)
         assert r.returncode == 0, r.stderr
         return r.stdout
     def sums(name):
@@ -465,20 +467,29 @@ def test_frt_main_checkpoint_resume(built, tmp_path):
         nx, ny, done, seed, version, integ, max_depth, scene_hash = np.frombuffer(raw[8:40], np.uint32)
         assert version == 2 and integ == 0 and max_depth == 34
         return int(done), np.frombuffer(raw[40:], np.float32).reshape(ny, nx, 3)
-    run("--ns", "8", "--checkpoint", "whole.ck")
+    run("--ns", "8", "--checkpoint", "whole.ck", "--png", "whole.png")
+    # --png: the 8-bit tone-mapped film (viewer::out_image, what the reference's window shows) as a file
+    import struct
+    import zlib
+    raw = (tmp_path / "whole.png").read_bytes()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n" and struct.unpack(">II", raw[16:24]) == (48, 32)
+    n_idat = struct.unpack(">I", raw[33:37])[0]
+    assert raw[37:41] == b"IDAT"
+    rows = np.frombuffer(zlib.decompress(raw[41:41 + n_idat]), np.uint8).reshape(32, 1 + 3 * 48)
+    assert rows[:, 1:].max() > 100 and rows[:, 1:].min() == 0  # a lit Cornell box with black surroundings
     run("--ns", "3", "--checkpoint", "part.ck")
     out = run("--ns", "8", "--resume", "part.ck", "--checkpoint", "resumed.ck")
     assert "Resuming at sample 3 of 8" in out
     (dw, whole), (dp, _), (dr, resumed) = sums("whole.ck"), sums("part.ck"), sums("resumed.ck")
     assert (dw, dp, dr) == (8, 3, 8)
     assert np.allclose(whole, resumed, rtol=1e-4, atol=1e-5)
-    bad = subprocess.run([exe, "--res", "40x32", "--ns", "8", "--resume", "part.ck"], cwd=tmp_path, capture_output=True, text=True)
+    bad = subprocess.run([exe, "--res", "40x32", "--ns", "8", "--resume", "part.ck"], cwd=tmp_path, capture_output=True, text=True, env=env)
     assert bad.returncode == 1 and "resolution" in bad.stderr
     # a checkpoint of another scene / integrator is refused instead of silently mixing estimators
-    bad = subprocess.run([exe, "--scene", "veach", "--res", "48x32", "--ns", "8", "--resume", "part.ck"], cwd=tmp_path, capture_output=True, text=True)
+    bad = subprocess.run([exe, "--scene", "veach", "--res", "48x32", "--ns", "8", "--resume", "part.ck"], cwd=tmp_path, capture_output=True, text=True, env=env)
     assert bad.returncode == 1 and "scene" in bad.stderr
     bad = subprocess.run([exe, "--scene", "cornell", "--integrator", "gpu_ao", "--res", "48x32", "--ns", "8", "--resume", "part.ck"],
-                         cwd=tmp_path, capture_output=True, text=True)
+                         cwd=tmp_path, capture_output=True, text=True, env=env)
     assert bad.returncode == 1 and "integrator" in bad.stderr
 
 
