@@ -462,6 +462,19 @@ def config_soup(rig: Rig, n_tri: int, n_rays: int, peaks):
     res["e2e"] = {"value": m * rig.world / wall / 1e6, "unit": "Mrays/s", "rays_per_rank": m, "seconds": wall, "device_ms": dms,
                   "h2d_bytes": m * 24, "d2h_bytes": m * 16, "call": "frt_trace_rays, pinned host rays in / hits out, closest hit, unsorted"}
     pr.close(); ph.close()
+    # what ncu measured on this kernel (another launch size: 2^22 rays; per-ray figures carry over): real DRAM and L2 bytes
+    m, src = ncu_metrics()
+    if m:
+        ncu = {}
+        for key, label in (("k_trace", "closest"), ("k_trace_any", "shadow")):
+            k = m.get(key) or {}
+            if k.get("dram_bytes") and k.get("duration_s"):
+                rays_captured = 1 << 22
+                ncu[label] = {"dram_bytes_per_ray": k["dram_bytes"] / rays_captured, "l2_bytes_per_ray": (k.get("lts_bytes") or 0) / rays_captured,
+                              "dram_gbs": k["dram_bytes"] / k["duration_s"] / 1e9, "dram_frac_of_peak": k["dram_bytes"] / k["duration_s"] / 1e9 / peak,
+                              "issue_active_frac": (k.get("issue_active_pct") or 0) / 100.0, "active_lanes_per_inst": k.get("lanes_per_inst"),
+                              "capture": k.get("capture")}
+        res["ncu"] = dict(ncu, source=src)
     res["clocks"] = sampler.finish()
     res["sm_mhz_per_rank"] = rig.per_rank(res["clocks"].get("sm_mhz") or 0.0)
     scene.close()
